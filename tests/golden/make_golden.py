@@ -1,0 +1,306 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference (run in the build container only).
+
+    make -C oracle ref
+    PYTHONPATH=oracle/_ref:/root/reference python tests/golden/make_golden.py
+
+The reference (numpy physics, Python agents/env, its own C++ PID compiled into oracle/_ref) is imported
+from /root/reference; nothing is copied.  Each fixture stores the inputs (initial states, command /
+action sequences) next to the reference's outputs, so the tests need neither the reference nor this
+script at run time.  Conventions: SoA [field][n]; state rows = N,E,D,u,v,w,phi,theta,psi,p,q,r,time;
+controls rows = elevator, aileron, rudder, throttle (ControlSurfaces.to_array order);
+env actions = aileron, elevator, rudder, throttle (rate_env.py:228-233).
+"""
+import logging
+import multiprocessing as mp
+import os
+import sys
+
+import numpy as np
+
+logging.disable(logging.CRITICAL)
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+import aircraft_controls_bindings as acb  # noqa: E402  (reference C++ PID, oracle/_ref)
+from controllers.attitude_agent import AttitudeAgent  # noqa: E402
+from controllers.rate_agent import RateAgent  # noqa: E402
+from controllers.types import (AircraftState, ControlCommand, ControlMode, ControllerConfig,  # noqa: E402
+                               ControlSurfaces)
+from simulation.simulation_backend import SimulationAircraftBackend  # noqa: E402
+
+
+def state_vec(backend):
+    ph = backend._physics
+    return np.concatenate([ph._state, [ph._time]])
+
+
+def derived_vec(st):
+    return np.array([st.airspeed, st.altitude, st.ground_speed, st.heading])
+
+
+def make_state(v):
+    return AircraftState(time=float(v[12]), position=v[0:3].copy(), velocity=v[3:6].copy(),
+                         attitude=v[6:9].copy(), angular_rate=v[9:12].copy())
+
+
+def sample_initial_states(rng, n):
+    """SURVEY.md 8(d) C2 inputs: V~U(15,30), h~U(50,200), phi,theta~U(+-15deg), psi~U(0,2pi), pqr~U(+-0.1)."""
+    s = np.zeros((13, n))
+    s[2] = -rng.uniform(50, 200, n)
+    s[3] = rng.uniform(15, 30, n)
+    s[6] = rng.uniform(-np.radians(15), np.radians(15), n)
+    s[7] = rng.uniform(-np.radians(15), np.radians(15), n)
+    s[8] = rng.uniform(0, 2 * np.pi, n)
+    s[9:12] = rng.uniform(-0.1, 0.1, (3, n))
+    return s
+
+
+# ------------------------------------------------------------------------------------------------
+def gen_pid_kat():
+    """Known-answer vectors for cpp/src/pid_controller.cpp through its own pybind module."""
+    rng = np.random.default_rng(7)
+    cases = []
+    cfgs = [
+        dict(kp=1.3, ki=0.4, kd=0.012, omin=-1.0, omax=1.0, imin=-25.0, imax=25.0, alpha=0.1),
+        dict(kp=8.0, ki=2.0, kd=0.3, omin=-np.pi, omax=np.pi, imin=-25.0, imax=25.0, alpha=0.1),
+        dict(kp=0.12, ki=0.03, kd=0.03, omin=-0.5, omax=0.5, imin=-10.0, imax=10.0, alpha=0.1),
+        dict(kp=2.0, ki=5.0, kd=0.5, omin=-0.5, omax=0.5, imin=-0.2, imax=0.2, alpha=1.0),
+        dict(kp=0.0, ki=1.0, kd=0.0, omin=-10.0, omax=10.0, imin=-5.0, imax=5.0, alpha=0.3),
+    ]
+    T = 400
+    cfg_arr = np.zeros((len(cfgs), 8), np.float32)
+    sp = np.zeros((len(cfgs), T), np.float32); meas = np.zeros_like(sp); dts = np.zeros_like(sp)
+    out = np.zeros((len(cfgs), T, 4), np.float32)  # output, error, integral, derivative_filtered
+    for ci, c in enumerate(cfgs):
+        pc = acb.PIDConfig()
+        pc.gains = acb.PIDGains(c["kp"], c["ki"], c["kd"])
+        pc.output_min, pc.output_max = c["omin"], c["omax"]
+        pc.integral_min, pc.integral_max = c["imin"], c["imax"]
+        pc.derivative_filter_alpha = c["alpha"]
+        pid = acb.PIDController(pc)
+        cfg_arr[ci] = [c["kp"], c["ki"], c["kd"], c["omin"], c["omax"], c["imin"], c["imax"], c["alpha"]]
+        for t in range(T):
+            s_ = np.float32(rng.normal(0, 1.0) if t % 50 else rng.normal(0, 5.0))
+            m_ = np.float32(rng.normal(0, 1.0))
+            d_ = np.float32([0.01, 0.001, 0.02, 1e-7][t % 4] if t % 37 else 0.0)
+            if t == 123:
+                m_ = np.float32(np.nan)   # NaN path through std::min/std::max
+            if t == 130:
+                pid.reset(); out[ci, t] = np.nan; sp[ci, t] = np.nan; continue  # marker: reset here
+            o = pid.compute(float(s_), float(m_), float(d_))
+            sp[ci, t], meas[ci, t], dts[ci, t] = s_, m_, d_
+            out[ci, t] = [o, pid.get_error(), pid.get_integral(), pid.get_derivative()]
+    np.savez(os.path.join(HERE, "pid_kat.npz"), cfg=cfg_arr, sp=sp, meas=meas, dt=dts, out=out)
+    print("pid_kat", out.shape)
+
+
+def gen_dynamics_kat():
+    """Simplified6DOF._dynamics on random (incl. degenerate) states."""
+    from simulation.simplified_6dof import Simplified6DOF
+    rng = np.random.default_rng(5)
+    sim = Simplified6DOF()
+    n = 3000
+    S = np.zeros((n, 12)); Cc = np.zeros((n, 4)); O = np.zeros((n, 12))
+    for i in range(n):
+        s = S[i]
+        s[0:3] = rng.uniform(-500, 500, 3); s[3] = rng.uniform(-5, 40); s[4:6] = rng.uniform(-8, 8, 2)
+        s[6] = rng.uniform(-3.2, 3.2); s[7] = rng.uniform(-1.6, 1.6); s[8] = rng.uniform(-3.2, 3.2)
+        s[9:12] = rng.uniform(-4, 4, 3)
+        if i % 50 == 0: s[3] = rng.uniform(-1e-6, 1e-6)       # u_safe branch
+        if i % 77 == 0: s[3:6] = 0.0                          # zero airspeed
+        if i % 91 == 0: s[3:6] = rng.uniform(-90, 90, 3)      # derivative clamps
+        c = Cc[i]; c[0:3] = rng.uniform(-1, 1, 3); c[3] = rng.uniform(0, 1)
+        ctl = ControlSurfaces(elevator=np.float64(c[0]), aileron=np.float64(c[1]), rudder=np.float64(c[2]),
+                              throttle=np.float64(c[3]))
+        O[i] = sim._dynamics(s, ctl)
+    np.savez(os.path.join(HERE, "dynamics_kat.npz"), s=S, ctrl=Cc, out=O)
+    print("dynamics_kat", O.shape)
+
+
+# ------------------------------------------------------------------------------------------------
+def _open_loop_worker(args):
+    s0, ctrl_seq, hold, steps, dt, dt_physics, every = args
+    b = SimulationAircraftBackend({"aircraft_type": "rc_plane", "dt_physics": dt_physics})
+    b.reset(make_state(s0))
+    snaps, ders = [], []
+    for t in range(steps):
+        c = ctrl_seq[t // hold]
+        b.set_controls(ControlSurfaces(elevator=c[0], aileron=c[1], rudder=c[2], throttle=c[3]))
+        st = b.step(dt)
+        if (t + 1) % every == 0:
+            snaps.append(state_vec(b)); ders.append(derived_vec(st))
+    return np.array(snaps), np.array(ders)
+
+
+def gen_open_loop(pool):
+    """Config 2: open-loop surface-level stepping, piecewise-constant random surfaces."""
+    for name, n, steps, dt, dtp, every in [("open_loop_k1", 16, 10000, 0.01, 0.01, 25),
+                                           ("open_loop_k10", 8, 1000, 0.01, 0.001, 5),
+                                           ("open_loop_k20", 8, 300, 0.02, 0.001, 1)]:
+        rng = np.random.default_rng(1234)
+        s0 = sample_initial_states(rng, n)
+        hold = 50
+        nseg = (steps + hold - 1) // hold
+        ctrl = np.zeros((nseg, 4, n))
+        # surface amplitude per aircraft: U(+-0.3) tumbles this airframe out of the env's envelope
+        # within ~0.5 s, so most aircraft get gentler inputs that keep them flying for the whole run
+        amp = np.array([0.01, 0.01, 0.03, 0.01, 0.1, 0.01, 0.03, 0.3] * 2)[:n]
+        ctrl[:, 0:3] = rng.uniform(-1.0, 1.0, (nseg, 3, n)) * amp
+        ctrl[:, 3] = rng.uniform(0.3, 0.9, (nseg, n))
+        # a few out-of-range commands to exercise set_controls clipping
+        ctrl[1, 0, 0] = 1.7; ctrl[1, 3, 1] = -0.2; ctrl[2, 1, 2] = -3.0
+        res = pool.map(_open_loop_worker, [(s0[:, i], ctrl[:, :, i], hold, steps, dt, dtp, every) for i in range(n)])
+        states = np.stack([r[0] for r in res], axis=2)   # [snap][13][n]
+        ders = np.stack([r[1] for r in res], axis=2)     # [snap][4][n]
+        np.savez(os.path.join(HERE, name + ".npz"), s0=s0, ctrl=ctrl, hold=hold, steps=steps, dt=dt,
+                 dt_physics=dtp, every=every, states=states, derived=ders)
+        print(name, states.shape)
+
+
+# ------------------------------------------------------------------------------------------------
+def _cascade_worker(args):
+    level, s0, cmd_seq, hold, steps, dt, dt_ctrl, every = args
+    b = SimulationAircraftBackend({"aircraft_type": "rc_plane"})
+    agent = RateAgent(ControllerConfig()) if level == 4 else AttitudeAgent(ControllerConfig())
+    state = b.reset(make_state(s0))
+    S, U, PI = [], [], []
+    for t in range(steps):
+        c = cmd_seq[t // hold]
+        if level == 4:
+            cmd = ControlCommand(mode=ControlMode.RATE, roll_rate=c[0], pitch_rate=c[1], yaw_rate=c[2], throttle=c[3])
+        else:
+            # NaN = yaw_angle None; +inf = hold the current yaw, the command HSAAgent issues (hsa_agent.py:214-216)
+            yaw = None if np.isnan(c[2]) else (state.yaw if np.isinf(c[2]) else c[2])
+            cmd = ControlCommand(mode=ControlMode.ATTITUDE, roll_angle=c[0], pitch_angle=c[1],
+                                 yaw_angle=yaw, throttle=c[3])
+        surf = agent.compute_action(cmd, state, dt=dt_ctrl)
+        b.set_controls(surf)
+        state = b.step(dt)
+        if (t + 1) % every:
+            continue
+        S.append(state_vec(b)); U.append(surf.to_array())
+        rc = agent.rate_controller if level == 4 else agent.rate_agent.rate_controller
+        e = rc.get_error(); i_ = rc.get_integral()
+        row = [e.x, e.y, e.z, i_.x, i_.y, i_.z]
+        if level == 3:
+            e2 = agent.angle_controller.get_error(); i2 = agent.angle_controller.get_integral()
+            row += [e2.x, e2.y, e2.z, i2.x, i2.y, i2.z]
+        PI.append(row)
+    return np.array(S), np.array(U), np.array(PI)
+
+
+def gen_cascade(pool):
+    """Config 1 (RateAgent, 30 deg/s roll step) + random rate / attitude command sequences."""
+    for name, level, n, steps, dt, dt_ctrl, every in [("rate_agent", 4, 8, 1000, 0.01, 0.01, 4),
+                                                      ("attitude_agent", 3, 8, 2000, 0.01, 0.01, 8),
+                                                      ("attitude_agent_dt02", 3, 4, 500, 0.02, 0.02, 2),
+                                                      ("attitude_agent_10k", 3, 8, 10000, 0.01, 0.01, 50)]:
+        rng = np.random.default_rng(99 + level)
+        s0 = sample_initial_states(rng, n)
+        # aircraft 0 is the reference's hello-controls case: level 100 m, 20 m/s
+        s0[:, 0] = 0.0; s0[2, 0] = -100.0; s0[3, 0] = 20.0
+        hold = 250
+        nseg = (steps + hold - 1) // hold
+        cmd = np.zeros((nseg, 4, n))
+        if level == 4:
+            cmd[:, 0:3] = rng.uniform(-0.6, 0.6, (nseg, 3, n))
+            cmd[:, :, 0] = 0.0; cmd[:, 0, 0] = np.radians(30.0)          # examples/01_hello_controls.py
+            cmd[1, 0, 1] = 5.0                                            # beyond max_roll_rate -> clipped
+        else:
+            # gentle attitude hold: the default gains are only well-conditioned near level flight; aggressive
+            # commands tumble the aircraft and 1-ulp differences then grow by 10x per 0.1 s (measured)
+            cmd[:, 0] = rng.uniform(-0.35, 0.35, (nseg, n))
+            cmd[:, 1] = rng.uniform(-0.03, 0.08, (nseg, n))
+            cmd[:, 2] = np.inf                                             # hold current yaw
+            cmd[1, 0, 1] = 1.0                                            # beyond max_roll -> clipped
+            if name == "attitude_agent_dt02":
+                s0[8] = rng.uniform(-0.3, 0.3, n)
+                cmd[:, 0] = rng.uniform(-0.05, 0.05, (nseg, n))
+                cmd[:, 2, 0:2] = np.nan                                   # yaw_angle=None -> 0.0
+                cmd[:, 2, 2:4] = s0[8, 2:4] + rng.uniform(-0.2, 0.2, (nseg, 2)) + 2 * np.pi   # wrapped setpoint
+        cmd[:, 3] = rng.uniform(0.4, 0.8, (nseg, n)); cmd[:, 3, 0] = 0.7
+        res = pool.map(_cascade_worker, [(level, s0[:, i], cmd[:, :, i], hold, steps, dt, dt_ctrl, every) for i in range(n)])
+        np.savez(os.path.join(HERE, name + ".npz"), level=level, s0=s0, cmd=cmd, hold=hold, steps=steps, dt=dt,
+                 dt_ctrl=dt_ctrl, every=every,
+                 states=np.stack([r[0] for r in res], axis=2),      # [snap][13][n]
+                 surfaces=np.stack([r[1] for r in res], axis=2),    # [snap][4][n]
+                 pid=np.stack([r[2] for r in res], axis=2))         # [snap][6 or 12][n]
+        print(name, res[0][0].shape)
+
+
+# ------------------------------------------------------------------------------------------------
+def _env_worker(args):
+    from learned_controllers.envs.rate_env import RateControlEnv
+    from learned_controllers.envs.residual_rate_env import ResidualRateControlEnv
+    seed, difficulty, command_type, controller, steps = args
+    rng = np.random.default_rng(seed)
+    if controller == 3:
+        env = ResidualRateControlEnv(difficulty=difficulty, command_type=command_type, rng_seed=seed)
+        base = env.base_env
+    else:
+        env = RateControlEnv(difficulty=difficulty, command_type=command_type, rng_seed=seed)
+        base = env
+    obs0, info = env.reset(seed=seed)
+    obs0 = obs0.copy()
+    s0 = state_vec(base.sim)
+    cmd0 = base.rate_command.copy()
+    sched = np.zeros(7)
+    if command_type == "ramp":
+        sched[0:3] = base.command_schedule["end"]
+    elif command_type == "sine":
+        sched[0:3] = base.sine_params["amplitudes"]; sched[3] = base.sine_params["frequency"]
+    agent = RateAgent(ControllerConfig()) if controller == 1 else None
+    A, O, R, TE, TR, CMP, S, CMD, SET = [], [], [], [], [], [], [], [], []
+    for t in range(steps):
+        if controller == 0:      # external float32 policy actions (random, some out of the Box)
+            a = rng.uniform(-1.2, 1.2, 4).astype(np.float32)
+            if t < 150:          # start gently so the episode survives long enough to be interesting
+                a = (a * 0.1).astype(np.float32); a[3] = np.float32(0.6)
+        elif controller == 3:    # residual policy output
+            a = rng.uniform(-1.0, 1.0, 4).astype(np.float32)
+        else:                    # pid_demonstrations.py:55-78
+            st = base.sim.get_state()
+            p, q, r = base.rate_command
+            sf = agent.compute_action(ControlCommand(mode=ControlMode.RATE, roll_rate=p, pitch_rate=q, yaw_rate=r,
+                                                     throttle=0.6), st, dt=0.02)
+            a = np.array([sf.aileron, sf.elevator, sf.rudder, sf.throttle], dtype=np.float32)
+        obs, rew, term, trunc, info = env.step(a)
+        rc = info["reward_components"]
+        comp = [rc["tracking"], rc["smoothness"], rc["stability"], rc["oscillation"], rc["survival"],
+                0.0, rc.get("crash_penalty", 0.0), 0.0]
+        comp[5] = float(rew) - float(rc["total"]) - comp[6]      # settle bonus (+ residual bonus for controller 3)
+        A.append(a); O.append(obs.copy()); R.append(float(rew)); TE.append(term); TR.append(trunc)
+        CMP.append(comp); S.append(state_vec(base.sim)); CMD.append(base.rate_command.copy())
+        SET.append(base.settle_bonus.is_settled)
+        if term or trunc:
+            break
+    return dict(s0=s0, cmd0=cmd0, sched=sched, obs0=obs0, actions=np.array(A), obs=np.array(O), reward=np.array(R),
+                terminated=np.array(TE), truncated=np.array(TR), components=np.array(CMP), states=np.array(S),
+                rate_cmd=np.array(CMD), is_settled=np.array(SET))
+
+
+def gen_env(pool):
+    """RateControlEnv / ResidualRateControlEnv episodes with the reference's own initial draws recorded."""
+    scale = {"easy": 0.3, "medium": 0.5, "hard": 0.7}
+    cases = []
+    for ctrl in (0, 1, 3):
+        for diff, ctype in [("easy", "step"), ("medium", "step"), ("hard", "step"), ("medium", "ramp"),
+                            ("medium", "sine"), ("hard", "sine")]:
+            cases.append((1000 + len(cases), diff, ctype, ctrl, 500))
+    res = pool.map(_env_worker, cases)
+    out = {"n_cases": len(cases)}
+    for k, (c, r) in enumerate(zip(cases, res)):
+        out[f"c{k}_meta"] = np.array([c[0], scale[c[1]], {"step": 0, "ramp": 1, "sine": 2}[c[2]], c[3]], dtype=np.float64)
+        for key, v in r.items():
+            out[f"c{k}_{key}"] = v
+        print("env case", k, c, "steps", len(r["reward"]), "return", r["reward"].sum())
+    np.savez_compressed(os.path.join(HERE, "rate_env.npz"), **out)
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env"]
+    with mp.Pool(8) as pool:
+        if "pid" in which: gen_pid_kat()
+        if "dyn" in which: gen_dynamics_kat()
+        if "open" in which: gen_open_loop(pool)
+        if "cascade" in which: gen_cascade(pool)
+        if "env" in which: gen_env(pool)
