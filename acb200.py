@@ -1,0 +1,14 @@
+"""Import alias: the package directory is named after the reference repository
+(hybrid-classical-and-reinforcement-learning-aircraft-controllers_b200), which is not a Python
+identifier; ``import acb200`` loads it under this name."""
+import importlib.util
+import os
+import sys
+
+_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                    "hybrid-classical-and-reinforcement-learning-aircraft-controllers_b200")
+_spec = importlib.util.spec_from_file_location(__name__, os.path.join(_dir, "__init__.py"),
+                                               submodule_search_locations=[_dir])
+_mod = importlib.util.module_from_spec(_spec)
+sys.modules[__name__] = _mod
+_spec.loader.exec_module(_mod)

@@ -1,0 +1,10 @@
+"""acb200: B200-native batched flight-control path (6-DOF step, cascaded PID, rate-env) behind the
+reference's interfaces.  Import as ``acb200`` (see acb200.py at the repository root)."""
+from . import _cabi
+from ._cabi import Context, default_aircraft_params, default_controller_params, kernel_info
+from .envs import BatchedRateControlEnv
+from .fleet import AircraftFleet
+
+__all__ = ["_cabi", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
+           "default_controller_params", "kernel_info"]
+__version__ = "0.1.0"

@@ -1,0 +1,333 @@
+// capi.cu -- the extern "C" boundary declared in include/acb200.h.  Validates arguments the way the
+// reference's Python does (bad dt / bad parameters -> ACB200_EVALUE, which the adapters raise as
+// ValueError), converts the plain-pointer descriptors into typed ones and enqueues the kernels.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+
+#include "kernels.h"
+#include "params.cuh"
+#include "pid.cuh"
+
+using namespace acb;
+
+struct acb200_ctx {
+    int device;
+    cudaStream_t stream;
+    acb200_aircraft_params aircraft;
+    acb200_controller_params controller;
+    int64_t launches;
+    std::string error;
+};
+
+namespace {
+
+int fail(acb200_ctx* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->error = msg;
+    return code;
+}
+int cuda_fail(acb200_ctx* ctx, cudaError_t e, const char* where) {
+    return fail(ctx, ACB200_ECUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+
+// K = max(1, int(dt/dt_physics)), h = dt/K (simulation_backend.py:95-96); dt range check
+// (simplified_6dof.py:241-245) applied to the substep the physics actually sees.
+int substeps(acb200_ctx* ctx, double dt, double dt_physics, int* K, double* h) {
+    if (!(dt_physics > 0.0) || !(dt == dt)) return fail(ctx, ACB200_EVALUE, "Invalid timestep");
+    int k = (int)(dt / dt_physics);
+    if (k < 1) k = 1;
+    const double hh = dt / k;
+    if (hh <= ctx->aircraft.min_timestep || hh > ctx->aircraft.max_timestep || !(hh == hh)) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "Invalid timestep dt=%.6fs, must be in (%g, %g]", hh, ctx->aircraft.min_timestep,
+                 ctx->aircraft.max_timestep);
+        return fail(ctx, ACB200_EVALUE, buf);
+    }
+    *K = k;
+    *h = hh;
+    return ACB200_OK;
+}
+
+template <typename T> FleetPtrs<T> typed(const acb200_fleet& f) {
+    return FleetPtrs<T>{f.n, (T*)f.state, (T*)f.controls, (T*)f.derived, f.pid};
+}
+template <typename T> EnvPtrs<T> typed(const acb200_env& e, float* reward_f32) {
+    EnvPtrs<T> o;
+    o.f = typed<T>(e.fleet);
+    o.att_cmd = (T*)e.att_cmd; o.rate_cmd = (T*)e.rate_cmd; o.prev_action = e.prev_action; o.rew_mem = (T*)e.rew_mem;
+    o.sched = (T*)e.sched; o.env_time = (T*)e.env_time; o.step_count = e.step_count; o.is_settled = e.is_settled;
+    o.command_type = e.command_type; o.difficulty = e.difficulty; o.episode_idx = e.episode_idx; o.ep_return = (T*)e.ep_return;
+    o.obs = e.obs; o.reward = (T*)e.reward; o.terminated = e.terminated; o.truncated = e.truncated;
+    o.terminal_obs = e.terminal_obs; o.components = (T*)e.components; o.stats = e.stats; o.reward_f32 = reward_f32;
+    return o;
+}
+
+int check_fleet(acb200_ctx* ctx, const acb200_fleet* f, bool need_pid) {
+    if (!ctx) return ACB200_ENULL;
+    if (!f || !f->state) return fail(ctx, ACB200_ENULL, "fleet.state is NULL");
+    if (f->precision != 64 && f->precision != 32) return fail(ctx, ACB200_EVALUE, "fleet.precision must be 64 or 32");
+    if (f->n < 0) return fail(ctx, ACB200_EVALUE, "fleet.n < 0");
+    if (need_pid && !f->pid) return fail(ctx, ACB200_ENULL, "fleet.pid is NULL");
+    return ACB200_OK;
+}
+
+int check_env(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg) {
+    if (!ctx) return ACB200_ENULL;
+    if (!e || !cfg) return fail(ctx, ACB200_ENULL, "env or config is NULL");
+    const int rc = check_fleet(ctx, &e->fleet, true);
+    if (rc) return rc;
+    if (!e->fleet.derived || !e->rate_cmd || !e->prev_action || !e->rew_mem || !e->sched || !e->env_time || !e->step_count ||
+        !e->is_settled || !e->command_type || !e->difficulty || !e->episode_idx || !e->ep_return || !e->obs || !e->reward ||
+        !e->terminated || !e->truncated)
+        return fail(ctx, ACB200_ENULL, "a required env buffer is NULL");
+    if (cfg->controller < ACB200_CTRL_EXTERNAL || cfg->controller > ACB200_CTRL_RESIDUAL)
+        return fail(ctx, ACB200_EVALUE, "unknown controller");
+    if (cfg->controller == ACB200_CTRL_ATTITUDE_PID && !e->att_cmd) return fail(ctx, ACB200_ENULL, "env.att_cmd is NULL");
+    if (cfg->max_steps < 1) return fail(ctx, ACB200_EVALUE, "max_steps < 1");
+    return ACB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* acb200_version(void) { return ACB200_VERSION; }
+
+int acb200_create(int device, acb200_ctx** out) {
+    if (!out) return ACB200_ENULL;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) return ACB200_ECUDA;   // no CPU fallback: fail loudly
+    acb200_ctx* ctx = new acb200_ctx();
+    ctx->device = device;
+    ctx->stream = nullptr;
+    ctx->launches = 0;
+    acb200_default_aircraft_params(&ctx->aircraft);
+    acb200_default_controller_params(&ctx->controller);
+    *out = ctx;
+    return ACB200_OK;
+}
+
+void acb200_destroy(acb200_ctx* ctx) { delete ctx; }
+
+const char* acb200_last_error(const acb200_ctx* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
+
+int acb200_set_stream(acb200_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return ACB200_ENULL;
+    ctx->stream = (cudaStream_t)cuda_stream;
+    return ACB200_OK;
+}
+
+int acb200_synchronize(acb200_ctx* ctx) {
+    if (!ctx) return ACB200_ENULL;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "cudaStreamSynchronize");
+}
+
+int64_t acb200_launch_count(const acb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// simulation/simplified_6dof.py:45-117
+void acb200_default_aircraft_params(acb200_aircraft_params* p) {
+    const acb200_aircraft_params d = {
+        8.0, 0.4, 0.6, 0.7,          // mass, inertia
+        0.5, 2.0, 0.25,              // wing area, span, chord
+        0.4, 5.0, 0.025, 0.04,       // cl_0, cl_alpha, cd_0, cd_alpha2
+        0.6, -2.0, 0.5, -0.40, 0.50, // control effectiveness
+        -0.15, 0.04, -0.02,          // cm_alpha, cn_beta, cl_beta
+        -0.8, -2.0, -0.6,            // damping
+        50.0, 1.225, 9.81,           // thrust, density, gravity
+        10.0, 0.1,                   // min airspeed (aero), min u
+        30.0, 30.0, 30.0,            // deflection limits, degrees
+        50.0,                        // thrust_zero_velocity
+        100.0, 360.0, 85.0, 30.0,    // state limits
+        50.0, 1000.0,                // derivative limits
+        1.0, 1e-6};                  // timestep limits
+    *p = d;
+}
+
+// simulation/simulation_backend.py:64-73
+void acb200_cessna_aircraft_params(acb200_aircraft_params* p) {
+    acb200_default_aircraft_params(p);
+    p->mass = 15.0; p->inertia_xx = 1.0; p->inertia_yy = 2.0; p->inertia_zz = 2.5;
+    p->wing_area = 1.0; p->wing_span = 3.0; p->max_thrust = 80.0;
+}
+
+static acb200_pid_config pid_cfg(double kp, double ki, double kd, double i_limit, double omin, double omax) {
+    acb200_pid_config c;   // create_pid_config, controllers/utils/pid_utils.py:16-46 (pybind narrows to float)
+    c.kp = (float)kp; c.ki = (float)ki; c.kd = (float)kd;
+    c.output_min = (float)omin; c.output_max = (float)omax;
+    c.integral_min = (float)(-i_limit); c.integral_max = (float)i_limit;
+    c.derivative_filter_alpha = 0.1f;   // cpp/include/pid_controller.h:48
+    return c;
+}
+
+// controllers/types.py:294-350
+void acb200_default_controller_params(acb200_controller_params* c) {
+    const double il = 25.0;
+    c->max_roll_rate = host_radians(180.0); c->max_pitch_rate = host_radians(180.0); c->max_yaw_rate = host_radians(160.0);
+    c->max_roll = host_radians(30.0); c->max_pitch = host_radians(30.0);
+    c->rate[0] = pid_cfg(1.3, 0.4, 0.012, il, -1.0, 1.0);
+    c->rate[1] = pid_cfg(0.6, 0.2, 0.008, il, -1.0, 1.0);
+    c->rate[2] = pid_cfg(1.6, 0.15, 0.01, il, -1.0, 1.0);
+    c->angle[0] = pid_cfg(8.0, 2.0, 0.3, il, -c->max_roll_rate, c->max_roll_rate);
+    c->angle[1] = pid_cfg(6.0, 1.5, 0.2, il, -c->max_pitch_rate, c->max_pitch_rate);
+    c->angle[2] = pid_cfg(1.6, 0.15, 0.01, il, -c->max_yaw_rate, c->max_yaw_rate);
+}
+
+// AircraftParams.__post_init__, simplified_6dof.py:119-143
+int acb200_set_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p) {
+    if (!ctx || !p) return ACB200_ENULL;
+    if (!(p->mass > 0)) return fail(ctx, ACB200_EVALUE, "Mass must be positive");
+    if (!(p->inertia_xx > 0) || !(p->inertia_yy > 0) || !(p->inertia_zz > 0))
+        return fail(ctx, ACB200_EVALUE, "All inertia values must be positive");
+    if (!(p->wing_area > 0)) return fail(ctx, ACB200_EVALUE, "Wing area must be positive");
+    if (!(p->wing_span > 0)) return fail(ctx, ACB200_EVALUE, "Wing span must be positive");
+    if (!(p->chord > 0)) return fail(ctx, ACB200_EVALUE, "Chord must be positive");
+    if (!(p->air_density > 0 && p->air_density < 10)) return fail(ctx, ACB200_EVALUE, "Invalid air density");
+    if (!(p->gravity > 0 && p->gravity < 20)) return fail(ctx, ACB200_EVALUE, "Invalid gravity");
+    if (p->max_thrust < 0) return fail(ctx, ACB200_EVALUE, "Max thrust cannot be negative");
+    ctx->aircraft = *p;
+    return ACB200_OK;
+}
+
+int acb200_set_controller_params(acb200_ctx* ctx, const acb200_controller_params* c) {
+    if (!ctx || !c) return ACB200_ENULL;
+    ctx->controller = *c;
+    return ACB200_OK;
+}
+
+int acb200_fleet_reset(acb200_ctx* ctx, const acb200_fleet* f, const uint8_t* mask, const void* init_state) {
+    int rc = check_fleet(ctx, f, false);
+    if (rc) return rc;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e = (f->precision == 64)
+                              ? Launch<double>::fleet_reset(typed<double>(*f), mask, (const double*)init_state, ctx->stream)
+                              : Launch<float>::fleet_reset(typed<float>(*f), mask, (const float*)init_state, ctx->stream);
+    ctx->launches += 1;
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "fleet_reset");
+}
+
+int acb200_step_surface(acb200_ctx* ctx, const acb200_fleet* f, const void* ctrl_in, double dt, double dt_physics) {
+    int rc = check_fleet(ctx, f, false);
+    if (rc) return rc;
+    if (!ctrl_in) return fail(ctx, ACB200_ENULL, "ctrl_in is NULL");
+    int K; double h;
+    if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e = (f->precision == 64)
+                              ? Launch<double>::step_surface(ctx->aircraft, typed<double>(*f), (const double*)ctrl_in, K, h, ctx->stream)
+                              : Launch<float>::step_surface(ctx->aircraft, typed<float>(*f), (const float*)ctrl_in, K, h, ctx->stream);
+    ctx->launches += 1;
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "step_surface");
+}
+
+int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const void* cmd, double dt_ctrl, double dt,
+                        double dt_physics, void* surfaces_out) {
+    int rc = check_fleet(ctx, f, true);
+    if (rc) return rc;
+    if (!cmd) return fail(ctx, ACB200_ENULL, "cmd is NULL");
+    if (level != ACB200_LEVEL_ATTITUDE && level != ACB200_LEVEL_RATE)
+        return fail(ctx, ACB200_ENOSUP, "step_cascade supports levels 3 (attitude) and 4 (rate)");
+    int K; double h;
+    if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e =
+        (f->precision == 64)
+            ? Launch<double>::step_cascade(ctx->aircraft, ctx->controller, typed<double>(*f), level, (const double*)cmd, dt_ctrl, K,
+                                           h, (double*)surfaces_out, ctx->stream)
+            : Launch<float>::step_cascade(ctx->aircraft, ctx->controller, typed<float>(*f), level, (const float*)cmd, dt_ctrl, K, h,
+                                          (float*)surfaces_out, ctx->stream);
+    ctx->launches += 1;
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "step_cascade");
+}
+
+int acb200_env_reset(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const uint8_t* mask) {
+    int rc = check_env(ctx, env, cfg);
+    if (rc) return rc;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e = (env->fleet.precision == 64)
+                              ? Launch<double>::env_reset(typed<double>(*env, nullptr), *cfg, mask, ctx->stream)
+                              : Launch<float>::env_reset(typed<float>(*env, nullptr), *cfg, mask, ctx->stream);
+    ctx->launches += 1;
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_reset");
+}
+
+static int env_step_impl(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action,
+                         float* reward_f32) {
+    int rc = check_env(ctx, env, cfg);
+    if (rc) return rc;
+    if (!action && (cfg->controller == ACB200_CTRL_EXTERNAL || cfg->controller == ACB200_CTRL_RESIDUAL))
+        return fail(ctx, ACB200_ENULL, "action is NULL");
+    if (action && ((uintptr_t)action & 15)) return fail(ctx, ACB200_EVALUE, "action must be 16-byte aligned");
+    int K; double h;
+    if ((rc = substeps(ctx, cfg->dt, cfg->dt_physics, &K, &h))) return rc;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e =
+        (env->fleet.precision == 64)
+            ? Launch<double>::env_step(ctx->aircraft, ctx->controller, typed<double>(*env, reward_f32), *cfg, K, h, action, ctx->stream)
+            : Launch<float>::env_step(ctx->aircraft, ctx->controller, typed<float>(*env, reward_f32), *cfg, K, h, action, ctx->stream);
+    ctx->launches += 1;
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step");
+}
+
+int acb200_env_step(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action) {
+    return env_step_impl(ctx, env, cfg, action, nullptr);
+}
+
+// Host-buffer step: H2D action, kernel, D2H obs / reward / done flags, all on the context's stream.
+// action_dev is caller-owned device scratch of n*4 + n floats: the staged action followed by the
+// float copy of the reward that the kernel writes for the host.
+int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action_host,
+                         float* action_dev, float* obs_host, float* reward_host, uint8_t* terminated_host,
+                         uint8_t* truncated_host) {
+    if (!ctx || !env) return ACB200_ENULL;
+    if (!action_dev || !obs_host || !reward_host || !terminated_host || !truncated_host)
+        return fail(ctx, ACB200_ENULL, "a host/scratch buffer is NULL");
+    const int64_t n = env->fleet.n;
+    cudaSetDevice(ctx->device);
+    cudaError_t e;
+    if (action_host) {
+        e = cudaMemcpyAsync(action_dev, action_host, (size_t)n * 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "H2D action");
+    }
+    float* reward_dev = action_dev + n * 4;
+    const int rc = env_step_impl(ctx, env, cfg, action_host ? action_dev : nullptr, reward_dev);
+    if (rc) return rc;
+    e = cudaMemcpyAsync(obs_host, env->obs, (size_t)n * ACB200_OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, reward_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(terminated_host, env->terminated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(truncated_host, env->truncated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step_host");
+}
+
+float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt) {
+    const float old_prev = st->error_prev;
+    PidMem m{st->integral, st->error_prev, st->derivative_filtered};
+    const float out = pid_compute(*cfg, m, setpoint, measurement, dt);
+    // the observable-only words of PIDController (pid_controller.h:128-133)
+    st->error = m.error_prev;
+    st->derivative = (dt > 1e-6f) ? (st->error - old_prev) / dt : 0.0f;
+    st->integral = m.integral; st->error_prev = m.error_prev; st->derivative_filtered = m.derivative_filtered;
+    st->output = out;
+    return out;
+}
+
+void acb200_pid_reset(acb200_pid_state* st) { memset(st, 0, sizeof *st); }   // pid_controller.cpp:62-69
+
+int acb200_kernel_info(int precision, const char* kernel, int* regs, int* local_bytes, int* max_threads) {
+    if (!kernel) return ACB200_ENULL;
+    KernelInfo ki;
+    const cudaError_t e = (precision == 64) ? Launch<double>::kernel_info(kernel, &ki) : Launch<float>::kernel_info(kernel, &ki);
+    if (e != cudaSuccess) return ACB200_ECUDA;
+    if (regs) *regs = ki.regs;
+    if (local_bytes) *local_bytes = ki.local_bytes;
+    if (max_threads) *max_threads = ki.max_threads;
+    return ACB200_OK;
+}
+
+}  // extern "C"

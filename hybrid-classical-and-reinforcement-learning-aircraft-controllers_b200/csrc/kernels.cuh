@@ -1,0 +1,401 @@
+// kernels.cuh -- the __global__ kernels: one thread owns one aircraft; HBM is touched only at the
+// control-step boundary through coalesced structure-of-arrays loads and stores; everything between
+// (K RK4 substeps x 4 derivative evaluations, PID, reward, termination, reset) runs out of registers.
+#pragma once
+#include <string.h>
+
+#include "env.cuh"
+#include "kernels.h"
+
+namespace acb {
+
+constexpr int kBlock = 128;
+
+template <typename T> __device__ __forceinline__ T ldf(const T* base, int f, int64_t n, int64_t i) { return base[(int64_t)f * n + i]; }
+template <typename T> __device__ __forceinline__ void stf(T* base, int f, int64_t n, int64_t i, T v) { base[(int64_t)f * n + i] = v; }
+
+__device__ __forceinline__ void load_pid(const float* pid, int64_t n, int64_t i, int loop, PidMem (&m)[3]) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const int b = (loop * 3 + a) * 3;
+        m[a].integral = ldf(pid, b + 0, n, i);
+        m[a].error_prev = ldf(pid, b + 1, n, i);
+        m[a].derivative_filtered = ldf(pid, b + 2, n, i);
+    }
+}
+__device__ __forceinline__ void store_pid(float* pid, int64_t n, int64_t i, int loop, const PidMem (&m)[3]) {
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const int b = (loop * 3 + a) * 3;
+        stf(pid, b + 0, n, i, m[a].integral);
+        stf(pid, b + 1, n, i, m[a].error_prev);
+        stf(pid, b + 2, n, i, m[a].derivative_filtered);
+    }
+}
+
+// ---- Simplified6DOF.reset for a masked subset (simplified_6dof.py:189-212) ------------------------
+template <typename T>
+__global__ void __launch_bounds__(kBlock) fleet_reset_kernel(FleetPtrs<T> f, const uint8_t* __restrict__ mask,
+                                                             const T* __restrict__ init_state) {
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.n || (mask && !mask[i])) return;
+    T s[12], time = T(0), d[4];
+    if (init_state) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) s[k] = ldf(init_state, k, f.n, i);
+        time = ldf(init_state, 12, f.n, i);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) s[k] = T(0);
+        s[2] = T(-100); s[3] = T(20);
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) stf(f.state, k, f.n, i, s[k]);
+    stf(f.state, 12, f.n, i, time);
+    if (f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.controls, k, f.n, i, T(0));
+    }
+    if (f.derived) {
+        derived_outputs(s, d);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.derived, k, f.n, i, d[k]);
+    }
+    if (f.pid) {
+#pragma unroll
+        for (int k = 0; k < ACB200_PID_FIELDS; ++k) stf(f.pid, k, f.n, i, 0.0f);
+    }
+}
+
+// ---- K-A: backend.set_controls + backend.step ------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kBlock) step_surface_kernel(const __grid_constant__ DynParams<T> P, FleetPtrs<T> f,
+                                                              const T* __restrict__ ctrl_in, int K, T h) {
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.n) return;
+    T s[12], time, cin[4], c[4], d[4];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s[k] = ldf(f.state, k, f.n, i);
+    time = ldf(f.state, 12, f.n, i);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) cin[k] = ldf(ctrl_in, k, f.n, i);
+    clip_controls(cin, c);
+    backend_step(P, s, time, c, K, h);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) stf(f.state, k, f.n, i, s[k]);
+    stf(f.state, 12, f.n, i, time);
+    if (f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.controls, k, f.n, i, c[k]);
+    }
+    if (f.derived) {
+        derived_outputs(s, d);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.derived, k, f.n, i, d[k]);
+    }
+}
+
+// ---- K-B: agent.compute_action + backend.set_controls + backend.step ------------------------------
+template <typename T, int LEVEL>
+__global__ void __launch_bounds__(kBlock) step_cascade_kernel(const __grid_constant__ DynParams<T> P,
+                                                              const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
+                                                              const T* __restrict__ cmd, float dt_ctrl, int K, T h,
+                                                              T* __restrict__ surfaces_out) {
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.n) return;
+    T s[12], time, cm[4], surf[4], c[4], d[4];
+    PidMem rate[3], ang[3];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s[k] = ldf(f.state, k, f.n, i);
+    time = ldf(f.state, 12, f.n, i);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) cm[k] = ldf(cmd, k, f.n, i);
+    load_pid(f.pid, f.n, i, 0, rate);
+    if (LEVEL == ACB200_LEVEL_ATTITUDE) {
+        load_pid(f.pid, f.n, i, 1, ang);
+        attitude_agent(C, ang, rate, cm[0], cm[1], cm[2], cm[3], s, dt_ctrl, surf);
+        store_pid(f.pid, f.n, i, 1, ang);
+    } else {
+        rate_agent(C, rate, cm[0], cm[1], cm[2], cm[3], s[9], s[10], s[11], dt_ctrl, surf);
+    }
+    store_pid(f.pid, f.n, i, 0, rate);
+    clip_controls(surf, c);
+    backend_step(P, s, time, c, K, h);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) stf(f.state, k, f.n, i, s[k]);
+    stf(f.state, 12, f.n, i, time);
+    if (surfaces_out) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(surfaces_out, k, f.n, i, surf[k]);
+    }
+    if (f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.controls, k, f.n, i, c[k]);
+    }
+    if (f.derived) {
+        derived_outputs(s, d);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.derived, k, f.n, i, d[k]);
+    }
+}
+
+// ---- env memory <-> registers ----------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ void env_gather(const EnvPtrs<T>& B, int64_t i, EnvRegs<T>& e) {
+    const int64_t n = B.f.n;
+#pragma unroll
+    for (int k = 0; k < 12; ++k) e.s[k] = ldf(B.f.state, k, n, i);
+    e.time = ldf(B.f.state, 12, n, i);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) e.d[k] = ldf(B.f.derived, k, n, i);
+    load_pid(B.f.pid, n, i, 0, e.rate);
+    load_pid(B.f.pid, n, i, 1, e.ang);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) e.rate_cmd[k] = ldf(B.rate_cmd, k, n, i);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) e.prev_action[k] = ldf(B.prev_action, k, n, i);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { e.prev_err[k] = ldf(B.rew_mem, k, n, i); e.sign_changes[k] = ldf(B.rew_mem, 3 + k, n, i); }
+    e.settle_timer = ldf(B.rew_mem, 6, n, i);
+#pragma unroll
+    for (int k = 0; k < 7; ++k) e.sched[k] = ldf(B.sched, k, n, i);
+    e.env_time = B.env_time[i];
+    e.step_count = B.step_count[i];
+    e.episode_idx = B.episode_idx[i];
+    e.is_settled = B.is_settled[i];
+    e.command_type = B.command_type[i];
+    e.difficulty = B.difficulty[i];
+    e.ep_return = B.ep_return[i];
+}
+
+template <typename T> __device__ __forceinline__ void env_scatter(const EnvPtrs<T>& B, int64_t i, const EnvRegs<T>& e) {
+    const int64_t n = B.f.n;
+#pragma unroll
+    for (int k = 0; k < 12; ++k) stf(B.f.state, k, n, i, e.s[k]);
+    stf(B.f.state, 12, n, i, e.time);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) stf(B.f.derived, k, n, i, e.d[k]);
+    store_pid(B.f.pid, n, i, 0, e.rate);
+    store_pid(B.f.pid, n, i, 1, e.ang);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) stf(B.rate_cmd, k, n, i, e.rate_cmd[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) stf(B.prev_action, k, n, i, e.prev_action[k]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { stf(B.rew_mem, k, n, i, e.prev_err[k]); stf(B.rew_mem, 3 + k, n, i, e.sign_changes[k]); }
+    stf(B.rew_mem, 6, n, i, e.settle_timer);
+#pragma unroll
+    for (int k = 0; k < 7; ++k) stf(B.sched, k, n, i, e.sched[k]);
+    B.env_time[i] = e.env_time;
+    B.step_count[i] = e.step_count;
+    B.episode_idx[i] = e.episode_idx;
+    B.is_settled[i] = e.is_settled;
+    B.ep_return[i] = e.ep_return;
+}
+
+// Observations are float[n][18] row-major (the gym / policy-GEMM layout): stage the block's rows in
+// shared memory and write them out as one contiguous, fully coalesced run.
+__device__ __forceinline__ void store_obs_block(float* __restrict__ obs, int64_t n, const float (&o)[18], bool valid,
+                                                float* stage) {
+    if (valid) {
+#pragma unroll
+        for (int k = 0; k < ACB200_OBS_DIM; ++k) stage[threadIdx.x * ACB200_OBS_DIM + k] = o[k];
+    }
+    __syncthreads();
+    const int64_t first = (int64_t)blockIdx.x * kBlock;
+    const int64_t rows = (n - first < kBlock) ? (n - first) : kBlock;
+    const int count = (int)rows * ACB200_OBS_DIM;
+    float* dst = obs + first * ACB200_OBS_DIM;   // first*18*4 B = blockIdx*9216 B: 16-byte aligned when obs is
+    if ((count & 3) == 0 && ((uintptr_t)dst & 15) == 0) {
+        for (int k = threadIdx.x; k < count / 4; k += kBlock)
+            reinterpret_cast<float4*>(dst)[k] = reinterpret_cast<const float4*>(stage)[k];
+    } else {
+        for (int k = threadIdx.x; k < count; k += kBlock) dst[k] = stage[k];
+    }
+    __syncthreads();
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvPtrs<T> B, const __grid_constant__ EnvConst<T> E,
+                                                           const uint8_t* __restrict__ mask) {
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= B.f.n || (mask && !mask[i])) return;
+    EnvRegs<T> e;
+    env_gather(B, i, e);
+    env_reset_one(E, i, e);
+    env_scatter(B, i, e);
+    if (B.f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(B.f.controls, k, B.f.n, i, T(0));
+    }
+    float o[18];
+    env_observe(e, o);
+#pragma unroll
+    for (int k = 0; k < ACB200_OBS_DIM; ++k) B.obs[i * ACB200_OBS_DIM + k] = o[k];   // masked resets are sparse: direct rows
+}
+
+// ---- K-C: controller + RateControlEnv.step + reward + termination + in-kernel auto-reset -----------
+template <typename T>
+__global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant__ DynParams<T> P,
+                                                          const __grid_constant__ CtrlParams<T> C,
+                                                          const __grid_constant__ EnvConst<T> E, EnvPtrs<T> B,
+                                                          const float* __restrict__ action) {
+    __shared__ __align__(16) float stage[kBlock * ACB200_OBS_DIM];
+    __shared__ double block_stats[ACB200_STATS_FIELDS];
+    const int64_t n = B.f.n;
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    const bool valid = i < n;
+    if (threadIdx.x < ACB200_STATS_FIELDS) block_stats[threadIdx.x] = 0.0;
+
+    float o[18];
+    T st[ACB200_STATS_FIELDS];
+#pragma unroll
+    for (int k = 0; k < ACB200_STATS_FIELDS; ++k) st[k] = T(0);
+
+    if (valid) {
+        EnvRegs<T> e;
+        env_gather(B, i, e);
+        float act[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (action) {
+            const float4 a4 = reinterpret_cast<const float4*>(action)[i];
+            act[0] = a4.x; act[1] = a4.y; act[2] = a4.z; act[3] = a4.w;
+        }
+        T att[4] = {T(0), T(0), T(0), T(0)};
+        if (E.controller == ACB200_CTRL_ATTITUDE_PID) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) att[k] = ldf(B.att_cmd, k, n, i);
+        }
+        T comp[8], reward;
+        bool terminated, truncated;
+        int repaired = 0;
+        env_step_one(P, C, E, e, act, att, comp, reward, terminated, truncated, repaired, i);
+        env_observe(e, o);
+
+        B.reward[i] = reward;
+        if (B.reward_f32) B.reward_f32[i] = (float)reward;
+        B.terminated[i] = (uint8_t)terminated;
+        B.truncated[i] = (uint8_t)truncated;
+        if (B.components) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) stf(B.components, k, n, i, comp[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) st[6 + k] = comp[k];
+        st[14] = (T)repaired;
+        st[15] = T(1);
+        if (terminated || truncated) {
+            st[0] = T(1); st[1] = e.ep_return; st[2] = e.ep_return * e.ep_return; st[3] = (T)e.step_count;
+            st[4] = (terminated && !truncated) ? T(1) : T(0);
+            st[5] = truncated ? T(1) : T(0);
+            if (E.auto_reset) {
+                // SB3 VecEnv semantics: keep the terminal observation, reset, hand back the reset observation
+                if (B.terminal_obs) {
+#pragma unroll
+                    for (int k = 0; k < ACB200_OBS_DIM; ++k) B.terminal_obs[i * ACB200_OBS_DIM + k] = o[k];
+                }
+                env_reset_one(E, i, e);
+                env_observe(e, o);
+            }
+        }
+        env_scatter(B, i, e);
+    }
+    store_obs_block(B.obs, n, o, valid, stage);
+
+    if (B.stats) {
+        // warp tree, one shared-memory atomic per warp and field, one global atomic per block and field
+#pragma unroll
+        for (int k = 0; k < ACB200_STATS_FIELDS; ++k) {
+            T v = st[k];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&block_stats[k], (double)v);
+        }
+        __syncthreads();
+        if (threadIdx.x < ACB200_STATS_FIELDS) atomicAdd(&B.stats[threadIdx.x], block_stats[threadIdx.x]);
+    }
+}
+
+// ---- launchers -------------------------------------------------------------------------------------
+static inline unsigned grid_for(int64_t n) { return (unsigned)((n + kBlock - 1) / kBlock); }
+
+// Smallest k such that k successive fp64 additions of dt reach 0.2 (SettlingTimeBonus, rewards.py:207-211):
+// 11 for dt = 0.02, because ten additions give 0.19999999999999998.
+static inline int settle_steps_for(double dt) {
+    double t = 0.0;
+    for (int k = 1; k < 1000000; ++k) {
+        t += dt;
+        if (t >= 0.2) return k;
+    }
+    return 1000000;
+}
+
+template <typename T> static inline EnvConst<T> make_env_const(const acb200_env_config& cfg, int K, double h) {
+    EnvConst<T> E;
+    E.dt = (T)cfg.dt; E.h = (T)h; E.pid_throttle = (T)cfg.pid_throttle;
+    E.dt_f32 = (float)cfg.dt; E.residual_scale = (float)cfg.residual_scale;
+    E.K = K; E.max_steps = cfg.max_steps; E.controller = cfg.controller; E.auto_reset = cfg.auto_reset;
+    E.settle_steps = settle_steps_for(cfg.dt);
+    E.seed = cfg.seed; E.id_offset = cfg.id_offset;
+    return E;
+}
+
+template <typename T>
+cudaError_t Launch<T>::fleet_reset(const FleetPtrs<T>& f, const uint8_t* mask, const T* init_state, cudaStream_t st) {
+    if (f.n <= 0) return cudaSuccess;
+    fleet_reset_kernel<T><<<grid_for(f.n), kBlock, 0, st>>>(f, mask, init_state);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::step_surface(const acb200_aircraft_params& ap, const FleetPtrs<T>& f, const T* ctrl_in, int K, double h,
+                                    cudaStream_t st) {
+    if (f.n <= 0) return cudaSuccess;
+    step_surface_kernel<T><<<grid_for(f.n), kBlock, 0, st>>>(make_dyn_params<T>(ap), f, ctrl_in, K, (T)h);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::step_cascade(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const FleetPtrs<T>& f,
+                                    int level, const T* cmd, double dt_ctrl, int K, double h, T* surfaces_out, cudaStream_t st) {
+    if (f.n <= 0) return cudaSuccess;
+    const DynParams<T> P = make_dyn_params<T>(ap);
+    const CtrlParams<T> C = make_ctrl_params<T>(cp);
+    if (level == ACB200_LEVEL_ATTITUDE)
+        step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (T)h, surfaces_out);
+    else
+        step_cascade_kernel<T, ACB200_LEVEL_RATE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (T)h, surfaces_out);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::env_reset(const EnvPtrs<T>& e, const acb200_env_config& cfg, const uint8_t* mask, cudaStream_t st) {
+    if (e.f.n <= 0) return cudaSuccess;
+    env_reset_kernel<T><<<grid_for(e.f.n), kBlock, 0, st>>>(e, make_env_const<T>(cfg, 1, cfg.dt), mask);
+    return cudaGetLastError();
+}
+
+template <typename T>
+cudaError_t Launch<T>::env_step(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const EnvPtrs<T>& e,
+                                const acb200_env_config& cfg, int K, double h, const float* action, cudaStream_t st) {
+    if (e.f.n <= 0) return cudaSuccess;
+    env_step_kernel<T><<<grid_for(e.f.n), kBlock, 0, st>>>(make_dyn_params<T>(ap), make_ctrl_params<T>(cp),
+                                                           make_env_const<T>(cfg, K, h), e, action);
+    return cudaGetLastError();
+}
+
+template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, KernelInfo* out) {
+    const void* fn = nullptr;
+    if (!strcmp(name, "step_surface")) fn = (const void*)step_surface_kernel<T>;
+    else if (!strcmp(name, "step_cascade_rate")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_RATE>;
+    else if (!strcmp(name, "step_cascade_attitude")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE>;
+    else if (!strcmp(name, "env_step")) fn = (const void*)env_step_kernel<T>;
+    else if (!strcmp(name, "env_reset")) fn = (const void*)env_reset_kernel<T>;
+    else if (!strcmp(name, "fleet_reset")) fn = (const void*)fleet_reset_kernel<T>;
+    if (!fn) return cudaErrorInvalidValue;
+    cudaFuncAttributes a;
+    const cudaError_t err = cudaFuncGetAttributes(&a, fn);
+    if (err != cudaSuccess) return err;
+    out->regs = a.numRegs; out->local_bytes = (int)a.localSizeBytes; out->max_threads = a.maxThreadsPerBlock;
+    return cudaSuccess;
+}
+
+}  // namespace acb

@@ -1,0 +1,69 @@
+// params.cuh -- launch-constant parameter blocks, converted once on the host into the arithmetic
+// type of the build and passed to the kernels as __grid_constant__ arguments (constant bank).
+#pragma once
+#include "../../include/acb200.h"
+#include "math.cuh"
+
+namespace acb {
+
+// Derived from acb200_aircraft_params exactly the way Simplified6DOF.__init__ / _dynamics derive
+// them (simplified_6dof.py:181-187, 379, 407-409, 455, 474-481): each field is the result of the
+// same double operation the reference performs, so hoisting it out of the loop changes no bit.
+template <typename T> struct DynParams {
+    T mass, inv_mass, g, neg_g, half_rho;
+    T wing_area, wing_span, chord;
+    T cl_0, cl_alpha, cd_0, cd_alpha2;
+    T cl_elevator, cm_elevator, cy_rudder, cn_rudder, cl_aileron;
+    T cm_alpha, cn_beta, cl_beta;
+    T damping_roll, damping_pitch, damping_yaw;
+    T max_thrust, thrust_zero_velocity;
+    T min_airspeed_aero, min_u_velocity;
+    T max_elevator_rad, max_aileron_rad, max_rudder_rad;
+    T max_velocity, max_rate_rad, max_pitch_rad, max_alpha_rad;
+    T max_acceleration, max_angular_acceleration;
+    T ixx, iyy, izz, izz_m_iyy, ixx_m_izz, iyy_m_ixx;
+};
+
+template <typename T> struct PidCfg3 { acb200_pid_config axis[3]; };
+
+template <typename T> struct CtrlParams {
+    acb200_pid_config rate[3];
+    acb200_pid_config angle[3];
+    T max_roll_rate, max_pitch_rate, max_yaw_rate, max_roll, max_pitch;
+};
+
+static inline double host_radians(double deg) { return deg * (3.141592653589793 / 180.0); }  // np.radians
+
+template <typename T> static inline DynParams<T> make_dyn_params(const acb200_aircraft_params& a) {
+    DynParams<T> d;
+    d.mass = (T)a.mass; d.inv_mass = (T)(1.0 / a.mass); d.g = (T)a.gravity; d.neg_g = (T)(-a.gravity);
+    d.half_rho = (T)(0.5 * a.air_density);
+    d.wing_area = (T)a.wing_area; d.wing_span = (T)a.wing_span; d.chord = (T)a.chord;
+    d.cl_0 = (T)a.cl_0; d.cl_alpha = (T)a.cl_alpha; d.cd_0 = (T)a.cd_0; d.cd_alpha2 = (T)a.cd_alpha2;
+    d.cl_elevator = (T)a.cl_elevator; d.cm_elevator = (T)a.cm_elevator; d.cy_rudder = (T)a.cy_rudder;
+    d.cn_rudder = (T)a.cn_rudder; d.cl_aileron = (T)a.cl_aileron;
+    d.cm_alpha = (T)a.cm_alpha; d.cn_beta = (T)a.cn_beta; d.cl_beta = (T)a.cl_beta;
+    d.damping_roll = (T)a.damping_roll; d.damping_pitch = (T)a.damping_pitch; d.damping_yaw = (T)a.damping_yaw;
+    d.max_thrust = (T)a.max_thrust; d.thrust_zero_velocity = (T)a.thrust_zero_velocity;
+    d.min_airspeed_aero = (T)a.min_airspeed_aero; d.min_u_velocity = (T)a.min_u_velocity;
+    d.max_elevator_rad = (T)host_radians(a.max_elevator_deflection);
+    d.max_aileron_rad = (T)host_radians(a.max_aileron_deflection);
+    d.max_rudder_rad = (T)host_radians(a.max_rudder_deflection);
+    d.max_velocity = (T)a.max_velocity; d.max_rate_rad = (T)host_radians(a.max_angular_rate);
+    d.max_pitch_rad = (T)host_radians(a.max_pitch_angle); d.max_alpha_rad = (T)host_radians(a.max_alpha);
+    d.max_acceleration = (T)a.max_acceleration; d.max_angular_acceleration = (T)a.max_angular_acceleration;
+    d.ixx = (T)a.inertia_xx; d.iyy = (T)a.inertia_yy; d.izz = (T)a.inertia_zz;
+    d.izz_m_iyy = (T)(a.inertia_zz - a.inertia_yy); d.ixx_m_izz = (T)(a.inertia_xx - a.inertia_zz);
+    d.iyy_m_ixx = (T)(a.inertia_yy - a.inertia_xx);
+    return d;
+}
+
+template <typename T> static inline CtrlParams<T> make_ctrl_params(const acb200_controller_params& c) {
+    CtrlParams<T> o;
+    for (int i = 0; i < 3; ++i) { o.rate[i] = c.rate[i]; o.angle[i] = c.angle[i]; }
+    o.max_roll_rate = (T)c.max_roll_rate; o.max_pitch_rate = (T)c.max_pitch_rate; o.max_yaw_rate = (T)c.max_yaw_rate;
+    o.max_roll = (T)c.max_roll; o.max_pitch = (T)c.max_pitch;
+    return o;
+}
+
+}  // namespace acb

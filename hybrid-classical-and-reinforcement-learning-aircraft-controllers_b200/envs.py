@@ -1,0 +1,109 @@
+"""Batched rate-tracking environment: N RateControlEnv instances (learned_controllers/envs/rate_env.py
+in the reference) advanced by one fused kernel per control step, with SB3-VecEnv auto-reset semantics
+and the curriculum (difficulty, command type) as per-aircraft tensors."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _cabi
+from .fleet import _dtype, _ptr
+
+DIFFICULTY_SCALE = {"easy": 0.3, "medium": 0.5, "hard": 0.7}          # generators.py:41-45
+COMMAND_TYPES = {"step": _cabi.CMD_STEP, "ramp": _cabi.CMD_RAMP, "sine": _cabi.CMD_SINE, "random": _cabi.CMD_RANDOM}
+CONTROLLERS = {"external": _cabi.CTRL_EXTERNAL, "rate_pid": _cabi.CTRL_RATE_PID, "attitude_pid": _cabi.CTRL_ATTITUDE_PID,
+               "residual": _cabi.CTRL_RESIDUAL}
+COMPONENT_NAMES = ("tracking", "smoothness", "stability", "oscillation", "survival", "settle_bonus", "crash_penalty",
+                   "residual_bonus")
+STATS_NAMES = ("episodes", "return_sum", "return_sq_sum", "length_sum", "crashes", "truncations") + tuple(
+    "sum_" + c for c in COMPONENT_NAMES) + ("nonfinite_repairs", "aircraft_steps")
+
+
+class BatchedRateControlEnv:
+    """obs float32 [n,18]; action float32 [n,4] = aileron, elevator, rudder, throttle (rate_env.py:228-233)."""
+
+    def __init__(self, n: int, difficulty="medium", episode_length: float = 10.0, dt: float = 0.02,
+                 command_type="step", controller: str = "external", precision: int = 32, device=0, seed: int = 0,
+                 id_offset: int = 0, auto_reset: bool = True, pid_throttle: float = 0.6, residual_scale: float = 0.3,
+                 track_components: bool = False, ctx: Optional[_cabi.Context] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("acb200 needs a CUDA device (no CPU fallback)")
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.n, self.num_envs, self.precision, self.dtype = int(n), int(n), precision, _dtype(precision)
+        self.dt, self.episode_length = dt, episode_length
+        self.ctx = ctx or _cabi.Context(self.device.index or 0)
+        self.cfg = _cabi.EnvConfigC(dt=dt, dt_physics=0.001, max_steps=int(episode_length / dt),
+                                    controller=CONTROLLERS[controller], auto_reset=int(auto_reset),
+                                    pid_throttle=pid_throttle, residual_scale=residual_scale, seed=seed, id_offset=id_offset)
+        d, r = self.device, self.dtype
+        z = lambda shape, dt_: torch.zeros(shape, device=d, dtype=dt_)
+        self.state, self.controls, self.derived = z((13, n), r), z((4, n), r), z((4, n), r)
+        self.pid = z((18, n), torch.float32)
+        self.att_cmd, self.rate_cmd = z((4, n), r), z((3, n), r)
+        self.prev_action = z((4, n), torch.float32)
+        self.rew_mem, self.sched, self.env_time = z((7, n), r), z((7, n), r), z((n,), r)
+        self.step_count = z((n,), torch.int32)
+        self.is_settled, self.command_type = z((n,), torch.uint8), z((n,), torch.uint8)
+        self.difficulty = z((n,), torch.float32)
+        self.episode_idx = z((n,), torch.int32)          # uint32 on the device; torch has no uint32 arithmetic
+        self.ep_return = z((n,), r)
+        self.obs = z((n, 18), torch.float32)
+        self.reward = z((n,), r)
+        self.terminated, self.truncated = z((n,), torch.uint8), z((n,), torch.uint8)
+        self.terminal_obs = z((n, 18), torch.float32)
+        self.components = z((8, n), r) if track_components else None
+        self.stats = z((16,), torch.float64)
+        self._scratch = z((n * 5,), torch.float32)       # staged action + float reward for step_host
+        self.set_curriculum(difficulty, command_type)
+        self.c = _cabi.EnvC()
+        self.c.fleet = _cabi.FleetC(n=n, precision=precision, state=self.state.data_ptr(), controls=self.controls.data_ptr(),
+                                    derived=self.derived.data_ptr(), pid=self.pid.data_ptr())
+        for name in _cabi.ENV_POINTER_FIELDS:
+            t = getattr(self, name)
+            setattr(self.c, name, None if t is None else t.data_ptr())
+
+    # -- curriculum: a tensor write, not an env re-creation (train_rate.py:150-180 re-creates envs) ----
+    def set_curriculum(self, difficulty, command_type, mask: Optional[torch.Tensor] = None):
+        dv = difficulty if not isinstance(difficulty, str) else DIFFICULTY_SCALE[difficulty]
+        cv = command_type if not isinstance(command_type, str) else COMMAND_TYPES[command_type]
+        dv = torch.as_tensor(dv, device=self.device, dtype=torch.float32).expand(self.n)
+        cv = torch.as_tensor(cv, device=self.device, dtype=torch.uint8).expand(self.n)
+        if mask is None:
+            self.difficulty.copy_(dv); self.command_type.copy_(cv)
+        else:
+            m = mask.to(self.device).bool()
+            self.difficulty[m] = dv[m]; self.command_type[m] = cv[m]
+
+    def _bind_stream(self):
+        self.ctx.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def reset(self, mask: Optional[torch.Tensor] = None):
+        self._bind_stream()
+        if mask is not None:
+            mask = mask.to(self.device, torch.uint8).contiguous()
+        self.ctx.check(self.ctx.lib.acb200_env_reset(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(mask)))
+        return self.obs
+
+    def step(self, action: Optional[torch.Tensor] = None):
+        """One control step for every aircraft; tensors returned are views of the env's own buffers."""
+        self._bind_stream()
+        if action is not None:
+            assert action.dtype == torch.float32 and action.shape == (self.n, 4) and action.is_contiguous()
+        self.ctx.check(self.ctx.lib.acb200_env_step(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action)))
+        return self.obs, self.reward, self.terminated, self.truncated
+
+    def step_host(self, action_host, obs_host, reward_host, terminated_host, truncated_host):
+        """Same step with (pinned) HOST tensors in and out; synchronous."""
+        self._bind_stream()
+        self.ctx.check(self.ctx.lib.acb200_env_step_host(
+            self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action_host), _ptr(self._scratch), _ptr(obs_host),
+            _ptr(reward_host), _ptr(terminated_host), _ptr(truncated_host)))
+        return obs_host, reward_host, terminated_host, truncated_host
+
+    def episode_stats(self, reset: bool = False) -> dict:
+        v = self.stats.cpu().tolist()
+        if reset:
+            self.stats.zero_()
+        return dict(zip(STATS_NAMES, v))

@@ -1,0 +1,115 @@
+"""Batched aircraft backend: N Simplified6DOF simulators as one structure-of-arrays on the GPU.
+
+Mirrors SimulationAircraftBackend (simulation/simulation_backend.py:13-170 in the reference) with
+tensors instead of dataclasses: ``set_controls`` / ``step(dt)`` / ``reset`` / ``get_state`` keep their
+meaning; the cascaded agents (``step_rate``, ``step_attitude``) are fused with the physics step.
+torch is only the allocator and stream provider here; all arithmetic happens in libacb200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _cabi
+
+
+def _dtype(precision: int):
+    if precision == 64:
+        return torch.float64
+    if precision == 32:
+        return torch.float32
+    raise ValueError("precision must be 64 (parity build) or 32 (throughput build)")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class AircraftFleet:
+    """N aircraft.  state[13][n] = N,E,D,u,v,w,roll,pitch,yaw,p,q,r,time; controls[4][n] = elevator,
+    aileron, rudder, throttle; derived[4][n] = airspeed, altitude, ground_speed, heading; pid[18][n]."""
+
+    def __init__(self, n: int, precision: int = 64, device: int | str | torch.device = 0, config: Optional[dict] = None,
+                 ctx: Optional[_cabi.Context] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("acb200 needs a CUDA device (no CPU fallback)")
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.n, self.precision, self.dtype = int(n), precision, _dtype(precision)
+        config = config or {}
+        self.dt_physics = float(config.get("dt_physics", 0.001))          # simulation_backend.py:50
+        self.ctx = ctx or _cabi.Context(self.device.index or 0)
+        self.aircraft_params = config.get("params") or _cabi.default_aircraft_params(config.get("aircraft_type", "rc_plane"))
+        self.ctx.check(self.ctx.lib.acb200_set_aircraft_params(self.ctx.handle, C.byref(self.aircraft_params)))
+        self.controller_params = config.get("controller_params") or _cabi.default_controller_params()
+        self.ctx.check(self.ctx.lib.acb200_set_controller_params(self.ctx.handle, C.byref(self.controller_params)))
+        kw = dict(device=self.device, dtype=self.dtype)
+        self.state = torch.zeros((13, n), **kw)
+        self.controls = torch.zeros((4, n), **kw)
+        self.derived = torch.zeros((4, n), **kw)
+        self.pid = torch.zeros((18, n), device=self.device, dtype=torch.float32)
+        self._pending = torch.zeros((4, n), **kw)
+        self.c = _cabi.FleetC(n=n, precision=precision, state=self.state.data_ptr(), controls=self.controls.data_ptr(),
+                              derived=self.derived.data_ptr(), pid=self.pid.data_ptr())
+        self.reset()
+
+    # -- stream plumbing: enqueue on torch's current stream --------------------------------------
+    def _bind_stream(self):
+        self.ctx.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def reset(self, initial_state: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None):
+        """Simplified6DOF.reset: initial_state [13][n] or None for level flight at 100 m, 20 m/s."""
+        self._bind_stream()
+        if initial_state is not None:
+            initial_state = initial_state.to(self.device, self.dtype).contiguous()
+            assert initial_state.shape == (13, self.n)
+        if mask is not None:
+            mask = mask.to(self.device, torch.uint8).contiguous()
+        self.ctx.check(self.ctx.lib.acb200_fleet_reset(self.ctx.handle, C.byref(self.c), _ptr(mask), _ptr(initial_state)))
+        return self.state
+
+    def set_controls(self, surfaces: torch.Tensor):
+        """surfaces [4][n] in ControlSurfaces.to_array order; clipped when the step consumes them."""
+        self._pending.copy_(surfaces.to(self.device, self.dtype))
+
+    def step(self, dt: float):
+        self._bind_stream()
+        self.ctx.check(self.ctx.lib.acb200_step_surface(self.ctx.handle, C.byref(self.c), _ptr(self._pending), dt,
+                                                        self.dt_physics))
+        return self.state
+
+    def step_surface(self, surfaces: torch.Tensor, dt: float):
+        self.set_controls(surfaces)
+        return self.step(dt)
+
+    def _cascade(self, level, cmd, dt, dt_ctrl, surfaces_out):
+        self._bind_stream()
+        cmd = cmd.to(self.device, self.dtype).contiguous()
+        assert cmd.shape == (4, self.n)
+        self.ctx.check(self.ctx.lib.acb200_step_cascade(self.ctx.handle, C.byref(self.c), level, _ptr(cmd),
+                                                        dt if dt_ctrl is None else dt_ctrl, dt, self.dt_physics,
+                                                        _ptr(surfaces_out)))
+        return self.state
+
+    def step_rate(self, cmd: torch.Tensor, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None):
+        """RateAgent.compute_action(cmd, state, dt_ctrl) + set_controls + step(dt); cmd = p,q,r,throttle."""
+        return self._cascade(_cabi.LEVEL_RATE, cmd, dt, dt_ctrl, surfaces_out)
+
+    def step_attitude(self, cmd: torch.Tensor, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None):
+        """AttitudeAgent cascade; cmd = roll, pitch, yaw (NaN = None, +inf = hold current yaw), throttle."""
+        return self._cascade(_cabi.LEVEL_ATTITUDE, cmd, dt, dt_ctrl, surfaces_out)
+
+    def get_state(self):
+        return self.state
+
+    def get_backend_type(self) -> str:
+        return "simulation"
+
+    def get_dt_nominal(self) -> float:
+        return 0.01
+
+    def get_info(self) -> dict:
+        return {"backend_type": "simulation", "dt_nominal": 0.01, "physics_engine": "simplified_6dof",
+                "dt_physics": self.dt_physics, "aircraft_mass": self.aircraft_params.mass,
+                "max_thrust": self.aircraft_params.max_thrust, "n_aircraft": self.n, "precision": self.precision}

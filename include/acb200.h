@@ -1,0 +1,206 @@
+/*
+ * acb200.h -- C ABI of the B200-native batched flight-control path.
+ *
+ * One shared library (libacb200.so, built from
+ * hybrid-classical-and-reinforcement-learning-aircraft-controllers_b200/csrc) replaces, for N
+ * independent aircraft at once, the reference's per-aircraft Python/C++ hot path:
+ *
+ *   Simplified6DOF.step / _dynamics / get_state      simulation/simplified_6dof.py:228-331,333-503
+ *   SimulationAircraftBackend.step / set_controls     simulation/simulation_backend.py:82-112
+ *   PIDController / MultiAxisPIDController::compute   cpp/src/pid_controller.cpp:24-69,100-111
+ *   RateAgent / AttitudeAgent.compute_action          controllers/rate_agent.py:65-124, attitude_agent.py:86-154
+ *   RateControlEnv.reset / step (+ rewards, sampler)  learned_controllers/envs/rate_env.py:151-300,
+ *                                                     envs/rewards.py, data/generators.py
+ *   ResidualRateControlEnv.step                       learned_controllers/envs/residual_rate_env.py:99-157
+ *
+ * (paths relative to the reference repository root).  Plain pointers and sizes only; no torch, no
+ * C++ types.  Every buffer is CALLER-OWNED device memory (e.g. torch CUDA tensors: pass
+ * tensor.data_ptr()); the library allocates nothing per aircraft and never frees caller memory.
+ * All work is enqueued on the context's stream and is asynchronous; no hidden device synchronise
+ * (the *_host entry points, which move host buffers, synchronise that stream before returning).
+ * A context is bound to one device and is not thread-safe.
+ *
+ * Layout: structure of arrays, field-major X[field][n], n contiguous.  `real` is double when
+ * precision == 64 (parity build: fp64 physics/reward, fp32 PID, no FMA contraction) and float when
+ * precision == 32 (throughput build).
+ *
+ * Errors: every function returns 0 or a negative ACB200_E* code and never throws or exits;
+ * acb200_last_error() gives the message.  The Python adapters map ACB200_EVALUE to ValueError
+ * (the reference's bad-dt / bad-parameter exceptions, simplified_6dof.py:119-143,241-245).
+ */
+#ifndef ACB200_H
+#define ACB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ACB200_VERSION "0.1.0"
+
+enum {
+    ACB200_OK = 0,
+    ACB200_EVALUE = -1,   /* invalid argument value (reference: ValueError) */
+    ACB200_ECUDA = -2,    /* CUDA runtime error */
+    ACB200_ENULL = -3,    /* required pointer is NULL */
+    ACB200_ENOSUP = -4    /* combination not supported */
+};
+
+/* control levels, controllers/types.py:9-24 (ControlMode) */
+enum { ACB200_LEVEL_WAYPOINT = 1, ACB200_LEVEL_HSA = 2, ACB200_LEVEL_ATTITUDE = 3, ACB200_LEVEL_RATE = 4, ACB200_LEVEL_SURFACE = 5 };
+/* who drives the env's action */
+enum { ACB200_CTRL_EXTERNAL = 0, ACB200_CTRL_RATE_PID = 1, ACB200_CTRL_ATTITUDE_PID = 2, ACB200_CTRL_RESIDUAL = 3 };
+/* RateControlEnv command_type, rate_env.py:302-340 */
+enum { ACB200_CMD_STEP = 0, ACB200_CMD_RAMP = 1, ACB200_CMD_SINE = 2, ACB200_CMD_RANDOM = 3 };
+
+#define ACB200_STATE_FIELDS 13   /* N,E,D, u,v,w, roll,pitch,yaw, p,q,r, time   simplified_6dof.py:172,179 */
+#define ACB200_CTRL_FIELDS 4     /* elevator, aileron, rudder, throttle          controllers/types.py:190-194 */
+#define ACB200_DERIVED_FIELDS 4  /* airspeed, altitude, ground_speed, heading    simplified_6dof.py:306-319 */
+#define ACB200_PID_FIELDS 18     /* ((loop*3+axis)*3 + {integral, error_prev, derivative_filtered}); loop 0 rate, 1 angle */
+#define ACB200_OBS_DIM 18        /* rate_env.py:374-408 */
+#define ACB200_STATS_FIELDS 16
+
+/* simulation/simplified_6dof.py:31-117 (AircraftParams), same field order; always double. */
+typedef struct {
+    double mass, inertia_xx, inertia_yy, inertia_zz;
+    double wing_area, wing_span, chord;
+    double cl_0, cl_alpha, cd_0, cd_alpha2;
+    double cl_elevator, cm_elevator, cy_rudder, cn_rudder, cl_aileron;
+    double cm_alpha, cn_beta, cl_beta;
+    double damping_roll, damping_pitch, damping_yaw;
+    double max_thrust, air_density, gravity;
+    double min_airspeed_aero, min_u_velocity;
+    double max_elevator_deflection, max_aileron_deflection, max_rudder_deflection; /* degrees */
+    double thrust_zero_velocity;
+    double max_velocity, max_angular_rate, max_pitch_angle, max_alpha;             /* m/s, deg/s, deg, deg */
+    double max_acceleration, max_angular_acceleration;
+    double max_timestep, min_timestep;
+} acb200_aircraft_params;
+
+/* cpp/include/pid_controller.h:22-49 (PIDGains + PIDConfig) */
+typedef struct {
+    float kp, ki, kd;
+    float output_min, output_max, integral_min, integral_max, derivative_filter_alpha;
+} acb200_pid_config;
+
+/* cpp/include/pid_controller.h:123-133 (PIDController state) */
+typedef struct {
+    float error, error_prev, integral, derivative, derivative_filtered, output;
+} acb200_pid_state;
+
+/* controllers/types.py:294-350 (ControllerConfig) after create_pid_config (pid_utils.py:16-46) */
+typedef struct {
+    acb200_pid_config rate[3];    /* roll_rate_gains, pitch_rate_gains, yaw_gains; output [-1,1]   rate_agent.py:41-50 */
+    acb200_pid_config angle[3];   /* roll_angle_gains, pitch_angle_gains, yaw_gains; output +-max rate  attitude_agent.py:43-64 */
+    double max_roll_rate, max_pitch_rate, max_yaw_rate;   /* rad/s */
+    double max_roll, max_pitch;                           /* rad   */
+} acb200_controller_params;
+
+/* The aircraft fleet: what N SimulationAircraftBackend objects hold. */
+typedef struct {
+    int64_t n;
+    int32_t precision;     /* 64 or 32 */
+    int32_t _pad;
+    void* state;           /* real[13][n] */
+    void* controls;        /* real[4][n]  controls held by the simulator (clipped)   simplified_6dof.py:221-226; nullable */
+    void* derived;         /* real[4][n]  refreshed at the end of every step call; nullable */
+    float* pid;            /* float[18][n] PID memory of the rate and angle loops; required for levels 3,4 */
+} acb200_fleet;
+
+/* What N RateControlEnv objects hold (plus the fleet they fly). */
+typedef struct {
+    acb200_fleet fleet;
+    void* att_cmd;          /* real[4][n]   roll,pitch,yaw,throttle for ACB200_CTRL_ATTITUDE_PID; yaw NaN = None (->0), +inf = hold current yaw */
+    void* rate_cmd;         /* real[3][n]   rate_env.py:92 */
+    float* prev_action;     /* float[4][n]  aileron, elevator, rudder, throttle   rate_env.py:93,193,282 */
+    void* rew_mem;          /* real[7][n]   prev_errors[3], sign_changes[3], settle_timer   rewards.py:44-46,187 */
+    void* sched;            /* real[7][n]   ramp end[3] | sine amplitudes[3], sine frequency   rate_env.py:96-97 */
+    void* env_time;         /* real[n]      rate_env.py:87,241 */
+    int32_t* step_count;    /* [n]          rate_env.py:89 */
+    uint8_t* is_settled;    /* [n]          rewards.py:188 */
+    uint8_t* command_type;  /* [n]          ACB200_CMD_*; the curriculum is a write to this and `difficulty` */
+    float* difficulty;      /* float[n]     difficulty_scale 0.3/0.5/0.7   generators.py:41-45 */
+    uint32_t* episode_idx;  /* [n]          Philox counter word, +1 per reset */
+    void* ep_return;        /* real[n]      running episode return (SB3 Monitor "r") */
+    /* outputs of reset/step */
+    float* obs;             /* float[n][18] row-major */
+    void* reward;           /* real[n] */
+    uint8_t* terminated;    /* [n] */
+    uint8_t* truncated;     /* [n] */
+    float* terminal_obs;    /* float[n][18] written for finished aircraft only (SB3 terminal_observation); nullable */
+    void* components;       /* real[8][n]  tracking, smoothness, stability, oscillation, survival, settle_bonus,
+                                            crash_penalty, residual_bonus (info["reward_components"]); nullable */
+    double* stats;          /* double[16] accumulated: episodes, sum return, sum return^2, sum length, crashes, truncations,
+                               sum of the 8 components, non-finite repairs, aircraft-steps; nullable */
+} acb200_env;
+
+typedef struct {
+    double dt;              /* 0.02   rate_env.py:42 */
+    double dt_physics;      /* 0.001  rate_env.py:69 */
+    int32_t max_steps;      /* int(episode_length/dt)  rate_env.py:88 */
+    int32_t controller;     /* ACB200_CTRL_* */
+    int32_t auto_reset;     /* 1 = SB3 VecEnv semantics */
+    int32_t _pad;
+    double pid_throttle;    /* 0.6  residual_rate_env.py:122 */
+    double residual_scale;  /* 0.3  residual_rate_env.py:33 */
+    uint64_t seed;          /* Philox key */
+    int64_t id_offset;      /* global id of local aircraft 0: results do not depend on how the fleet is sharded */
+} acb200_env_config;
+
+typedef struct acb200_ctx acb200_ctx;
+
+/* ---- context ---- */
+const char* acb200_version(void);
+int acb200_create(int device, acb200_ctx** out);
+void acb200_destroy(acb200_ctx* ctx);
+const char* acb200_last_error(const acb200_ctx* ctx);
+int acb200_set_stream(acb200_ctx* ctx, void* cuda_stream);          /* cudaStream_t; NULL = legacy default stream */
+int acb200_synchronize(acb200_ctx* ctx);
+
+/* ---- parameters (AircraftParams.__post_init__ validation -> ACB200_EVALUE) ---- */
+void acb200_default_aircraft_params(acb200_aircraft_params* p);       /* 'rc_plane'  simulation_backend.py:74-76 */
+void acb200_cessna_aircraft_params(acb200_aircraft_params* p);        /* 'cessna'    simulation_backend.py:64-73 */
+void acb200_default_controller_params(acb200_controller_params* c);
+int acb200_set_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p);
+int acb200_set_controller_params(acb200_ctx* ctx, const acb200_controller_params* c);
+
+/* ---- physics ---- */
+/* Simplified6DOF.reset for aircraft with mask[i] != 0 (mask NULL = all).  init_state real[13][n] or
+ * NULL for the default level flight at 100 m / 20 m/s (simplified_6dof.py:197-204).  Zeroes their PID
+ * memory and held controls, refreshes derived. */
+int acb200_fleet_reset(acb200_ctx* ctx, const acb200_fleet* f, const uint8_t* mask, const void* init_state);
+
+/* backend.set_controls(ctrl_in) then backend.step(dt): K = max(1,int(dt/dt_physics)) RK4 substeps of
+ * h = dt/K.  ctrl_in real[4][n].  h outside (min_timestep, max_timestep] -> ACB200_EVALUE. */
+int acb200_step_surface(acb200_ctx* ctx, const acb200_fleet* f, const void* ctrl_in, double dt, double dt_physics);
+
+/* surfaces = agent(level).compute_action(cmd, state, dt_ctrl); backend.set_controls; backend.step(dt).
+ * level 4: cmd real[4][n] = roll_rate, pitch_rate, yaw_rate, throttle
+ * level 3: cmd real[4][n] = roll, pitch, yaw (NaN = None, +inf = hold current yaw), throttle
+ * surfaces_out real[4][n] nullable. */
+int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const void* cmd, double dt_ctrl,
+                        double dt, double dt_physics, void* surfaces_out);
+
+/* ---- rate-tracking environment ---- */
+int acb200_env_reset(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const uint8_t* mask);
+/* action float[n][4] (aileron, elevator, rudder, throttle); may be NULL unless controller is EXTERNAL/RESIDUAL */
+int acb200_env_step(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const float* action);
+/* Same step with HOST buffers (pinned for speed): copies action in, obs/reward/terminated/truncated out,
+ * and synchronises the stream.  reward_host is float[n] (what a VecEnv hands to the trainer). */
+int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg,
+                         const float* action_host, float* action_dev /* device scratch, n*5 floats */, float* obs_host, float* reward_host,
+                         uint8_t* terminated_host, uint8_t* truncated_host);
+
+/* ---- host-side PID core (the same fp32 arithmetic as the kernels; mirrors PIDController::compute/reset) ---- */
+float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt);
+void acb200_pid_reset(acb200_pid_state* st);
+
+/* ---- introspection ---- */
+int acb200_kernel_info(int precision, const char* kernel, int* regs, int* local_bytes, int* max_threads);
+int64_t acb200_launch_count(const acb200_ctx* ctx);   /* kernels launched through this context so far */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ACB200_H */

@@ -1,0 +1,133 @@
+"""Parity of the fp64 env kernel (controller + RateControlEnv.step + reward + termination + Philox
+auto-reset) against the golden reference episodes and against the CPU oracle."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, rel_err
+from helpers import rel_err_cols
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+CTRL_NAME = {0: "external", 1: "rate_pid", 2: "attitude_pid", 3: "residual"}
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import torch
+    import acb200
+    from oracle import oracle as orc
+    return torch, acb200, orc
+
+
+def test_golden_episodes(mods):
+    """Reference episodes (RateControlEnv / ResidualRateControlEnv, its own initial draws injected)."""
+    torch, acb200, orc = mods
+    g = np.load(os.path.join(GOLDEN, "rate_env.npz"))
+    for k in range(int(g["n_cases"])):
+        seed, scale, ctype, ctrl = g[f"c{k}_meta"]
+        env = acb200.BatchedRateControlEnv(1, difficulty=float(scale), command_type=int(ctype), controller=CTRL_NAME[int(ctrl)],
+                                           precision=64, auto_reset=False, track_components=True)
+        s0 = g[f"c{k}_s0"]
+        env.state[:, 0] = torch.as_tensor(s0, device="cuda")
+        env.derived[:, 0] = torch.as_tensor(orc.derived(np.ascontiguousarray(s0[:12])), device="cuda")
+        env.rate_cmd[:, 0] = torch.as_tensor(g[f"c{k}_cmd0"], device="cuda")
+        env.sched[:, 0] = torch.as_tensor(g[f"c{k}_sched"], device="cuda")
+        env.prev_action[:, 0] = torch.tensor([0, 0, 0, 0.5], device="cuda")
+        acts = torch.as_tensor(g[f"c{k}_actions"], device="cuda")
+        T = len(g[f"c{k}_reward"])
+        for t in range(T):
+            a = acts[t][None, :].contiguous() if int(ctrl) in (0, 3) else None
+            obs, rew, term, trunc = env.step(a)
+            ctx = f"case {k} step {t + 1}"
+            assert rel_err(env.state[:, 0].cpu().numpy(), g[f"c{k}_states"][t]) <= TOL, ctx
+            assert rel_err(obs[0].cpu().numpy(), g[f"c{k}_obs"][t]) <= 2e-7, ctx
+            assert abs(float(rew[0]) - g[f"c{k}_reward"][t]) <= 1e-7, ctx
+            assert bool(term[0]) == bool(g[f"c{k}_terminated"][t]) and bool(trunc[0]) == bool(g[f"c{k}_truncated"][t]), ctx
+            assert bool(env.is_settled[0]) == bool(g[f"c{k}_is_settled"][t]), ctx
+            comp = env.components[:, 0].cpu().numpy(); exp = g[f"c{k}_components"][t]
+            assert np.allclose(comp[:5], exp[:5], rtol=0, atol=1e-7), ctx
+            assert abs((comp[5] + comp[7]) - exp[5]) <= 1e-7 and comp[6] == exp[6], ctx
+            if int(ctrl) == 1:
+                assert np.array_equal(env.prev_action[:, 0].cpu().numpy(), g[f"c{k}_actions"][t]), ctx
+
+
+def test_reset_sampler_matches_oracle_bit_for_bit(mods):
+    torch, acb200, orc = mods
+    n = 5000
+    ct = np.arange(n) % 4
+    diff = np.array([0.3, 0.5, 0.7], np.float32)[np.arange(n) % 3]
+    env = acb200.BatchedRateControlEnv(n, precision=64, seed=42, id_offset=1000)
+    env.set_curriculum(torch.as_tensor(diff), torch.as_tensor(ct.astype(np.uint8)))
+    ref = orc.Env(n, seed=42, id_offset=1000, difficulty=diff, command_type=ct.astype(np.uint8))
+    for _ in range(2):          # two episodes: the counter word moves
+        env.reset(); ref.reset()
+        assert np.array_equal(env.state.cpu().numpy()[:12], ref.state[:12])
+        assert np.array_equal(env.rate_cmd.cpu().numpy(), ref.rate_cmd)
+        assert np.array_equal(env.sched.cpu().numpy(), ref.sched)
+        assert rel_err(env.derived.cpu().numpy(), ref.derived) <= 1e-12
+        assert rel_err(env.obs.cpu().numpy(), ref.obs) <= 2e-7
+    # masked reset touches only the selected aircraft
+    before = env.state.clone()
+    mask = torch.zeros(n, dtype=torch.uint8); mask[::3] = 1
+    env.reset(mask); ref.reset(mask.numpy())
+    assert np.array_equal(env.state.cpu().numpy()[:12], ref.state[:12])
+    assert torch.equal(env.state[:, 1], before[:, 1])
+
+
+@pytest.mark.parametrize("controller,steps", [("rate_pid", 700), ("attitude_pid", 300), ("external", 300), ("residual", 300)])
+def test_env_vs_oracle_with_auto_reset(mods, controller, steps):
+    """Config 3 shape at reduced N: mixed curriculum, in-kernel Philox auto-reset, episode statistics."""
+    torch, acb200, orc = mods
+    n = 2048
+    rng = np.random.default_rng(7)
+    ct = (np.arange(n) % 3).astype(np.uint8)                       # step / ramp / sine (random walk: distribution test)
+    diff = np.array([0.3, 0.5, 0.7], np.float32)[rng.integers(0, 3, n)]
+    env = acb200.BatchedRateControlEnv(n, controller=controller, precision=64, seed=42, track_components=True)
+    env.set_curriculum(torch.as_tensor(diff), torch.as_tensor(ct))
+    ref = orc.Env(n, controller=acb200.envs.CONTROLLERS[controller], seed=42, difficulty=diff, command_type=ct)
+    att = np.zeros((4, n)); att[0] = rng.uniform(-0.35, 0.35, n); att[1] = rng.uniform(-0.03, 0.08, n)
+    att[2] = np.inf; att[3] = rng.uniform(0.5, 0.8, n)
+    env.att_cmd.copy_(torch.as_tensor(att)); ref.att_cmd[:] = att
+    env.reset(); ref.reset()
+    ok = np.ones(n, bool)
+    diverged = 0
+    worst = 0.0
+    done_total = 0
+    for t in range(steps):
+        a = None
+        if controller in ("external", "residual"):
+            a = (rng.uniform(-1, 1, (n, 4)) * (0.05 if controller == "external" else 1.0)).astype(np.float32)
+            if controller == "external":
+                a[:, 3] = 0.6
+        obs, rew, term, trunc = env.step(None if a is None else torch.as_tensor(a, device="cuda"))
+        robs, rrew, rterm, rtrunc = ref.step(a)
+        gterm, gtrunc = term.cpu().numpy(), trunc.cpu().numpy()
+        # an aircraft stays in the comparison while its float memories are bit-identical to the oracle's
+        same = (np.all(env.pid.cpu().numpy().view(np.uint32) == ref.pid.view(np.uint32), axis=0)
+                & np.all(env.prev_action.cpu().numpy().view(np.uint32) == ref.prev_action.view(np.uint32), axis=0)
+                & (gterm == rterm) & (gtrunc == rtrunc))
+        diverged += int((ok & ~same).sum())
+        ok &= same
+        e = rel_err_cols(env.state.cpu().numpy(), ref.state)
+        worst = max(worst, float(e[ok].max()))
+        assert (e[ok] <= TOL).all(), f"step {t + 1}: {e[ok].max():.3e}"
+        assert np.array_equal(gterm[ok], rterm[ok]) and np.array_equal(gtrunc[ok], rtrunc[ok])
+        assert np.max(np.abs(rew.cpu().numpy()[ok] - rrew[ok])) <= 1e-7
+        assert rel_err(obs.cpu().numpy()[ok], robs[ok]) <= 2e-7
+        done = (rterm | rtrunc).astype(bool)
+        done_total += int(done.sum())
+        if done.any():
+            sel = done & ok
+            assert rel_err(env.terminal_obs.cpu().numpy()[sel], ref.terminal_obs[sel]) <= 2e-7
+        # a finished aircraft starts a fresh episode from the shared Philox stream: it rejoins the comparison
+        ok |= done & (gterm == rterm) & (gtrunc == rtrunc)
+    assert done_total > 0, "no episode finished: auto-reset path untested"
+    assert diverged <= 0.02 * n + 2, diverged
+    if diverged == 0:
+        st, rst = env.episode_stats(), ref.stats
+        got = np.array(list(st.values()))
+        assert np.allclose(got[[0, 3, 4, 5, 15]], rst[[0, 3, 4, 5, 15]])
+        assert np.allclose(got[[1, 6, 7, 8, 9, 10, 11, 12, 13]], rst[[1, 6, 7, 8, 9, 10, 11, 12, 13]], rtol=1e-9, atol=1e-6)
+    print(f"{controller}: worst state rel err {worst:.3e}, {done_total} episodes finished, {diverged} aircraft left bit-identity")
