@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py -- env-steps/s of the batched flight-control path on B200 (BASELINE.json metric).
+
+Workload (BASELINE.json configs[2], "C3"): 2^20 aircraft per GPU, each a RateControlEnv (dt 0.02 =
+20 RK4 substeps of 1 ms) flown by the full cascaded attitude -> rate -> surface PID, "step" rate
+commands, per-aircraft difficulty drawn from {easy, medium, hard}, in-kernel Philox curriculum
+resets.  One "step" = one control step of every aircraft = ONE launch of env_step_kernel<float>.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+    python bench.py --impl reference [...]                          # the CPU arm (oracle port, all cores)
+
+For N > 1 launch under torchrun (one rank per GPU); aircraft are sharded by global id with no
+data-path collective (weak scaling), the only NCCL traffic is the episode-statistics all-reduce.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "aircraft env-steps/sec (full cascaded PID, 20 RK4 substeps per env step)"
+UNIT = "env-steps/s"
+K_SUB = 20
+# algorithmic work per env step, A(K) = 1014 K + 320 FLOP; HBM bytes at the control-step boundary
+FLOP_PER_ENV_STEP = 1014 * K_SUB + 320
+FP32_PEAK_DERIVED_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # 74.4: 148 SM x 128 lanes x FMA x max clock
+
+
+def workload_name(n):
+    return (f"C3: {n} aircraft/GPU, attitude->rate->surface PID cascade + RateControlEnv reward/termination/"
+            f"Philox curriculum reset (easy/medium/hard mix), dt=0.02 K=20 RK4 substeps")
+
+
+def env_bytes_per_step(precision):
+    """Algorithmic HBM bytes per aircraft per env step for env_step_kernel (read + write), from the
+    buffers the kernel gathers and scatters (kernels.cuh env_gather / env_scatter / outputs)."""
+    r = precision // 8
+    rd = 13 * r + 4 * r + 18 * 4 + 3 * r + 4 * 4 + 7 * r + 7 * r + r + 4 + 4 + 1 + 1 + 4 + r + 4 * r   # + att_cmd
+    wr = 13 * r + 4 * r + 18 * 4 + 3 * r + 4 * 4 + 7 * r + 7 * r + r + 4 + 4 + 1 + r + 72 + r + 1 + 1
+    return rd + wr
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1])); pw.append(float(p[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_inputs(n, id_offset, seed=42):
+    """Synthetic C3 inputs by GLOBAL aircraft id, so results do not depend on the sharding."""
+    import numpy as np
+    ids = np.arange(id_offset, id_offset + n, dtype=np.uint64)
+    # splitmix-style hash -> three uniform streams (host side, cheap, shard-independent)
+    def u(stream):
+        x = (ids + np.uint64(seed * 0x9E3779B97F4A7C15 & 0xFFFFFFFFFFFFFFFF) + np.uint64(stream) * np.uint64(0xBF58476D1CE4E5B9))
+        x ^= x >> np.uint64(30); x *= np.uint64(0xBF58476D1CE4E5B9)
+        x ^= x >> np.uint64(27); x *= np.uint64(0x94D049BB133111EB)
+        x ^= x >> np.uint64(31)
+        return (x >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+    with np.errstate(over="ignore"):
+        difficulty = np.array([0.3, 0.5, 0.7], np.float32)[np.minimum((u(1) * 3).astype(np.int64), 2)]
+        att = np.zeros((4, n), np.float64)
+        att[0] = np.radians(-20 + 40 * u(2)); att[1] = np.radians(-20 + 40 * u(3))
+        att[2] = np.inf                                   # hold current yaw (what HSAAgent commands, hsa_agent.py:214-216)
+        att[3] = 0.6
+        phase = (u(4) * 500).astype(np.int32)             # de-synchronise the episodes: resets are spread over steps
+    return difficulty, att, phase
+
+
+def oracle_env(n, nthreads, id_offset=0):
+    import numpy as np
+    from oracle import oracle as orc
+    difficulty, att, phase = make_inputs(n, id_offset)
+    env = orc.Env(n, controller=orc.CTRL_ATTITUDE_PID, seed=42, id_offset=id_offset, difficulty=difficulty,
+                  command_type=orc.CMD_STEP, nthreads=nthreads)
+    env.att_cmd[:] = att
+    env.reset()
+    env.step_count[:] = phase
+    return env
+
+
+def time_oracle(n, nthreads, warmup, steps=None, budget_s=None):
+    env = oracle_env(n, nthreads)
+    for _ in range(warmup):
+        env.step()
+    t0 = time.perf_counter()
+    done = 0
+    while True:
+        env.step(); done += 1
+        if steps is not None and done >= steps:
+            break
+        if budget_s is not None and done >= 3 and time.perf_counter() - t0 >= budget_s:
+            break
+    el = time.perf_counter() - t0
+    return n * done / el, done, el
+
+
+def run_reference(args):
+    """CPU arm: the reference algorithm (oracle port, C, OpenMP over aircraft) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n = args.ref_envs
+    value, done, el = time_oracle(n, cores, args.warmup, steps=args.steps)
+    sample = f"{n} aircraft x {done} env steps of the same C3 workload (bounded sample), OpenMP over aircraft"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * el / done, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(1 << 20), "sample_envs": n},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def run_gpu(args):
+    import numpy as np
+    import torch
+    import acb200
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.envs
+    precision = args.precision
+    env = acb200.BatchedRateControlEnv(n, controller="attitude_pid", precision=precision, device=local, seed=42,
+                                       id_offset=rank * n, command_type="step")
+    difficulty, att, phase = make_inputs(n, rank * n)
+    env.set_curriculum(torch.as_tensor(difficulty), "step")
+    env.att_cmd.copy_(torch.as_tensor(att).to(env.dtype))
+    env.reset()
+    env.step_count.copy_(torch.as_tensor(phase))
+    torch.cuda.synchronize()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident arm: `value` -------------------------------------------------------------
+    for _ in range(args.warmup):
+        env.step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    l0 = env.ctx.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        env.step()
+    ev1.record()
+    barrier()
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = env.ctx.launch_count - l0
+    clk = clocks.stop() if rank == 0 else None
+    # the one collective of the path: episode statistics summed over ranks (outside the per-step loop)
+    stats = env.stats.clone()
+    if dist is not None:
+        dist.all_reduce(stats)
+    value = n * world * args.steps / (ms * 1e-3)
+
+    # ---- end-to-end arm: host buffers, H2D of the step's commands + D2H of obs/reward/done every step
+    pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
+    att_host = pin((4, n), env.dtype); att_host.copy_(torch.as_tensor(att).to(env.dtype))
+    obs_h, rew_h = pin((n, 18), torch.float32), pin((n,), torch.float32)
+    term_h, trunc_h = pin((n,), torch.uint8), pin((n,), torch.uint8)
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    for _ in range(2):
+        env.att_cmd.copy_(att_host, non_blocking=True)
+        env.step_host(None, obs_h, rew_h, term_h, trunc_h)
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        env.att_cmd.copy_(att_host, non_blocking=True)
+        env.step_host(None, obs_h, rew_h, term_h, trunc_h)
+    ev1.record()
+    barrier()
+    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
+    h2d = att_host.numel() * att_host.element_size()
+    d2h = sum(t.numel() * t.element_size() for t in (obs_h, rew_h, term_h, trunc_h))
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    per_gpu = value / world
+    bytes_step = env_bytes_per_step(precision)
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    fp_peak = FP32_PEAK_DERIVED_TFLOPS if precision == 32 else FP32_PEAK_DERIVED_TFLOPS / 2
+    achieved_tflops = per_gpu * FLOP_PER_ENV_STEP / 1e12
+    achieved_gbs = per_gpu * bytes_step / 1e9
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if precision == 32 else "f64", "data": "synthetic",
+        "config": {"workload": workload_name(n), "envs_per_gpu": n, "controller": "attitude_pid", "substeps": K_SUB,
+                   "l2": f"working set {n * bytes_step / 2 / 1e6:.0f} MB per step > 126 MB L2 (inputs larger than L2)",
+                   "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
+        "roofline": {"bound": "fp32-pipe (non-tensor compute; see DESIGN.md: the path is not HBM- or tensor-bound)",
+                     "achieved": achieved_tflops, "peak": fp_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fp_peak,
+                     "peak_source": "derived 148 SM x 128 lanes x 2 x 1.965 GHz (no non-tensor peak in MEASURED_PEAKS.json)",
+                     "flop_per_env_step": FLOP_PER_ENV_STEP, "kernel": "env_step_kernel", "kernel_ms": ms / args.steps,
+                     "traffic": None},
+        "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+                         "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
+                         "bytes_per_env_step": bytes_step, "traffic": None},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "ms_per_step": e2e_ms / e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "episode_stats": dict(zip(acb200.envs.STATS_NAMES, stats.cpu().tolist())),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        v, done, el = time_oracle(args.ref_envs, cores, 1, budget_s=args.cpu_seconds)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"{args.ref_envs} aircraft x {done} env steps ({el:.1f} s) of the same workload, C oracle with OpenMP"}
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--envs", type=int, default=1 << 20, help="aircraft per GPU")
+    ap.add_argument("--precision", type=int, default=32, choices=[32, 64])
+    ap.add_argument("--ref-envs", type=int, default=16384, help="aircraft in the bounded CPU sample")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--e2e-steps", type=int, default=50)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
