@@ -221,7 +221,6 @@ def run_gpu(args):
     barrier()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = env.ctx.launch_count - l0
-    clk = clocks.stop() if rank == 0 else None
     # the one collective of the path: episode statistics summed over ranks (outside the per-step loop)
     stats = env.stats.clone()
     if dist is not None:
@@ -246,6 +245,7 @@ def run_gpu(args):
     barrier()
     e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
     e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
+    clk = clocks.stop() if rank == 0 else None           # sampled over both timed regions
     h2d = att_host.numel() * att_host.element_size()
     d2h = sum(t.numel() * t.element_size() for t in (obs_h, rew_h, term_h, trunc_h))
 
@@ -300,7 +300,7 @@ def run_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--envs", type=int, default=1 << 20, help="aircraft per GPU")

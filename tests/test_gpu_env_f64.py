@@ -84,9 +84,14 @@ def test_env_vs_oracle_with_auto_reset(mods, controller, steps):
     rng = np.random.default_rng(7)
     ct = (np.arange(n) % 3).astype(np.uint8)                       # step / ramp / sine (random walk: distribution test)
     diff = np.array([0.3, 0.5, 0.7], np.float32)[rng.integers(0, 3, n)]
-    env = acb200.BatchedRateControlEnv(n, controller=controller, precision=64, seed=42, track_components=True)
+    # the attitude cascade keeps every aircraft inside the envelope: shorten its episodes so that truncation
+    # exercises the in-kernel auto-reset too
+    ep_len = 2.0 if controller == "attitude_pid" else 10.0
+    env = acb200.BatchedRateControlEnv(n, controller=controller, precision=64, seed=42, track_components=True,
+                                       episode_length=ep_len)
     env.set_curriculum(torch.as_tensor(diff), torch.as_tensor(ct))
-    ref = orc.Env(n, controller=acb200.envs.CONTROLLERS[controller], seed=42, difficulty=diff, command_type=ct)
+    ref = orc.Env(n, controller=acb200.envs.CONTROLLERS[controller], seed=42, difficulty=diff, command_type=ct,
+                  episode_length=ep_len)
     att = np.zeros((4, n)); att[0] = rng.uniform(-0.35, 0.35, n); att[1] = rng.uniform(-0.03, 0.08, n)
     att[2] = np.inf; att[3] = rng.uniform(0.5, 0.8, n)
     env.att_cmd.copy_(torch.as_tensor(att)); ref.att_cmd[:] = att

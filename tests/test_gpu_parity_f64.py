@@ -148,16 +148,25 @@ def test_cascade_vs_oracle(mods, level, n, steps):
     cmd_dev = _t(torch, cmd)
     P, Cp = orc.default_aircraft_params(), orc.default_controller_params()
     ref = s0.copy(); rpid = np.zeros((18, n), np.float32); rder = np.zeros((4, n)); rsurf = np.zeros((4, n))
+    # conditioning probe: the oracle itself, started one ulp away in u.  An aircraft whose own reference
+    # trajectory moves by more than 1e-11 under that perturbation (violent manoeuvres near saturation) cannot
+    # be expected to agree to 1e-9 between two libms; it leaves the comparison and is counted.
+    pert = s0.copy(); pert[3] = np.nextafter(pert[3], np.inf); ppid = np.zeros((18, n), np.float32)
     surf = torch.zeros((4, n), device="cuda", dtype=torch.float64)
-    ok = np.ones(n, bool)          # in envelope and no float rounding flip so far
+    ok = np.ones(n, bool)          # in envelope, well conditioned and no float rounding flip so far
     flips = 0
+    ill = 0
     worst = 0.0
     for t in range(steps):
         (fleet.step_rate if level == 4 else fleet.step_attitude)(cmd_dev[t // hold], dt, surfaces_out=surf)
         orc.step_cascade(P, Cp, level, ref, np.ascontiguousarray(cmd[t // hold]), rpid, dt, surfaces_out=rsurf, derived_out=rder)
+        orc.step_cascade(P, Cp, level, pert, np.ascontiguousarray(cmd[t // hold]), ppid, dt)
         if (t + 1) % 20 == 0 or t == steps - 1:
             got = fleet.state.cpu().numpy(); gpid = fleet.pid.cpu().numpy()
             env_ok = in_envelope(ref, rder)
+            well = rel_err_cols(pert, ref) <= 1e-11
+            ill += int((ok & env_ok & ~well).sum())
+            ok &= well
             same_pid = np.all(gpid.view(np.uint32) == rpid.view(np.uint32), axis=0)
             flips += int((ok & env_ok & ~same_pid).sum())
             ok &= env_ok & same_pid
@@ -166,5 +175,7 @@ def test_cascade_vs_oracle(mods, level, n, steps):
                 worst = max(worst, float(e[ok].max()))
                 assert (e[ok] <= TOL).all(), f"level {level} step {t + 1}: {e[ok].max():.3e}"
     assert flips <= 0.02 * n, f"{flips} aircraft lost PID bit-identity"
+    assert ill <= 0.05 * n, f"{ill} aircraft ill-conditioned"
     assert ok.mean() > 0.4, ok.mean()
-    print(f"cascade level {level}: worst rel err {worst:.3e}; {ok.mean():.0%} compared to the end, {flips} float-rounding flips")
+    print(f"cascade level {level}: worst rel err {worst:.3e}; {ok.mean():.0%} compared to the end, {flips} float-rounding flips, "
+          f"{ill} ill-conditioned (reference moves > 1e-11 under a 1-ulp perturbation)")
