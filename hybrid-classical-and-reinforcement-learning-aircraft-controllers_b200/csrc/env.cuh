@@ -43,15 +43,22 @@ template <typename T> __device__ __forceinline__ void env_observe(const EnvRegs<
     o[14] = e.prev_action[0]; o[15] = e.prev_action[1]; o[16] = e.prev_action[2]; o[17] = e.prev_action[3];
 }
 
-// RateControlEnv.reset with FlightEnvelopeSampler.sample and _generate_new_command.  Draw plan
-// (Philox block b of counter (id_lo, id_hi, episode, b)):
+// What a reset draws: RateControlEnv.reset with FlightEnvelopeSampler.sample and _generate_new_command.
+template <typename T> struct ResetDraw {
+    T s[12], d[4], rate_cmd[3], sched[7];
+};
+
+// Draw plan (Philox block b of counter (id_lo, id_hi, episode, b)):
 //   b0 airspeed U(15,30), altitude U(50,200) | b1 roll, pitch U(+-15 deg) | b2 yaw U(0,2pi), p U(+-0.1)
 //   b3 q, r U(+-0.1) | b4 w0 -> #axes, w1 -> permutation, w2 bits -> signs | b5 mag0, mag1 | b6 mag2, sine f
 // All sampling arithmetic is double in both builds (a reset is rare), then narrowed to T.
-template <typename T> __device__ __noinline__ void env_reset_one(const EnvConst<T>& E, int64_t local_i, EnvRegs<T>& e) {
+// Not inlined: it is the cold path of the step kernel, and keeping it out of line keeps its registers
+// (Philox rounds, double arithmetic) out of the hot loop's allocation.
+template <typename T>
+__device__ __noinline__ void env_reset_draw(uint64_t seed, uint64_t global_id, uint32_t episode_idx, float difficulty,
+                                            uint8_t command_type, ResetDraw<T>* out) {
     const double PI = 3.141592653589793;
-    e.episode_idx += 1;
-    const Philox g(E.seed, (uint64_t)(E.id_offset + local_i), e.episode_idx);
+    const Philox g(seed, global_id, episode_idx);
     uint32_t w[4];
     const double att_lo = -15.0 * (PI / 180.0), att_hi = 15.0 * (PI / 180.0);
     g.block(0, w);
@@ -67,15 +74,20 @@ template <typename T> __device__ __noinline__ void env_reset_one(const EnvConst<
     const double q = uniform_lh(-0.1, 0.1, u53(w[0], w[1]));
     const double r = uniform_lh(-0.1, 0.1, u53(w[2], w[3]));
 
-    e.s[0] = T(0); e.s[1] = T(0); e.s[2] = (T)(-altitude);
-    e.s[3] = (T)airspeed; e.s[4] = T(0); e.s[5] = T(0);
-    e.s[6] = (T)roll; e.s[7] = (T)pitch; e.s[8] = (T)yaw;
-    e.s[9] = (T)p; e.s[10] = (T)q; e.s[11] = (T)r;
-    e.time = T(0);
-    derived_outputs(e.s, e.d);
+    T s[12];
+    s[0] = T(0); s[1] = T(0); s[2] = (T)(-altitude);
+    s[3] = (T)airspeed; s[4] = T(0); s[5] = T(0);
+    s[6] = (T)roll; s[7] = (T)pitch; s[8] = (T)yaw;
+    s[9] = (T)p; s[10] = (T)q; s[11] = (T)r;
+    T d[4];
+    derived_outputs(s, d);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) out->s[k] = s[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) out->d[k] = d[k];
 
     const double max_rates[3] = {180.0 * (PI / 180.0), 180.0 * (PI / 180.0), 160.0 * (PI / 180.0)};
-    const double scale = (double)e.difficulty;
+    const double scale = (double)difficulty;
     uint32_t sel[4];
     g.block(4, sel);
     double mag[3];
@@ -85,11 +97,11 @@ template <typename T> __device__ __noinline__ void env_reset_one(const EnvConst<
     mag[2] = u53(w[0], w[1]);
     const double ufreq = u53(w[2], w[3]);
     const int perm = (int)__umulhi(sel[1], 6u);
+    T sched[7], rate_cmd[3] = {T(0), T(0), T(0)};
 #pragma unroll
-    for (int f = 0; f < 7; ++f) e.sched[f] = T(0);
+    for (int f = 0; f < 7; ++f) sched[f] = T(0);
     double cmd[3] = {0.0, 0.0, 0.0};
-    e.rate_cmd[0] = e.rate_cmd[1] = e.rate_cmd[2] = T(0);
-    if (e.command_type == ACB200_CMD_STEP || e.command_type == ACB200_CMD_RAMP) {
+    if (command_type == ACB200_CMD_STEP || command_type == ACB200_CMD_RAMP) {
         const int n_axes = 1 + (int)__umulhi(sel[0], 3u);
         for (int k = 0; k < n_axes; ++k) {
             const int axis = kPerm3[perm][k];
@@ -97,21 +109,41 @@ template <typename T> __device__ __noinline__ void env_reset_one(const EnvConst<
             const double sign = ((sel[2] >> k) & 1u) ? 1.0 : -1.0;
             cmd[axis] = __dmul_rn(__dmul_rn(sign, magnitude), max_rates[axis]);
         }
-        if (e.command_type == ACB200_CMD_STEP) {
-            for (int a = 0; a < 3; ++a) e.rate_cmd[a] = (T)cmd[a];
+        if (command_type == ACB200_CMD_STEP) {
+            for (int a = 0; a < 3; ++a) rate_cmd[a] = (T)cmd[a];
         } else {
-            for (int a = 0; a < 3; ++a) e.sched[a] = (T)cmd[a];
+            for (int a = 0; a < 3; ++a) sched[a] = (T)cmd[a];
         }
-    } else if (e.command_type == ACB200_CMD_SINE) {
+    } else if (command_type == ACB200_CMD_SINE) {
         const int n_axes = 1 + (int)__umulhi(sel[0], 2u);
         for (int k = 0; k < n_axes; ++k) {
             const int axis = kPerm3[perm][k];
             const double amp = __dmul_rn(__dmul_rn(uniform_lh(0.3, 1.0, mag[k]), 0.5), scale);
             cmd[axis] = __dmul_rn(amp, max_rates[axis]);
         }
-        for (int a = 0; a < 3; ++a) e.sched[a] = (T)cmd[a];
-        e.sched[3] = (T)uniform_lh(0.1, 2.0, ufreq);
+        for (int a = 0; a < 3; ++a) sched[a] = (T)cmd[a];
+        sched[3] = (T)uniform_lh(0.1, 2.0, ufreq);
     }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) out->rate_cmd[a] = rate_cmd[a];
+#pragma unroll
+    for (int f = 0; f < 7; ++f) out->sched[f] = sched[f];
+}
+
+// RateControlEnv.reset (rate_env.py:151-210): a fresh episode for one aircraft.
+template <typename T> __device__ __forceinline__ void env_reset_one(const EnvConst<T>& E, int64_t local_i, EnvRegs<T>& e) {
+    e.episode_idx += 1;
+    ResetDraw<T> dr;
+    env_reset_draw<T>(E.seed, (uint64_t)(E.id_offset + local_i), e.episode_idx, e.difficulty, e.command_type, &dr);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) e.s[k] = dr.s[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) e.d[k] = dr.d[k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) e.rate_cmd[k] = dr.rate_cmd[k];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) e.sched[k] = dr.sched[k];
+    e.time = T(0);
     e.env_time = T(0);
     e.step_count = 0;
     e.prev_action[0] = 0.0f; e.prev_action[1] = 0.0f; e.prev_action[2] = 0.0f; e.prev_action[3] = 0.5f;
@@ -164,28 +196,27 @@ template <typename T> __device__ __forceinline__ void env_update_command(const E
     }
 }
 
-// RateControlEnv.step (rate_env.py:212-300) with the selected controller in front of it.
-// act_in = the caller's action (EXTERNAL) or residual (RESIDUAL), env order aileron, elevator, rudder, throttle.
-// comp[8] = tracking, smoothness, stability, oscillation, survival, settle_bonus, crash_penalty, residual_bonus.
-// obs receives the post-step observation (the terminal one if the episode ended).
+// Who drives the action of RateControlEnv.step (rate_env.py:212-233): the caller (EXTERNAL), the PID
+// compositions the reference itself uses (pid_demonstrations.py:55-78: RATE_PID; AttitudeAgent in front:
+// ATTITUDE_PID) or PID + residual (residual_rate_env.py:112-155).
+// act_in = the caller's action / residual, env order aileron, elevator, rudder, throttle.
+// Returns the clipped float32 action in act and the surfaces the simulator holds in c.
 template <typename T>
-__device__ __forceinline__ void env_step_one(const DynParams<T>& P, const CtrlParams<T>& C, const EnvConst<T>& E, EnvRegs<T>& e,
-                                             const float (&act_in)[4], const T (&att_cmd)[4], T (&comp)[8], T& reward_out,
-                                             bool& terminated_out, bool& truncated_out, int& repaired, int64_t local_i) {
-    using M = Math<T>;
-    float act[4];
-    T residual_bonus = T(0);
+__device__ __forceinline__ void env_action(const CtrlParams<T>& C, const EnvConst<T>& E, const T (&s)[12], PidMem (&rate)[3],
+                                           PidMem (&ang)[3], const T (&rate_cmd)[3], const T (&att_cmd)[4],
+                                           const float (&act_in)[4], float (&act)[4], T (&c)[4], T& residual_bonus) {
+    residual_bonus = T(0);
     if (E.controller == ACB200_CTRL_EXTERNAL) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) act[k] = act_in[k];
     } else if (E.controller == ACB200_CTRL_ATTITUDE_PID) {
         T surf[4];
-        attitude_agent(C, e.ang, e.rate, att_cmd[0], att_cmd[1], att_cmd[2], att_cmd[3], e.s, E.dt_f32, surf);
+        attitude_agent(C, ang, rate, att_cmd[0], att_cmd[1], att_cmd[2], att_cmd[3], s, E.dt_f32, surf);
         act[0] = (float)surf[1]; act[1] = (float)surf[0]; act[2] = (float)surf[2]; act[3] = (float)surf[3];
     } else {
         // pid_demonstrations.py:55-78 / residual_rate_env.py:112-135
         T surf[4];
-        rate_agent(C, e.rate, e.rate_cmd[0], e.rate_cmd[1], e.rate_cmd[2], E.pid_throttle, e.s[9], e.s[10], e.s[11], E.dt_f32, surf);
+        rate_agent(C, rate, rate_cmd[0], rate_cmd[1], rate_cmd[2], E.pid_throttle, s[9], s[10], s[11], E.dt_f32, surf);
         act[0] = (float)surf[1]; act[1] = (float)surf[0]; act[2] = (float)surf[2]; act[3] = (float)surf[3];
         if (E.controller == ACB200_CTRL_RESIDUAL) {
             // residual_rate_env.py:138-155, float32 arithmetic (individually rounded, as numpy does it)
@@ -203,12 +234,19 @@ __device__ __forceinline__ void env_step_one(const DynParams<T>& P, const CtrlPa
 #pragma unroll
     for (int k = 0; k < 3; ++k) act[k] = np_clip(act[k], -1.0f, 1.0f);
     act[3] = np_clip(act[3], 0.0f, 1.0f);
-    // :228-237
+    // :228-233 and set_controls (simplified_6dof.py:221-226)
     const T cin[4] = {(T)act[1], (T)act[0], (T)act[2], (T)act[3]};
-    T c[4];
     clip_controls(cin, c);
-    repaired += backend_step(P, e.s, e.time, c, E.K, E.h);
-    derived_outputs(e.s, e.d);
+}
+
+// The rest of RateControlEnv.step after sim.step (rate_env.py:241-300): time, command update, reward,
+// settle bonus, termination.  e.s / e.d hold the post-step state and derived outputs.
+// comp[8] = tracking, smoothness, stability, oscillation, survival, settle_bonus, crash_penalty, residual_bonus.
+template <typename T>
+__device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<T>& e, const float (&act)[4], T residual_bonus,
+                                                  T (&comp)[8], T& reward_out, bool& terminated_out, bool& truncated_out,
+                                                  int64_t local_i) {
+    using M = Math<T>;
     // :241-245
     e.step_count += 1;
     if (M::kParity) e.env_time += E.dt;

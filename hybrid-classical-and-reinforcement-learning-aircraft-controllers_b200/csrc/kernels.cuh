@@ -234,6 +234,9 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvPtrs<T> B, const _
 }
 
 // ---- K-C: controller + RateControlEnv.step + reward + termination + in-kernel auto-reset -----------
+// Loads are staged so that only what the substep loop needs is live across it: (A) state + PID memory
+// -> controller -> PID memory stored back; (B) K RK4 substeps on 12 states + held controls; (C) the
+// env's bookkeeping words are loaded only now -> reward / termination / (cold) Philox reset -> scatter.
 template <typename T>
 __global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant__ DynParams<T> P,
                                                           const __grid_constant__ CtrlParams<T> C,
@@ -253,21 +256,56 @@ __global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant_
 
     if (valid) {
         EnvRegs<T> e;
-        env_gather(B, i, e);
-        float act[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        // (A) controller
+#pragma unroll
+        for (int k = 0; k < 12; ++k) e.s[k] = ldf(B.f.state, k, n, i);
+        e.time = ldf(B.f.state, 12, n, i);
+        float act_in[4] = {0.0f, 0.0f, 0.0f, 0.0f}, act[4];
         if (action) {
             const float4 a4 = reinterpret_cast<const float4*>(action)[i];
-            act[0] = a4.x; act[1] = a4.y; act[2] = a4.z; act[3] = a4.w;
+            act_in[0] = a4.x; act_in[1] = a4.y; act_in[2] = a4.z; act_in[3] = a4.w;
         }
-        T att[4] = {T(0), T(0), T(0), T(0)};
-        if (E.controller == ACB200_CTRL_ATTITUDE_PID) {
+        T c[4], residual_bonus;
+        {
+            T att[4] = {T(0), T(0), T(0), T(0)}, rcmd[3] = {T(0), T(0), T(0)};
+            PidMem rate[3], ang[3];
+            if (E.controller != ACB200_CTRL_EXTERNAL) load_pid(B.f.pid, n, i, 0, rate);
+            if (E.controller == ACB200_CTRL_ATTITUDE_PID) {
+                load_pid(B.f.pid, n, i, 1, ang);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) att[k] = ldf(B.att_cmd, k, n, i);
+                for (int k = 0; k < 4; ++k) att[k] = ldf(B.att_cmd, k, n, i);
+            } else if (E.controller != ACB200_CTRL_EXTERNAL) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) rcmd[k] = ldf(B.rate_cmd, k, n, i);
+            }
+            env_action(C, E, e.s, rate, ang, rcmd, att, act_in, act, c, residual_bonus);
+            if (E.controller != ACB200_CTRL_EXTERNAL) store_pid(B.f.pid, n, i, 0, rate);
+            if (E.controller == ACB200_CTRL_ATTITUDE_PID) store_pid(B.f.pid, n, i, 1, ang);
         }
+        // (B) physics: rate_env.py:234-237
+        const int repaired = backend_step(P, e.s, e.time, c, E.K, E.h);
+        derived_outputs(e.s, e.d);
+        // (C) the env's own memory
+#pragma unroll
+        for (int k = 0; k < 3; ++k) e.rate_cmd[k] = ldf(B.rate_cmd, k, n, i);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) e.prev_action[k] = ldf(B.prev_action, k, n, i);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { e.prev_err[k] = ldf(B.rew_mem, k, n, i); e.sign_changes[k] = ldf(B.rew_mem, 3 + k, n, i); }
+        e.settle_timer = ldf(B.rew_mem, 6, n, i);
+#pragma unroll
+        for (int k = 0; k < 7; ++k) e.sched[k] = ldf(B.sched, k, n, i);
+        e.env_time = B.env_time[i];
+        e.step_count = B.step_count[i];
+        e.episode_idx = B.episode_idx[i];
+        e.is_settled = B.is_settled[i];
+        e.command_type = B.command_type[i];
+        e.difficulty = B.difficulty[i];
+        e.ep_return = B.ep_return[i];
+
         T comp[8], reward;
         bool terminated, truncated;
-        int repaired = 0;
-        env_step_one(P, C, E, e, act, att, comp, reward, terminated, truncated, repaired, i);
+        env_after_physics(E, e, act, residual_bonus, comp, reward, terminated, truncated, i);
         env_observe(e, o);
 
         B.reward[i] = reward;
@@ -294,9 +332,38 @@ __global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant_
                 }
                 env_reset_one(E, i, e);
                 env_observe(e, o);
+#pragma unroll
+                for (int k = 0; k < ACB200_PID_FIELDS; ++k) stf(B.f.pid, k, n, i, 0.0f);   // agent.reset()
+#pragma unroll
+                for (int k = 0; k < 4; ++k) c[k] = T(0);
             }
         }
-        env_scatter(B, i, e);
+        // scatter
+#pragma unroll
+        for (int k = 0; k < 12; ++k) stf(B.f.state, k, n, i, e.s[k]);
+        stf(B.f.state, 12, n, i, e.time);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(B.f.derived, k, n, i, e.d[k]);
+        if (B.f.controls) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) stf(B.f.controls, k, n, i, c[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) stf(B.rate_cmd, k, n, i, e.rate_cmd[k]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(B.prev_action, k, n, i, e.prev_action[k]);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { stf(B.rew_mem, k, n, i, e.prev_err[k]); stf(B.rew_mem, 3 + k, n, i, e.sign_changes[k]); }
+        stf(B.rew_mem, 6, n, i, e.settle_timer);
+        if (e.step_count == 0) {   // the schedule only changes at a reset
+#pragma unroll
+            for (int k = 0; k < 7; ++k) stf(B.sched, k, n, i, e.sched[k]);
+        }
+        B.env_time[i] = e.env_time;
+        B.step_count[i] = e.step_count;
+        B.episode_idx[i] = e.episode_idx;
+        B.is_settled[i] = e.is_settled;
+        B.ep_return[i] = e.ep_return;
     }
     store_obs_block(B.obs, n, o, valid, stage);
 

@@ -2,6 +2,8 @@
 // type of the build and passed to the kernels as __grid_constant__ arguments (constant bank).
 #pragma once
 #include "../../include/acb200.h"
+#include <math.h>
+
 #include "math.cuh"
 
 namespace acb {
@@ -22,6 +24,15 @@ template <typename T> struct DynParams {
     T max_velocity, max_rate_rad, max_pitch_rad, max_alpha_rad;
     T max_acceleration, max_angular_acceleration;
     T ixx, iyy, izz, izz_m_iyy, ixx_m_izz, iyy_m_ixx;
+    // ---- products and reciprocals folded on the host in double, used by the throughput build only
+    // (physics_f32.cuh); the parity build keeps the reference's operation order and ignores them ----
+    T weight;                                    // mass * g
+    T half_rho_S;                                // 0.5 rho S
+    T cl_elev_rad, cm_elev_rad, cy_rud_rad, cn_rud_rad, cl_ail_rad;   // coefficient * max deflection [rad]
+    T damp_p, damp_q, damp_r;                    // damping * (b or c) / 2
+    T inv_vt0, inv_min_airspeed;
+    T tan_max_alpha, sin_max_pitch, cos_max_pitch;
+    T inv_ixx, inv_iyy, inv_izz;
 };
 
 template <typename T> struct PidCfg3 { acb200_pid_config axis[3]; };
@@ -55,6 +66,22 @@ template <typename T> static inline DynParams<T> make_dyn_params(const acb200_ai
     d.ixx = (T)a.inertia_xx; d.iyy = (T)a.inertia_yy; d.izz = (T)a.inertia_zz;
     d.izz_m_iyy = (T)(a.inertia_zz - a.inertia_yy); d.ixx_m_izz = (T)(a.inertia_xx - a.inertia_zz);
     d.iyy_m_ixx = (T)(a.inertia_yy - a.inertia_xx);
+    d.weight = (T)(a.mass * a.gravity);
+    d.half_rho_S = (T)(0.5 * a.air_density * a.wing_area);
+    d.cl_elev_rad = (T)(a.cl_elevator * host_radians(a.max_elevator_deflection));
+    d.cm_elev_rad = (T)(a.cm_elevator * host_radians(a.max_elevator_deflection));
+    d.cy_rud_rad = (T)(a.cy_rudder * host_radians(a.max_rudder_deflection));
+    d.cn_rud_rad = (T)(a.cn_rudder * host_radians(a.max_rudder_deflection));
+    d.cl_ail_rad = (T)(a.cl_aileron * host_radians(a.max_aileron_deflection));
+    d.damp_p = (T)(a.damping_roll * a.wing_span * 0.5);
+    d.damp_q = (T)(a.damping_pitch * a.chord * 0.5);
+    d.damp_r = (T)(a.damping_yaw * a.wing_span * 0.5);
+    d.inv_vt0 = (T)(1.0 / a.thrust_zero_velocity);
+    d.inv_min_airspeed = (T)(1.0 / a.min_airspeed_aero);
+    d.tan_max_alpha = (T)tan(host_radians(a.max_alpha));
+    d.sin_max_pitch = (T)sin(host_radians(a.max_pitch_angle));
+    d.cos_max_pitch = (T)cos(host_radians(a.max_pitch_angle));
+    d.inv_ixx = (T)(1.0 / a.inertia_xx); d.inv_iyy = (T)(1.0 / a.inertia_yy); d.inv_izz = (T)(1.0 / a.inertia_zz);
     return d;
 }
 

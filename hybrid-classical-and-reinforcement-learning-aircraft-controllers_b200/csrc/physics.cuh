@@ -207,3 +207,5 @@ __device__ __forceinline__ int backend_step(const DynParams<T>& P, T (&s)[12], T
 }
 
 }  // namespace acb
+
+#include "physics_f32.cuh"   // the throughput build's backend_step(float) overload

@@ -1,0 +1,221 @@
+// physics_f32.cuh -- THROUGHPUT build of one aircraft's 6-DOF substep (float), written for the
+// Blackwell SM's issue budget rather than for the reference's operation order.
+//
+// Same model as physics.cuh (Simplified6DOF._dynamics / step, simulation/simplified_6dof.py:228-293,
+// 333-503), restructured so that one derivative evaluation costs ~190 issue slots instead of ~580:
+//   * everything that depends only on the held controls (zero-order hold over the K substeps,
+//     simulation_backend.py:95-99) or only on parameters is folded once per control step / on the host;
+//   * no IEEE division or square root in the loop: MUFU.RCP / MUFU.RSQ (<= 1 ulp) times a multiply;
+//     divisions by mass / inertia / V_T0 / min airspeed are multiplications by host-side reciprocals;
+//   * alpha = clip(atan2(w, u_safe)) needs atan only on |t| <= tan(max_alpha): one odd polynomial, no
+//     octant logic; sin/cos(alpha) = (t, 1) / sqrt(1 + t^2);
+//   * clamps are FMNMX pairs (fminf/fmaxf), not compare+select chains;
+//   * the per-derivative NaN scrub of the reference (:496-501) is dropped: with finite state and
+//     controls every derivative is finite by construction (V_safe >= 10, |u_safe| >= 0.1,
+//     cos(theta_safe) >= cos 85 deg, clamped accelerations); the per-substep state scrub (:286-291)
+//     stays, as ONE fused test with a cold repair path.
+// The arithmetic differs from the fp64 oracle by float rounding only; tolerances are stated and
+// tested in tests/test_gpu_parity_f32.py (per step <= 5e-6, trajectories within 6x of the oracle's own
+// one-float-ulp sensitivity).
+#pragma once
+#include "math.cuh"
+#include "params.cuh"
+
+namespace acb {
+
+#ifndef ACB_F32_MUFU_TRIG
+#define ACB_F32_MUFU_TRIG 0      // 1: sin.approx/cos.approx (MUFU, abs err ~5e-7) instead of the polynomial pair
+#endif
+
+struct FastF32 {
+    static __device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ float rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ void sincos(float x, float* s, float* c) {
+#if ACB_F32_MUFU_TRIG
+        asm("sin.approx.ftz.f32 %0, %1;" : "=f"(*s) : "f"(x));
+        asm("cos.approx.ftz.f32 %0, %1;" : "=f"(*c) : "f"(x));
+#else
+        F32::sincos(x, s, c);
+#endif
+    }
+    static __device__ __forceinline__ float clamp(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+};
+
+// What the K substeps of one control step share: the held controls folded into the coefficients
+// they multiply (simplified_6dof.py:383-390, 402-404, 415-435).
+struct HeldControlsF32 {
+    float cl_c;        // cl_0 + cl_elevator * elevator_rad
+    float cy;          // cy_rudder * rudder_rad
+    float l_c, m_c, n_c;   // cl_aileron * aileron_rad, cm_elevator * elevator_rad, cn_rudder * rudder_rad
+    float thrust_max;  // max_thrust * throttle
+};
+
+__device__ __forceinline__ HeldControlsF32 hold_controls(const DynParams<float>& P, const float (&c)[4]) {
+    HeldControlsF32 H;
+    H.cl_c = fmaf(P.cl_elev_rad, c[0], P.cl_0);
+    H.m_c = P.cm_elev_rad * c[0];
+    H.l_c = P.cl_ail_rad * c[1];
+    H.cy = P.cy_rud_rad * c[2];
+    H.n_c = P.cn_rud_rad * c[2];
+    H.thrust_max = P.max_thrust * c[3];
+    return H;
+}
+
+// _dynamics for a stage state t[12] whose attitude sines/cosines are already known.
+__device__ __forceinline__ void dynamics_f32(const DynParams<float>& P, const HeldControlsF32& H, const float (&t)[12],
+                                             float sphi, float cphi, float sth, float cth, float spsi, float cpsi,
+                                             float (&k)[12]) {
+    const float u = t[3], v = t[4], w = t[5], theta = t[7], p = t[9], q = t[10], r = t[11];
+
+    // airspeed, 1/V_safe (:363-364): V = V2 * rsqrt(V2); 1/max(V, Vmin) = min(1/V, 1/Vmin)
+    const float V2 = fmaf(w, w, fmaf(v, v, u * u));
+    const float rV = FastF32::rsqrt(fmaxf(V2, 1e-20f));
+    const float V = V2 * rV;
+    const float inv_Vs = fminf(rV, P.inv_min_airspeed);
+
+    // u_safe and alpha (:367-373).  u_safe < 0 puts atan2 beyond +-90 deg, i.e. on the clip, with the sign of w.
+    const float au = fabsf(u);
+    const float us = (au > 1e-6f) ? copysignf(fmaxf(au, P.min_u_velocity), u) : P.min_u_velocity;
+    float tcl = FastF32::clamp(w * FastF32::rcp(us), -P.tan_max_alpha, P.tan_max_alpha);
+    tcl = (us < 0.0f) ? copysignf(P.tan_max_alpha, w) : tcl;
+    const float alpha = F32::atan_unit(tcl);                 // odd polynomial, valid on [-1, 1]
+    const float cos_alpha = FastF32::rsqrt(fmaf(tcl, tcl, 1.0f));
+    const float sin_alpha = tcl * cos_alpha;
+
+    // sideslip (:376) and dynamic pressure * S (:379, 392)
+    const float beta = F32::asin(FastF32::clamp(v * inv_Vs, -1.0f, 1.0f));
+    const float qS = P.half_rho_S * V2;
+
+    // aerodynamic forces (:383-399)
+    const float cl = fmaf(P.cl_alpha, alpha, H.cl_c);
+    const float cd = fmaf(P.cd_alpha2, alpha * alpha, P.cd_0);
+    const float lift = qS * cl, drag = qS * cd;
+    const float fx_aero = fmaf(lift, sin_alpha, -drag * cos_alpha);
+    const float fz_aero = -fmaf(drag, sin_alpha, lift * cos_alpha);
+    // thrust (:402-404), gravity (:407-411)
+    const float thrust = H.thrust_max * fmaxf(0.0f, fmaf(-V, P.inv_vt0, 1.0f));
+    const float wcth = P.weight * cth;
+    const float fx = fmaf(-P.weight, sth, fx_aero + thrust);
+    const float fy = fmaf(wcth, sphi, qS * H.cy);
+    const float fz = fmaf(wcth, cphi, fz_aero);
+
+    // moments (:415-435)
+    const float qSb = qS * P.wing_span, qSc = qS * P.chord;
+    const float l_m = qSb * fmaf(P.cl_beta, beta, fmaf(P.damp_p * p, inv_Vs, H.l_c));
+    const float m_m = qSc * fmaf(P.damp_q * q, inv_Vs, fmaf(P.cm_alpha, alpha, H.m_c));
+    const float n_m = qSb * fmaf(P.cn_beta, beta, fmaf(P.damp_r * r, inv_Vs, H.n_c));
+
+    // position kinematics (:440-452)
+    const float sps = sphi * sth, cps = cphi * sth;
+    k[0] = fmaf(fmaf(cps, cpsi, sphi * spsi), w, fmaf(fmaf(sps, cpsi, -cphi * spsi), v, cth * cpsi * u));
+    k[1] = fmaf(fmaf(cps, spsi, -sphi * cpsi), w, fmaf(fmaf(sps, spsi, cphi * cpsi), v, cth * spsi * u));
+    k[2] = fmaf(cphi * cth, w, fmaf(sphi * cth, v, -sth * u));
+
+    // translational dynamics (:455-460) with the acceleration clamp (:488-490)
+    k[3] = FastF32::clamp(fmaf(r, v, fmaf(-q, w, fx * P.inv_mass)), -P.max_acceleration, P.max_acceleration);
+    k[4] = FastF32::clamp(fmaf(p, w, fmaf(-r, u, fy * P.inv_mass)), -P.max_acceleration, P.max_acceleration);
+    k[5] = FastF32::clamp(fmaf(q, u, fmaf(-p, v, fz * P.inv_mass)), -P.max_acceleration, P.max_acceleration);
+
+    // Euler-angle kinematics with the pitch clipped to +-max_pitch for tan/cos only (:463-471)
+    const bool clipped = fabsf(theta) > P.max_pitch_rad;
+    const float sth_s = clipped ? copysignf(P.sin_max_pitch, theta) : sth;
+    const float cth_s = clipped ? P.cos_max_pitch : cth;
+    const float rc = FastF32::rcp(cth_s);
+    const float yaw_num = fmaf(sphi, q, cphi * r);
+    k[6] = fmaf(sth_s * rc, yaw_num, p);
+    k[7] = fmaf(cphi, q, -sphi * r);
+    k[8] = yaw_num * rc;
+
+    // Euler's equations (:474-487)
+    k[9] = FastF32::clamp(fmaf(-P.izz_m_iyy * q, r, l_m) * P.inv_ixx, -P.max_angular_acceleration, P.max_angular_acceleration);
+    k[10] = FastF32::clamp(fmaf(-P.ixx_m_izz * p, r, m_m) * P.inv_iyy, -P.max_angular_acceleration, P.max_angular_acceleration);
+    k[11] = FastF32::clamp(fmaf(-P.iyy_m_ixx * p, q, n_m) * P.inv_izz, -P.max_angular_acceleration, P.max_angular_acceleration);
+}
+
+// Cold path of the per-substep scrub (:258, 286-291): position nan->0 / +-inf->+-1e4, the rest -> 0.
+static __device__ __noinline__ int repair_state_f32(float* s) {
+    int repaired = 0;
+    for (int i = 0; i < 12; ++i) {
+        const float x = s[i];
+        if (isfinite(x)) continue;
+        s[i] = (i < 3 && x == x) ? (x > 0.0f ? 10000.0f : -10000.0f) : 0.0f;
+        ++repaired;
+    }
+    return repaired;
+}
+
+// One RK4 substep (:248-254) and the post-step clamps (:258-291).
+__device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const HeldControlsF32& H, float (&s)[12], float& time,
+                                            float dt) {
+    float k[12], acc[12], t[12];
+    const float half_dt = 0.5f * dt;
+    float sphi, cphi, sth, cth, spsi, cpsi;
+    // stage 1 at the state itself
+    FastF32::sincos(s[6], &sphi, &cphi);
+    FastF32::sincos(s[7], &sth, &cth);
+    FastF32::sincos(s[8], &spsi, &cpsi);
+    dynamics_f32(P, H, s, sphi, cphi, sth, cth, spsi, cpsi, k);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) acc[i] = k[i];
+    // stages 2-4 at s + a k; weights 2, 2, 1.  Rolled: one more copy of the derivative code in the
+    // instruction stream, not three.
+#pragma unroll 1
+    for (int stage = 1; stage < 4; ++stage) {
+        const float a = (stage == 3) ? dt : half_dt;
+        const float wgt = (stage == 3) ? 1.0f : 2.0f;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) t[i] = fmaf(a, k[i], s[i]);
+        FastF32::sincos(t[6], &sphi, &cphi);
+        FastF32::sincos(t[7], &sth, &cth);
+        FastF32::sincos(t[8], &spsi, &cpsi);
+        dynamics_f32(P, H, t, sphi, cphi, sth, cth, spsi, cpsi, k);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) acc[i] = fmaf(wgt, k[i], acc[i]);
+    }
+    const float dt6 = dt * (1.0f / 6.0f);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) s[i] = fmaf(dt6, acc[i], s[i]);
+    time += dt;
+
+    // :262-273
+#pragma unroll
+    for (int i = 3; i < 6; ++i) s[i] = FastF32::clamp(s[i], -P.max_velocity, P.max_velocity);
+    s[6] = Math<float>::wrap_pi(s[6]);
+    s[7] = FastF32::clamp(s[7], -P.max_pitch_rad, P.max_pitch_rad);
+    s[8] = Math<float>::wrap_pi(s[8]);
+#pragma unroll
+    for (int i = 9; i < 12; ++i) s[i] = FastF32::clamp(s[i], -P.max_rate_rad, P.max_rate_rad);
+    // :276-283  ground: altitude = -z < 0
+    if (s[2] > 0.0f) {
+        s[2] = 0.0f;
+        s[5] = fmaxf(0.0f, s[5]);
+    }
+    // :258, 286-291 as one test: 0 * x is NaN for x = NaN or +-inf (fminf/fmaxf above turn a NaN into a bound,
+    // so test the unclamped positions and attitude; velocities and rates are finite after their clamps unless NaN
+    // went in, which the clamps map to a bound)
+    float chk = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) chk = fmaf(0.0f, s[i], chk);
+    int repaired = 0;
+    if (chk != 0.0f) {        // NaN compares unequal
+        float tmp[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) tmp[i] = s[i];
+        repaired = repair_state_f32(tmp);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) s[i] = tmp[i];
+    }
+    return repaired;
+}
+
+// SimulationAircraftBackend.step for the throughput build: K substeps of h under zero-order hold.
+__device__ __forceinline__ int backend_step(const DynParams<float>& P, float (&s)[12], float& time, const float (&c)[4], int K,
+                                            float h) {
+    const HeldControlsF32 H = hold_controls(P, c);
+    int repaired = 0;
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) repaired += rk4_step_f32(P, H, s, time, h);
+    return repaired;
+}
+
+}  // namespace acb
