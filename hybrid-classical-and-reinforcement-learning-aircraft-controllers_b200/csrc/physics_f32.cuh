@@ -24,21 +24,105 @@
 namespace acb {
 
 #ifndef ACB_F32_MUFU_TRIG
-#define ACB_F32_MUFU_TRIG 0      // 1: sin.approx/cos.approx (MUFU, abs err ~5e-7) instead of the polynomial pair
+#define ACB_F32_MUFU_TRIG 1      // 1: sin.approx/cos.approx (MUFU, abs err ~5e-7) for all three Euler angles; 0: polynomials for roll/pitch
 #endif
 
+// Trigonometry of the throughput build.  Default (ACB_F32_MUFU_TRIG=1): the SFU's sin.approx / cos.approx for all
+// three Euler angles, 4 issue slots per angle instead of ~27 for a Cody-Waite + polynomial sincos.  Its absolute
+// error (~5e-7 on |x| <= 2 pi) perturbs the gravity projection by 5e-6 m/s^2 -- one float ulp of the force sums it
+// is added to -- and the ground track by 1.5e-5 m/s; measured on B200 the per-step and trajectory error
+// quantiles of the three variants (library-grade polynomial everywhere / polynomial for roll+pitch / MUFU
+// everywhere) are identical to two digits up to the 99.99th percentile (profiles/r01_f32_trig_variants.md).
+// ACB_F32_MUFU_TRIG=0 keeps yaw on MUFU (it enters only the position kinematics, :440-452) and uses for
+//   pitch  (clamped to +-85 deg every substep, :268; a stage moves it by < 0.01 rad) one polynomial pair
+//          without range reduction;
+//   roll   (wrapped to [-pi, pi] every substep, :266) one fold about +-pi/2, then the same pair.
+// Polynomials: least-squares Chebyshev fits in x^2 on |x| <= 1.6, abs err <= 1.5e-7 (tools/fit_trig_f32.py).
 struct FastF32 {
     static __device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
     static __device__ __forceinline__ float rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-    static __device__ __forceinline__ void sincos(float x, float* s, float* c) {
-#if ACB_F32_MUFU_TRIG
+    static __device__ __forceinline__ float sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+    static __device__ __forceinline__ void sincos_mufu(float x, float* s, float* c) {
         asm("sin.approx.ftz.f32 %0, %1;" : "=f"(*s) : "f"(x));
         asm("cos.approx.ftz.f32 %0, %1;" : "=f"(*c) : "f"(x));
+    }
+    // |x| <= 1.6
+    static __device__ __forceinline__ void sincos_halfpi(float x, float* s, float* c) {
+        const float z = x * x;
+        float ps = fmaf(z, 2.630042899909313e-06f, -0.00019821259775198996f);
+        ps = fmaf(ps, z, 0.008333231322467327f);
+        ps = fmaf(ps, z, -0.1666666567325592f);
+        *s = fmaf(x * z, ps, x);
+        float pc = fmaf(z, -2.624827857289347e-07f, 2.4772412871243432e-05f);
+        pc = fmaf(pc, z, -0.0013888622634112835f);
+        pc = fmaf(pc, z, 0.041666656732559204f);
+        pc = fmaf(pc, z, -0.5f);
+        *c = fmaf(pc, z, 1.0f);
+    }
+    // |x| <= 3 pi / 2: sin(x) = sin(pi sign(x) - x), cos(x) = -cos(pi sign(x) - x) beyond +-pi/2
+    static __device__ __forceinline__ void sincos_pi(float x, float* s, float* c) {
+        const bool fold = fabsf(x) > 1.57079637050628662109375f;
+        const float xr = fold ? (copysignf(3.14159274101257324f, x) - x) + copysignf(-8.74227765734758577e-08f, x) : x;
+        float cc;
+        sincos_halfpi(xr, s, &cc);
+        *c = fold ? -cc : cc;
+    }
+    static __device__ __forceinline__ void sincos_pitch(float x, float* s, float* c) {
+#if ACB_F32_MUFU_TRIG
+        sincos_mufu(x, s, c);
 #else
-        F32::sincos(x, s, c);
+        sincos_halfpi(x, s, c);
+#endif
+    }
+    static __device__ __forceinline__ void sincos_roll(float x, float* s, float* c) {
+#if ACB_F32_MUFU_TRIG
+        sincos_mufu(x, s, c);
+#else
+        sincos_pi(x, s, c);
+#endif
+    }
+    static __device__ __forceinline__ void sincos_yaw(float x, float* s, float* c) { sincos_mufu(x, s, c); }
+    // roll, pitch, yaw of one (stage) state.  The guards only fire for states the physics itself never produces
+    // (a caller-injected attitude far outside the wrapped/clamped ranges, or a substep so long that a stage overshoots).
+    static __device__ __forceinline__ void attitude_trig(float phi, float theta, float psi, float* sphi, float* cphi, float* sth,
+                                                         float* cth, float* spsi, float* cpsi) {
+#if ACB_F32_MUFU_TRIG
+        if (fmaxf(fmaxf(fabsf(phi), fabsf(theta)), fabsf(psi)) > 12.0f) {
+            F32::sincos(phi, sphi, cphi);
+            F32::sincos(theta, sth, cth);
+            F32::sincos(psi, spsi, cpsi);
+        } else {
+            sincos_mufu(phi, sphi, cphi);
+            sincos_mufu(theta, sth, cth);
+            sincos_mufu(psi, spsi, cpsi);
+        }
+#else
+        if (fabsf(theta) > 1.6f || fabsf(phi) > 4.7f) {
+            F32::sincos(phi, sphi, cphi);
+            F32::sincos(theta, sth, cth);
+        } else {
+            sincos_roll(phi, sphi, cphi);
+            sincos_pitch(theta, sth, cth);
+        }
+        if (fabsf(psi) > 12.0f) F32::sincos(psi, spsi, cpsi);
+        else sincos_yaw(psi, spsi, cpsi);
 #endif
     }
     static __device__ __forceinline__ float clamp(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+    // asin with the common case (|x| <= 0.5, i.e. sideslip below 30 deg) as straight-line code
+    static __device__ __forceinline__ float asin(float x) {
+        const float ax = fabsf(x);
+        float z = x * x, t = x;
+        const bool big = ax > 0.5f;
+        if (big) { z = fmaf(ax, -0.5f, 0.5f); t = sqrt(z); }
+        float p = fmaf(z, 4.2163199048e-2f, 2.4181311049e-2f);
+        p = fmaf(p, z, 4.5470025998e-2f);
+        p = fmaf(p, z, 7.4953002686e-2f);
+        p = fmaf(p, z, 1.6666752422e-1f);
+        float r = fmaf(p * z, t, t);
+        if (big) r = copysignf(fmaf(r, -2.0f, 1.57079637050628662109375f), x);
+        return r;
+    }
 };
 
 // What the K substeps of one control step share: the held controls folded into the coefficients
@@ -83,7 +167,7 @@ __device__ __forceinline__ void dynamics_f32(const DynParams<float>& P, const He
     const float sin_alpha = tcl * cos_alpha;
 
     // sideslip (:376) and dynamic pressure * S (:379, 392)
-    const float beta = F32::asin(FastF32::clamp(v * inv_Vs, -1.0f, 1.0f));
+    const float beta = FastF32::asin(FastF32::clamp(v * inv_Vs, -1.0f, 1.0f));
     const float qS = P.half_rho_S * V2;
 
     // aerodynamic forces (:383-399)
@@ -151,9 +235,7 @@ __device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const Hel
     const float half_dt = 0.5f * dt;
     float sphi, cphi, sth, cth, spsi, cpsi;
     // stage 1 at the state itself
-    FastF32::sincos(s[6], &sphi, &cphi);
-    FastF32::sincos(s[7], &sth, &cth);
-    FastF32::sincos(s[8], &spsi, &cpsi);
+    FastF32::attitude_trig(s[6], s[7], s[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
     dynamics_f32(P, H, s, sphi, cphi, sth, cth, spsi, cpsi, k);
 #pragma unroll
     for (int i = 0; i < 12; ++i) acc[i] = k[i];
@@ -165,9 +247,7 @@ __device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const Hel
         const float wgt = (stage == 3) ? 1.0f : 2.0f;
 #pragma unroll
         for (int i = 0; i < 12; ++i) t[i] = fmaf(a, k[i], s[i]);
-        FastF32::sincos(t[6], &sphi, &cphi);
-        FastF32::sincos(t[7], &sth, &cth);
-        FastF32::sincos(t[8], &spsi, &cpsi);
+        FastF32::attitude_trig(t[6], t[7], t[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
         dynamics_f32(P, H, t, sphi, cphi, sth, cth, spsi, cpsi, k);
 #pragma unroll
         for (int i = 0; i < 12; ++i) acc[i] = fmaf(wgt, k[i], acc[i]);

@@ -25,6 +25,7 @@ from helpers import in_envelope, rel_err_cols, sample_initial_states, surface_se
 
 pytestmark = pytest.mark.gpu
 PER_STEP_TOL = 5e-6        # measured worst 1.8e-6 (dt=0.02, 20 substeps); tools/f32_tolerance_probe.py
+DERIVED_TOL = 1e-5         # airspeed, altitude, ground speed (ground speed inherits the yaw error x V)
 HEADING_TOL = 2e-5         # heading is an angle in [-pi, pi]: absolute; measured worst 3.6e-6 (= 5.8e-7 relative yaw error x 2 pi)
 SHORT_STEPS = 10           # 10 env steps = 200 RK4 substeps
 SHORT_TRAJ_TOL = 2e-3      # every aircraft over SHORT_STEPS; measured worst 1.2e-4 (rate) / 6.5e-4 (attitude)
@@ -72,7 +73,7 @@ def test_per_step_tolerance_open_loop(mods, dt, dtp):
         dh = np.abs(np.angle(np.exp(1j * (gder[3] - rder[3]))))
         worst = max(worst, float(e[alive].max())); worst_d = max(worst_d, float(np.maximum(ed, dh)[alive].max()))
         assert (e[alive] <= PER_STEP_TOL).all(), f"step {t + 1}: {e[alive].max():.3e}"
-        assert (ed[alive] <= PER_STEP_TOL).all() and (dh[alive] <= HEADING_TOL).all(), f"derived, step {t + 1}"
+        assert (ed[alive] <= DERIVED_TOL).all() and (dh[alive] <= HEADING_TOL).all(), f"derived, step {t + 1}"
     print(f"fp32 per-step (dt={dt}, dt_physics={dtp}): worst state {worst:.3e}, derived {worst_d:.3e} (tol {PER_STEP_TOL})")
 
 

@@ -22,7 +22,7 @@ for dt, dtp in ((0.01, 0.01), (0.01, 0.001), (0.02, 0.001)):
     s0 = sample_initial_states(rng, n); ctrl = surface_sequence(rng, n, steps // hold)
     P = orc.default_aircraft_params()
     fleet = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dtp})
-    ref = s0.copy(); rder = np.zeros((4, n)); errs = []; field_worst = np.zeros(12)
+    ref = s0.copy(); rder = np.zeros((4, n)); errs = []; field_worst = np.zeros(12); der_worst = np.zeros(4)
     for t in range(steps):
         c = np.ascontiguousarray(ctrl[t // hold])
         start32 = ref.astype(np.float32)
@@ -35,7 +35,12 @@ for dt, dtp in ((0.01, 0.01), (0.01, 0.001), (0.02, 0.001)):
         ef = np.abs(got[:12] - ref[:12]) / np.maximum(np.abs(ref[:12]), 1.0)
         field_worst = np.maximum(field_worst, ef[:, alive].max(axis=1))
         errs.append(ef.max(axis=0)[alive])
-    out[f"per_step dt={dt} dtp={dtp}"] = {"q": quant(np.concatenate(errs)), "field_worst": field_worst.tolist()}
+        gder = fleet.derived.double().cpu().numpy()
+        ed = np.abs(gder[:3] - rder[:3]) / np.maximum(np.abs(rder[:3]), 1.0)
+        dh = np.abs(np.angle(np.exp(1j * (gder[3] - rder[3]))))
+        der_worst = np.maximum(der_worst, np.concatenate([ed[:, alive].max(axis=1), [dh[alive].max()]]))
+    out[f"per_step dt={dt} dtp={dtp}"] = {"q": quant(np.concatenate(errs)), "field_worst": field_worst.tolist(),
+                                          "derived_worst(airspeed,altitude,ground_speed,heading_abs)": der_worst.tolist()}
 
 # closed loop trajectories
 for controller in ("rate_pid", "attitude_pid"):
