@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libacb200.so")
+LIB_PATH = os.environ.get("ACB200_LIB") or os.path.join(_PKG, "libacb200.so")   # ACB200_LIB: A/B builds of the same ABI
 
 OK, EVALUE, ECUDA, ENULL, ENOSUP = 0, -1, -2, -3, -4
 LEVEL_WAYPOINT, LEVEL_HSA, LEVEL_ATTITUDE, LEVEL_RATE, LEVEL_SURFACE = 1, 2, 3, 4, 5

@@ -33,6 +33,8 @@ template <typename T> struct DynParams {
     T inv_vt0, inv_min_airspeed;
     T tan_max_alpha, sin_max_pitch, cos_max_pitch;
     T inv_ixx, inv_iyy, inv_izz;
+    T b_ixx, c_iyy, b_izz;                       // span / Ixx, chord / Iyy, span / Izz
+    T gyro_x, gyro_y, gyro_z;                    // (Izz-Iyy)/Ixx, (Ixx-Izz)/Iyy, (Iyy-Ixx)/Izz
 };
 
 template <typename T> struct PidCfg3 { acb200_pid_config axis[3]; };
@@ -82,6 +84,10 @@ template <typename T> static inline DynParams<T> make_dyn_params(const acb200_ai
     d.sin_max_pitch = (T)sin(host_radians(a.max_pitch_angle));
     d.cos_max_pitch = (T)cos(host_radians(a.max_pitch_angle));
     d.inv_ixx = (T)(1.0 / a.inertia_xx); d.inv_iyy = (T)(1.0 / a.inertia_yy); d.inv_izz = (T)(1.0 / a.inertia_zz);
+    d.b_ixx = (T)(a.wing_span / a.inertia_xx); d.c_iyy = (T)(a.chord / a.inertia_yy); d.b_izz = (T)(a.wing_span / a.inertia_zz);
+    d.gyro_x = (T)((a.inertia_zz - a.inertia_yy) / a.inertia_xx);
+    d.gyro_y = (T)((a.inertia_xx - a.inertia_zz) / a.inertia_yy);
+    d.gyro_z = (T)((a.inertia_yy - a.inertia_xx) / a.inertia_zz);
     return d;
 }
 

@@ -23,6 +23,9 @@
 
 namespace acb {
 
+#ifndef ACB_F32_UNROLL_STAGES
+#define ACB_F32_UNROLL_STAGES 0
+#endif
 #ifndef ACB_F32_MUFU_TRIG
 #define ACB_F32_MUFU_TRIG 1      // 1: sin.approx/cos.approx (MUFU, abs err ~5e-7) for all three Euler angles; 0: polynomials for roll/pitch
 #endif
@@ -131,7 +134,7 @@ struct HeldControlsF32 {
     float cl_c;        // cl_0 + cl_elevator * elevator_rad
     float cy;          // cy_rudder * rudder_rad
     float l_c, m_c, n_c;   // cl_aileron * aileron_rad, cm_elevator * elevator_rad, cn_rudder * rudder_rad
-    float thrust_max;  // max_thrust * throttle
+    float thrust_max_m;  // max_thrust * throttle / mass
 };
 
 __device__ __forceinline__ HeldControlsF32 hold_controls(const DynParams<float>& P, const float (&c)[4]) {
@@ -141,7 +144,7 @@ __device__ __forceinline__ HeldControlsF32 hold_controls(const DynParams<float>&
     H.l_c = P.cl_ail_rad * c[1];
     H.cy = P.cy_rud_rad * c[2];
     H.n_c = P.cn_rud_rad * c[2];
-    H.thrust_max = P.max_thrust * c[3];
+    H.thrust_max_m = (P.max_thrust * P.inv_mass) * c[3];
     return H;
 }
 
@@ -170,35 +173,33 @@ __device__ __forceinline__ void dynamics_f32(const DynParams<float>& P, const He
     const float beta = FastF32::asin(FastF32::clamp(v * inv_Vs, -1.0f, 1.0f));
     const float qS = P.half_rho_S * V2;
 
-    // aerodynamic forces (:383-399)
+    // aerodynamic + thrust + gravity accelerations (:383-411, 455-460); 1/m is folded into qS and thrust on the way in
+    const float qS_m = qS * P.inv_mass;
     const float cl = fmaf(P.cl_alpha, alpha, H.cl_c);
     const float cd = fmaf(P.cd_alpha2, alpha * alpha, P.cd_0);
-    const float lift = qS * cl, drag = qS * cd;
-    const float fx_aero = fmaf(lift, sin_alpha, -drag * cos_alpha);
-    const float fz_aero = -fmaf(drag, sin_alpha, lift * cos_alpha);
-    // thrust (:402-404), gravity (:407-411)
-    const float thrust = H.thrust_max * fmaxf(0.0f, fmaf(-V, P.inv_vt0, 1.0f));
-    const float wcth = P.weight * cth;
-    const float fx = fmaf(-P.weight, sth, fx_aero + thrust);
-    const float fy = fmaf(wcth, sphi, qS * H.cy);
-    const float fz = fmaf(wcth, cphi, fz_aero);
+    const float lift = qS_m * cl, drag = qS_m * cd;
+    const float thrust = H.thrust_max_m * fmaxf(0.0f, fmaf(-V, P.inv_vt0, 1.0f));
+    const float gcth = P.g * cth;
+    const float ax = fmaf(-P.g, sth, fmaf(lift, sin_alpha, fmaf(-drag, cos_alpha, thrust)));
+    const float ay = fmaf(gcth, sphi, qS_m * H.cy);
+    const float az = fmaf(gcth, cphi, -fmaf(drag, sin_alpha, lift * cos_alpha));
 
-    // moments (:415-435)
-    const float qSb = qS * P.wing_span, qSc = qS * P.chord;
-    const float l_m = qSb * fmaf(P.cl_beta, beta, fmaf(P.damp_p * p, inv_Vs, H.l_c));
-    const float m_m = qSc * fmaf(P.damp_q * q, inv_Vs, fmaf(P.cm_alpha, alpha, H.m_c));
-    const float n_m = qSb * fmaf(P.cn_beta, beta, fmaf(P.damp_r * r, inv_Vs, H.n_c));
+    // moments / inertia (:415-435, 474-482); 1/I is folded into the span/chord factors
+    const float l_a = (qS * P.b_ixx) * fmaf(P.cl_beta, beta, fmaf(P.damp_p * p, inv_Vs, H.l_c));
+    const float m_a = (qS * P.c_iyy) * fmaf(P.damp_q * q, inv_Vs, fmaf(P.cm_alpha, alpha, H.m_c));
+    const float n_a = (qS * P.b_izz) * fmaf(P.cn_beta, beta, fmaf(P.damp_r * r, inv_Vs, H.n_c));
 
-    // position kinematics (:440-452)
-    const float sps = sphi * sth, cps = cphi * sth;
-    k[0] = fmaf(fmaf(cps, cpsi, sphi * spsi), w, fmaf(fmaf(sps, cpsi, -cphi * spsi), v, cth * cpsi * u));
-    k[1] = fmaf(fmaf(cps, spsi, -sphi * cpsi), w, fmaf(fmaf(sps, spsi, cphi * cpsi), v, cth * spsi * u));
-    k[2] = fmaf(cphi * cth, w, fmaf(sphi * cth, v, -sth * u));
+    // position kinematics (:440-452) as three plane rotations, R = Rz(psi) Ry(theta) Rx(phi)
+    const float y1 = fmaf(cphi, v, -sphi * w), z1 = fmaf(sphi, v, cphi * w);
+    const float x2 = fmaf(cth, u, sth * z1);
+    k[0] = fmaf(cpsi, x2, -spsi * y1);
+    k[1] = fmaf(spsi, x2, cpsi * y1);
+    k[2] = fmaf(cth, z1, -sth * u);
 
     // translational dynamics (:455-460) with the acceleration clamp (:488-490)
-    k[3] = FastF32::clamp(fmaf(r, v, fmaf(-q, w, fx * P.inv_mass)), -P.max_acceleration, P.max_acceleration);
-    k[4] = FastF32::clamp(fmaf(p, w, fmaf(-r, u, fy * P.inv_mass)), -P.max_acceleration, P.max_acceleration);
-    k[5] = FastF32::clamp(fmaf(q, u, fmaf(-p, v, fz * P.inv_mass)), -P.max_acceleration, P.max_acceleration);
+    k[3] = FastF32::clamp(fmaf(r, v, fmaf(-q, w, ax)), -P.max_acceleration, P.max_acceleration);
+    k[4] = FastF32::clamp(fmaf(p, w, fmaf(-r, u, ay)), -P.max_acceleration, P.max_acceleration);
+    k[5] = FastF32::clamp(fmaf(q, u, fmaf(-p, v, az)), -P.max_acceleration, P.max_acceleration);
 
     // Euler-angle kinematics with the pitch clipped to +-max_pitch for tan/cos only (:463-471)
     const bool clipped = fabsf(theta) > P.max_pitch_rad;
@@ -211,9 +212,9 @@ __device__ __forceinline__ void dynamics_f32(const DynParams<float>& P, const He
     k[8] = yaw_num * rc;
 
     // Euler's equations (:474-487)
-    k[9] = FastF32::clamp(fmaf(-P.izz_m_iyy * q, r, l_m) * P.inv_ixx, -P.max_angular_acceleration, P.max_angular_acceleration);
-    k[10] = FastF32::clamp(fmaf(-P.ixx_m_izz * p, r, m_m) * P.inv_iyy, -P.max_angular_acceleration, P.max_angular_acceleration);
-    k[11] = FastF32::clamp(fmaf(-P.iyy_m_ixx * p, q, n_m) * P.inv_izz, -P.max_angular_acceleration, P.max_angular_acceleration);
+    k[9] = FastF32::clamp(fmaf(-P.gyro_x * q, r, l_a), -P.max_angular_acceleration, P.max_angular_acceleration);
+    k[10] = FastF32::clamp(fmaf(-P.gyro_y * p, r, m_a), -P.max_angular_acceleration, P.max_angular_acceleration);
+    k[11] = FastF32::clamp(fmaf(-P.gyro_z * p, q, n_a), -P.max_angular_acceleration, P.max_angular_acceleration);
 }
 
 // Cold path of the per-substep scrub (:258, 286-291): position nan->0 / +-inf->+-1e4, the rest -> 0.
@@ -241,7 +242,11 @@ __device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const Hel
     for (int i = 0; i < 12; ++i) acc[i] = k[i];
     // stages 2-4 at s + a k; weights 2, 2, 1.  Rolled: one more copy of the derivative code in the
     // instruction stream, not three.
+#if ACB_F32_UNROLL_STAGES
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
     for (int stage = 1; stage < 4; ++stage) {
         const float a = (stage == 3) ? dt : half_dt;
         const float wgt = (stage == 3) ? 1.0f : 2.0f;
