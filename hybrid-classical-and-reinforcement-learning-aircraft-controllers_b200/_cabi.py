@@ -71,7 +71,7 @@ SYMBOLS = [
     "acb200_synchronize", "acb200_default_aircraft_params", "acb200_cessna_aircraft_params",
     "acb200_default_controller_params", "acb200_set_aircraft_params", "acb200_set_controller_params",
     "acb200_fleet_reset", "acb200_step_surface", "acb200_step_cascade", "acb200_env_reset", "acb200_env_step",
-    "acb200_env_step_host", "acb200_pid_compute_f32", "acb200_pid_reset", "acb200_kernel_info",
+    "acb200_env_step_host", "acb200_set_host_chunks", "acb200_pid_compute_f32", "acb200_pid_reset", "acb200_kernel_info",
     "acb200_launch_count",
 ]
 
@@ -105,7 +105,8 @@ def load() -> C.CDLL:
     L.acb200_step_cascade.argtypes = [vp, P(FleetC), i32, vp, dbl, dbl, dbl, vp]
     L.acb200_env_reset.argtypes = [vp, P(EnvC), P(EnvConfigC), vp]
     L.acb200_env_step.argtypes = [vp, P(EnvC), P(EnvConfigC), vp]
-    L.acb200_env_step_host.argtypes = [vp, P(EnvC), P(EnvConfigC), vp, vp, vp, vp, vp, vp]
+    L.acb200_env_step_host.argtypes = [vp, P(EnvC), P(EnvConfigC), vp, vp, vp, vp, vp, vp, vp]
+    L.acb200_set_host_chunks.argtypes = [vp, i32]
     L.acb200_pid_compute_f32.argtypes = [P(PidConfigC), P(PidStateC), flt, flt, flt]; L.acb200_pid_compute_f32.restype = flt
     L.acb200_pid_reset.argtypes = [P(PidStateC)]; L.acb200_pid_reset.restype = None
     L.acb200_kernel_info.argtypes = [i32, C.c_char_p, P(i32), P(i32), P(i32)]

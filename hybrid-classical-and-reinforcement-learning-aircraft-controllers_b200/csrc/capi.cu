@@ -20,6 +20,12 @@ struct acb200_ctx {
     acb200_controller_params controller;
     int64_t launches;
     std::string error;
+    // env_step_host pipeline: worker streams and their events, created on first use
+    static const int kPipe = 3;
+    cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pipe_done[kPipe] = {nullptr, nullptr, nullptr};
+    cudaEvent_t fork = nullptr;
+    int host_chunks = 0;   // 0 = automatic
 };
 
 namespace {
@@ -111,7 +117,15 @@ int acb200_create(int device, acb200_ctx** out) {
     return ACB200_OK;
 }
 
-void acb200_destroy(acb200_ctx* ctx) { delete ctx; }
+void acb200_destroy(acb200_ctx* ctx) {
+    if (!ctx) return;
+    for (int s = 0; s < acb200_ctx::kPipe; ++s) {
+        if (ctx->pipe_done[s]) cudaEventDestroy(ctx->pipe_done[s]);
+        if (ctx->pipe[s]) cudaStreamDestroy(ctx->pipe[s]);
+    }
+    if (ctx->fork) cudaEventDestroy(ctx->fork);
+    delete ctx;
+}
 
 const char* acb200_last_error(const acb200_ctx* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
 
@@ -257,7 +271,8 @@ int acb200_env_reset(acb200_ctx* ctx, const acb200_env* env, const acb200_env_co
 }
 
 static int env_step_impl(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action,
-                         float* reward_f32) {
+                         float* reward_f32, int64_t first = 0, int64_t count = -1, cudaStream_t stream = nullptr,
+                         bool own_stream = false) {
     int rc = check_env(ctx, env, cfg);
     if (rc) return rc;
     if (!action && (cfg->controller == ACB200_CTRL_EXTERNAL || cfg->controller == ACB200_CTRL_RESIDUAL))
@@ -266,10 +281,12 @@ static int env_step_impl(acb200_ctx* ctx, const acb200_env* env, const acb200_en
     int K; double h;
     if ((rc = substeps(ctx, cfg->dt, cfg->dt_physics, &K, &h))) return rc;
     cudaSetDevice(ctx->device);
+    if (count < 0) count = env->fleet.n;
+    const cudaStream_t st = own_stream ? stream : ctx->stream;
     const cudaError_t e =
         (env->fleet.precision == 64)
-            ? Launch<double>::env_step(ctx->aircraft, ctx->controller, typed<double>(*env, reward_f32), *cfg, K, h, action, ctx->stream)
-            : Launch<float>::env_step(ctx->aircraft, ctx->controller, typed<float>(*env, reward_f32), *cfg, K, h, action, ctx->stream);
+            ? Launch<double>::env_step(ctx->aircraft, ctx->controller, typed<double>(*env, reward_f32), *cfg, K, h, action, first, count, st)
+            : Launch<float>::env_step(ctx->aircraft, ctx->controller, typed<float>(*env, reward_f32), *cfg, K, h, action, first, count, st);
     ctx->launches += 1;
     return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step");
 }
@@ -278,31 +295,80 @@ int acb200_env_step(acb200_ctx* ctx, const acb200_env* env, const acb200_env_con
     return env_step_impl(ctx, env, cfg, action, nullptr);
 }
 
-// Host-buffer step: H2D action, kernel, D2H obs / reward / done flags, all on the context's stream.
-// action_dev is caller-owned device scratch of n*4 + n floats: the staged action followed by the
-// float copy of the reward that the kernel writes for the host.
+// Host-buffer step.  The fleet is cut into chunks and each chunk runs  H2D(action / attitude command) -> kernel ->
+// D2H(obs, reward, done flags)  on one of three worker streams, so that chunk c's D2H, chunk c+1's kernel and chunk
+// c+2's H2D overlap: the call is bound by the slower PCIe direction, not by the sum of the three phases.
+// action_dev is caller-owned device scratch of n*4 + n floats (staged action, float copy of the reward).
 int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action_host,
-                         float* action_dev, float* obs_host, float* reward_host, uint8_t* terminated_host,
-                         uint8_t* truncated_host) {
+                         const void* att_cmd_host, float* action_dev, float* obs_host, float* reward_host,
+                         uint8_t* terminated_host, uint8_t* truncated_host) {
     if (!ctx || !env) return ACB200_ENULL;
     if (!action_dev || !obs_host || !reward_host || !terminated_host || !truncated_host)
         return fail(ctx, ACB200_ENULL, "a host/scratch buffer is NULL");
-    const int64_t n = env->fleet.n;
-    cudaSetDevice(ctx->device);
-    cudaError_t e;
-    if (action_host) {
-        e = cudaMemcpyAsync(action_dev, action_host, (size_t)n * 4 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "H2D action");
-    }
-    float* reward_dev = action_dev + n * 4;
-    const int rc = env_step_impl(ctx, env, cfg, action_host ? action_dev : nullptr, reward_dev);
+    int rc = check_env(ctx, env, cfg);
     if (rc) return rc;
-    e = cudaMemcpyAsync(obs_host, env->obs, (size_t)n * ACB200_OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, reward_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(terminated_host, env->terminated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(truncated_host, env->truncated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (att_cmd_host && !env->att_cmd) return fail(ctx, ACB200_ENULL, "env.att_cmd is NULL");
+    const int64_t n = env->fleet.n;
+    if (n == 0) return ACB200_OK;
+    cudaSetDevice(ctx->device);
+    cudaError_t e = cudaSuccess;
+    if (!ctx->fork) {
+        for (int s = 0; s < acb200_ctx::kPipe && e == cudaSuccess; ++s) {
+            e = cudaStreamCreateWithFlags(&ctx->pipe[s], cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->pipe_done[s], cudaEventDisableTiming);
+        }
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming);
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "env_step_host: stream setup");
+    }
+    // chunks of a multiple of 128 aircraft (whole blocks, 16-byte aligned obs rows), about 64k aircraft each
+    int chunks = ctx->host_chunks > 0 ? ctx->host_chunks : (int)((n + 65535) / 65536);
+    if (chunks > 64) chunks = 64;
+    if (chunks < 1) chunks = 1;
+    int64_t per = ((n + chunks - 1) / chunks + 127) / 128 * 128;
+    float* reward_dev = action_dev + n * 4;
+    const size_t rsz = env->fleet.precision == 64 ? 8 : 4;
+    // the worker streams start after whatever is queued on the context's stream
+    e = cudaEventRecord(ctx->fork, ctx->stream);
+    for (int s = 0; s < acb200_ctx::kPipe && e == cudaSuccess; ++s) e = cudaStreamWaitEvent(ctx->pipe[s], ctx->fork, 0);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "env_step_host: fork");
+    int used = 0;
+    for (int64_t first = 0, c = 0; first < n; first += per, ++c) {
+        const int64_t count = (n - first < per) ? (n - first) : per;
+        const cudaStream_t st = ctx->pipe[c % acb200_ctx::kPipe];
+        used = (int)((c + 1 < acb200_ctx::kPipe) ? c + 1 : acb200_ctx::kPipe);
+        if (action_host) {
+            e = cudaMemcpyAsync(action_dev + first * 4, action_host + first * 4, (size_t)count * 4 * sizeof(float),
+                                cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return cuda_fail(ctx, e, "H2D action");
+        }
+        if (att_cmd_host) {   // real[4][n] field-major: 4 rows of `count` values, row pitch n
+            e = cudaMemcpy2DAsync((char*)env->att_cmd + first * rsz, (size_t)n * rsz, (const char*)att_cmd_host + first * rsz,
+                                  (size_t)n * rsz, (size_t)count * rsz, 4, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return cuda_fail(ctx, e, "H2D att_cmd");
+        }
+        rc = env_step_impl(ctx, env, cfg, action_host ? action_dev : nullptr, reward_dev, first, count, st, true);
+        if (rc) return rc;
+        e = cudaMemcpyAsync(obs_host + first * ACB200_OBS_DIM, env->obs + first * ACB200_OBS_DIM,
+                            (size_t)count * ACB200_OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host + first, reward_dev + first, (size_t)count * sizeof(float), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(terminated_host + first, env->terminated + first, (size_t)count, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(truncated_host + first, env->truncated + first, (size_t)count, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "D2H results");
+    }
+    // join: the context's stream continues after every worker, then the host waits for it
+    for (int s = 0; s < used && e == cudaSuccess; ++s) {
+        e = cudaEventRecord(ctx->pipe_done[s], ctx->pipe[s]);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->pipe_done[s], 0);
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step_host");
+}
+
+int acb200_set_host_chunks(acb200_ctx* ctx, int chunks) {
+    if (!ctx) return ACB200_ENULL;
+    if (chunks < 0) return fail(ctx, ACB200_EVALUE, "chunks < 0");
+    ctx->host_chunks = chunks;
+    return ACB200_OK;
 }
 
 float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt) {

@@ -194,15 +194,14 @@ template <typename T> __device__ __forceinline__ void env_scatter(const EnvPtrs<
 
 // Observations are float[n][18] row-major (the gym / policy-GEMM layout): stage the block's rows in
 // shared memory and write them out as one contiguous, fully coalesced run.
-__device__ __forceinline__ void store_obs_block(float* __restrict__ obs, int64_t n, const float (&o)[18], bool valid,
-                                                float* stage) {
+__device__ __forceinline__ void store_obs_block(float* __restrict__ obs, int64_t first, int64_t end, const float (&o)[18],
+                                                bool valid, float* stage) {
     if (valid) {
 #pragma unroll
         for (int k = 0; k < ACB200_OBS_DIM; ++k) stage[threadIdx.x * ACB200_OBS_DIM + k] = o[k];
     }
     __syncthreads();
-    const int64_t first = (int64_t)blockIdx.x * kBlock;
-    const int64_t rows = (n - first < kBlock) ? (n - first) : kBlock;
+    const int64_t rows = (end - first < kBlock) ? (end - first) : kBlock;
     const int count = (int)rows * ACB200_OBS_DIM;
     float* dst = obs + first * ACB200_OBS_DIM;   // first*18*4 B = blockIdx*9216 B: 16-byte aligned when obs is
     if ((count & 3) == 0 && ((uintptr_t)dst & 15) == 0) {
@@ -241,12 +240,14 @@ template <typename T>
 __global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant__ DynParams<T> P,
                                                           const __grid_constant__ CtrlParams<T> C,
                                                           const __grid_constant__ EnvConst<T> E, EnvPtrs<T> B,
-                                                          const float* __restrict__ action) {
+                                                          const float* __restrict__ action, int64_t first, int64_t count) {
+    // aircraft [first, first + count) of the fleet; n stays the field stride of the SoA buffers
     __shared__ __align__(16) float stage[kBlock * ACB200_OBS_DIM];
     __shared__ double block_stats[ACB200_STATS_FIELDS];
     const int64_t n = B.f.n;
-    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
-    const bool valid = i < n;
+    const int64_t block_first = first + (int64_t)blockIdx.x * kBlock;
+    const int64_t i = block_first + threadIdx.x;
+    const bool valid = i < first + count;
     if (threadIdx.x < ACB200_STATS_FIELDS) block_stats[threadIdx.x] = 0.0;
 
     float o[18];
@@ -365,7 +366,7 @@ __global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant_
         B.is_settled[i] = e.is_settled;
         B.ep_return[i] = e.ep_return;
     }
-    store_obs_block(B.obs, n, o, valid, stage);
+    store_obs_block(B.obs, block_first, first + count, o, valid, stage);
 
     if (B.stats) {
         // warp tree, one shared-memory atomic per warp and field, one global atomic per block and field
@@ -442,10 +443,11 @@ cudaError_t Launch<T>::env_reset(const EnvPtrs<T>& e, const acb200_env_config& c
 
 template <typename T>
 cudaError_t Launch<T>::env_step(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const EnvPtrs<T>& e,
-                                const acb200_env_config& cfg, int K, double h, const float* action, cudaStream_t st) {
-    if (e.f.n <= 0) return cudaSuccess;
-    env_step_kernel<T><<<grid_for(e.f.n), kBlock, 0, st>>>(make_dyn_params<T>(ap), make_ctrl_params<T>(cp),
-                                                           make_env_const<T>(cfg, K, h), e, action);
+                                const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
+                                cudaStream_t st) {
+    if (count <= 0) return cudaSuccess;
+    env_step_kernel<T><<<grid_for(count), kBlock, 0, st>>>(make_dyn_params<T>(ap), make_ctrl_params<T>(cp),
+                                                           make_env_const<T>(cfg, K, h), e, action, first, count);
     return cudaGetLastError();
 }
 

@@ -52,7 +52,8 @@ template <typename T> struct Launch {
                                     int level, const T* cmd, double dt_ctrl, int K, double h, T* surfaces_out, cudaStream_t st);
     static cudaError_t env_reset(const EnvPtrs<T>& e, const acb200_env_config& cfg, const uint8_t* mask, cudaStream_t st);
     static cudaError_t env_step(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const EnvPtrs<T>& e,
-                                const acb200_env_config& cfg, int K, double h, const float* action, cudaStream_t st);
+                                const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
+                                cudaStream_t st);
     static cudaError_t kernel_info(const char* name, KernelInfo* out);
 };
 

@@ -94,12 +94,15 @@ class BatchedRateControlEnv:
         self.ctx.check(self.ctx.lib.acb200_env_step(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action)))
         return self.obs, self.reward, self.terminated, self.truncated
 
-    def step_host(self, action_host, obs_host, reward_host, terminated_host, truncated_host):
-        """Same step with (pinned) HOST tensors in and out; synchronous."""
+    def step_host(self, action_host, obs_host, reward_host, terminated_host, truncated_host, att_cmd_host=None):
+        """Same step with (pinned) HOST tensors in and out; synchronous.  att_cmd_host [4][n] (dtype of the build)
+        is this step's attitude command for controller="attitude_pid"."""
         self._bind_stream()
+        if att_cmd_host is not None:
+            assert att_cmd_host.dtype == self.dtype and att_cmd_host.shape == (4, self.n) and att_cmd_host.is_contiguous()
         self.ctx.check(self.ctx.lib.acb200_env_step_host(
-            self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action_host), _ptr(self._scratch), _ptr(obs_host),
-            _ptr(reward_host), _ptr(terminated_host), _ptr(truncated_host)))
+            self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action_host), _ptr(att_cmd_host), _ptr(self._scratch),
+            _ptr(obs_host), _ptr(reward_host), _ptr(terminated_host), _ptr(truncated_host)))
         return obs_host, reward_host, terminated_host, truncated_host
 
     def episode_stats(self, reset: bool = False) -> dict:

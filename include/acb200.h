@@ -186,11 +186,17 @@ int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const
 int acb200_env_reset(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const uint8_t* mask);
 /* action float[n][4] (aileron, elevator, rudder, throttle); may be NULL unless controller is EXTERNAL/RESIDUAL */
 int acb200_env_step(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const float* action);
-/* Same step with HOST buffers (pinned for speed): copies action in, obs/reward/terminated/truncated out,
- * and synchronises the stream.  reward_host is float[n] (what a VecEnv hands to the trainer). */
+/* Same step with HOST buffers (pinned for speed), what SubprocVecEnv.step_wait hands to the trainer
+ * (learned_controllers/utils/training_utils.py:60-69): copies action_host (float[n][4], nullable) and att_cmd_host
+ * (real[4][n], nullable: the per-step attitude command of ACB200_CTRL_ATTITUDE_PID) in, obs / reward / terminated /
+ * truncated out, pipelined in chunks over three internal streams so that the two PCIe directions and the kernel
+ * overlap, and returns when the host buffers are complete.  reward_host is float[n].  action_dev: caller-owned
+ * device scratch of n*5 floats. */
 int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg,
-                         const float* action_host, float* action_dev /* device scratch, n*5 floats */, float* obs_host, float* reward_host,
-                         uint8_t* terminated_host, uint8_t* truncated_host);
+                         const float* action_host, const void* att_cmd_host, float* action_dev, float* obs_host,
+                         float* reward_host, uint8_t* terminated_host, uint8_t* truncated_host);
+/* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 64k aircraft per chunk) */
+int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 
 /* ---- host-side PID core (the same fp32 arithmetic as the kernels; mirrors PIDController::compute/reset) ---- */
 float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt);
