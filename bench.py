@@ -222,9 +222,7 @@ def run_gpu(args):
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = env.ctx.launch_count - l0
     # the one collective of the path: episode statistics summed over ranks (outside the per-step loop)
-    stats = env.stats.clone()
-    if dist is not None:
-        dist.all_reduce(stats)
+    stats = acb200.sharding.allreduce_episode_stats(env.stats)
     value = n * world * args.steps / (ms * 1e-3)
 
     # ---- end-to-end arm: host buffers, H2D of the step's commands + D2H of obs/reward/done every step

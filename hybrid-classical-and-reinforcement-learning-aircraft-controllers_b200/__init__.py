@@ -6,9 +6,9 @@ from .envs import BatchedRateControlEnv
 from .fleet import AircraftFleet
 from . import adapters, pid_bindings
 from .adapters import SimulationAircraftBackendB200
-from . import vecenv
+from . import sharding, vecenv
 from .vecenv import B200VecEnv
 
-__all__ = ["_cabi", "adapters", "pid_bindings", "SimulationAircraftBackendB200", "vecenv", "B200VecEnv", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
+__all__ = ["_cabi", "adapters", "pid_bindings", "SimulationAircraftBackendB200", "vecenv", "sharding", "B200VecEnv", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
            "default_controller_params", "kernel_info"]
 __version__ = "0.1.0"

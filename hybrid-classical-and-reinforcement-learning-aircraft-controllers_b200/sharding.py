@@ -1,0 +1,35 @@
+"""Multi-GPU layout of the fleet: one process per GPU, aircraft sharded by GLOBAL id, no data-path collective.
+
+No aircraft reads another aircraft's state anywhere on the path, so the only exchange is the
+episode-statistics all-reduce (16 doubles, once per report interval, NCCL over NVLink on GPUs; gloo in the CPU
+tests).  The Philox counter of a reset is (seed, global id, episode), so every trajectory is independent of how many
+ranks the fleet is cut into -- tests/test_gpu_sharding.py checks that bit for bit.
+"""
+from __future__ import annotations
+
+import torch
+
+
+def shard_range(n_total: int, rank: int, world: int):
+    """Contiguous slice [first, first + count) of the global ids owned by `rank`; the first n_total % world ranks get one more."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world of {world}")
+    base, extra = divmod(int(n_total), int(world))
+    first = rank * base + min(rank, extra)
+    return first, base + (1 if rank < extra else 0)
+
+
+def allreduce_episode_stats(stats: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum of the per-rank statistics vectors (envs.STATS_NAMES order); returns a new tensor, `stats` keeps accumulating."""
+    import torch.distributed as dist
+    out = stats.detach().clone()
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)
+    return out
+
+
+def make_sharded_env(n_total: int, rank: int, world: int, device=None, **kw):
+    """This rank's BatchedRateControlEnv over its slice of a fleet of n_total aircraft."""
+    from .envs import BatchedRateControlEnv
+    first, count = shard_range(n_total, rank, world)
+    return BatchedRateControlEnv(count, id_offset=first, device=rank if device is None else device, **kw)
