@@ -294,6 +294,12 @@ def run_gpu(args):
 
 
 def main():
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's version banner under torchrun)
+    # goes to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=1000)

@@ -32,4 +32,5 @@ def test_results_do_not_depend_on_the_sharding(precision):
         assert torch.equal(e.episode_idx, whole.episode_idx[first:first + count])
     tot = sum(e.stats for _, _, e in parts)
     assert tot[0] == whole.stats[0] and tot[15] == whole.stats[15] == 40 * n
-    assert torch.allclose(tot, whole.stats, rtol=1e-9, atol=1e-6)
+    # the per-warp partial sums are formed in the arithmetic type of the build, so their grouping shows at float precision
+    assert torch.allclose(tot, whole.stats, rtol=1e-9 if precision == 64 else 2e-6, atol=1e-6 if precision == 64 else 1e-2)
