@@ -41,11 +41,11 @@ def workload_name(n):
 
 
 def env_bytes_per_step(precision):
-    """Algorithmic HBM bytes per aircraft per env step for env_step_kernel (read + write), from the
-    buffers the kernel gathers and scatters (kernels.cuh env_gather / env_scatter / outputs)."""
+    """Algorithmic HBM bytes per aircraft per env step of env_step_kernel (attitude-PID controller): every buffer
+    the kernel loads (kernels.cuh phases A and C) and stores (scatter + outputs), once each."""
     r = precision // 8
-    rd = 13 * r + 4 * r + 18 * 4 + 3 * r + 4 * 4 + 7 * r + 7 * r + r + 4 + 4 + 1 + 1 + 4 + r + 4 * r   # + att_cmd
-    wr = 13 * r + 4 * r + 18 * 4 + 3 * r + 4 * 4 + 7 * r + 7 * r + r + 4 + 4 + 1 + r + 72 + r + 1 + 1
+    rd = (13 + 4 + 3 + 7 + 7 + 1 + 1) * r + 18 * 4 + 4 * 4 + 4 + 4 + 1 + 1 + 4      # state, att_cmd, rate_cmd, rew_mem, sched, env_time, ep_return | pid, prev_action, counters, flags, difficulty
+    wr = (13 + 4 + 4 + 3 + 7 + 1 + 1 + 1) * r + 18 * 4 + 4 * 4 + 4 + 4 + 1 + 72 + 1 + 1   # state, derived, controls, rate_cmd, rew_mem, env_time, ep_return, reward | pid, prev_action, counters, settled, obs, done flags
     return rd + wr
 
 
@@ -259,7 +259,17 @@ def run_gpu(args):
     per_gpu = value / world
     bytes_step = env_bytes_per_step(precision)
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
-    fp_peak = FP32_PEAK_DERIVED_TFLOPS if precision == 32 else FP32_PEAK_DERIVED_TFLOPS / 2
+    # non-tensor FP32 peak: measured on this device by the library's FMA-chain kernel (MEASURED_PEAKS.json has no
+    # non-tensor compute figure); fp64 denominator: half of it (B200: 64 FP64 lanes per SM against 128 FP32)
+    torch.cuda.synchronize()
+    fp32_measured = env.ctx.measure_fp32_peak()
+    fp_peak = fp32_measured if precision == 32 else fp32_measured / 2
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get(f"env_step_f{precision}_{n}")
+    except Exception:
+        pass
     achieved_tflops = per_gpu * FLOP_PER_ENV_STEP / 1e12
     achieved_gbs = per_gpu * bytes_step / 1e9
     out = {
@@ -269,14 +279,15 @@ def run_gpu(args):
         "config": {"workload": workload_name(n), "envs_per_gpu": n, "controller": "attitude_pid", "substeps": K_SUB,
                    "l2": f"working set {n * bytes_step / 2 / 1e6:.0f} MB per step > 126 MB L2 (inputs larger than L2)",
                    "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
-        "roofline": {"bound": "fp32-pipe (non-tensor compute; see DESIGN.md: the path is not HBM- or tensor-bound)",
+        "roofline": {"bound": "fp32", "note": "non-tensor FP32 issue-bound; the path is neither HBM- nor tensor-bound (DESIGN.md 4); HBM view in roofline_hbm",
                      "achieved": achieved_tflops, "peak": fp_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fp_peak,
-                     "peak_source": "derived 148 SM x 128 lanes x 2 x 1.965 GHz (no non-tensor peak in MEASURED_PEAKS.json)",
+                     "peak_source": "measured here: FMA-chain kernel, all SMs (derived nominal: %.1f)" % FP32_PEAK_DERIVED_TFLOPS,
                      "flop_per_env_step": FLOP_PER_ENV_STEP, "kernel": "env_step_kernel", "kernel_ms": ms / args.steps,
-                     "traffic": None},
+                     "traffic": traffic},
         "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
                          "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
-                         "bytes_per_env_step": bytes_step, "traffic": None},
+                         "bytes_per_env_step": bytes_step, "algorithmic_bytes_per_launch": bytes_step * n,
+                         "traffic": traffic},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": e2e_ms / e2e_steps},
         "gpu_launches": int(launches),

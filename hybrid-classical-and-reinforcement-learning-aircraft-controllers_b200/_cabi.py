@@ -72,7 +72,7 @@ SYMBOLS = [
     "acb200_default_controller_params", "acb200_set_aircraft_params", "acb200_set_controller_params",
     "acb200_fleet_reset", "acb200_step_surface", "acb200_step_cascade", "acb200_env_reset", "acb200_env_step",
     "acb200_env_step_host", "acb200_set_host_chunks", "acb200_pid_compute_f32", "acb200_pid_reset", "acb200_kernel_info",
-    "acb200_launch_count",
+    "acb200_launch_count", "acb200_measure_fp32_peak",
 ]
 
 _lib = None
@@ -111,6 +111,7 @@ def load() -> C.CDLL:
     L.acb200_pid_reset.argtypes = [P(PidStateC)]; L.acb200_pid_reset.restype = None
     L.acb200_kernel_info.argtypes = [i32, C.c_char_p, P(i32), P(i32), P(i32)]
     L.acb200_launch_count.argtypes = [vp]; L.acb200_launch_count.restype = i64
+    L.acb200_measure_fp32_peak.argtypes = [vp, P(dbl)]
     _lib = L
     return L
 
@@ -152,6 +153,12 @@ class Context:
 
     def synchronize(self):
         self.check(self.lib.acb200_synchronize(self.handle))
+
+    def measure_fp32_peak(self) -> float:
+        """TFLOP/s of an FMA-chain kernel on this device (non-tensor FP32 roofline denominator)."""
+        v = C.c_double()
+        self.check(self.lib.acb200_measure_fp32_peak(self.handle, C.byref(v)))
+        return v.value
 
     @property
     def launch_count(self) -> int:

@@ -385,6 +385,47 @@ float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st,
 
 void acb200_pid_reset(acb200_pid_state* st) { memset(st, 0, sizeof *st); }   // pid_controller.cpp:62-69
 
+// Non-tensor FP32 roofline denominator, measured: 8 independent FMA chains per thread, all SMs full.
+__global__ void __launch_bounds__(256) fma_peak_kernel(float* out, float a, float b, int iters) {
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 4
+    for (int i = 0; i < iters; ++i) {
+        x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+        x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+    const float s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (s == 123.456f) out[0] = s;   // never true in practice; keeps the chains alive
+}
+
+int acb200_measure_fp32_peak(acb200_ctx* ctx, double* tflops) {
+    if (!ctx || !tflops) return ACB200_ENULL;
+    cudaSetDevice(ctx->device);
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, ctx->device);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaGetDeviceProperties");
+    float* out = nullptr;
+    if ((e = cudaMalloc(&out, sizeof(float))) != cudaSuccess) return cuda_fail(ctx, e, "cudaMalloc");
+    const int blocks = prop.multiProcessorCount * 8, iters = 1 << 16;
+    cudaEvent_t t0, t1;
+    cudaEventCreate(&t0); cudaEventCreate(&t1);
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {     // first repetition is the warm-up
+        cudaEventRecord(t0, ctx->stream);
+        fma_peak_kernel<<<blocks, 256, 0, ctx->stream>>>(out, 0.999f, 0.001f, iters);
+        cudaEventRecord(t1, ctx->stream);
+        if ((e = cudaEventSynchronize(t1)) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, t0, t1);
+        const double tf = (double)blocks * 256 * iters * 8 * 2 / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(t0); cudaEventDestroy(t1); cudaFree(out);
+    ctx->launches += 4;
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "fma_peak_kernel");
+    *tflops = best;
+    return ACB200_OK;
+}
+
 int acb200_kernel_info(int precision, const char* kernel, int* regs, int* local_bytes, int* max_threads) {
     if (!kernel) return ACB200_ENULL;
     KernelInfo ki;

@@ -204,7 +204,9 @@ void acb200_pid_reset(acb200_pid_state* st);
 
 /* ---- introspection ---- */
 int acb200_kernel_info(int precision, const char* kernel, int* regs, int* local_bytes, int* max_threads);
-int64_t acb200_launch_count(const acb200_ctx* ctx);   /* kernels launched through this context so far */
+int64_t acb200_launch_count(const acb200_ctx* ctx);
+/* measured non-tensor FP32 throughput of this device (FMA = 2 FLOP), the denominator of the fused step's compute roofline */
+int acb200_measure_fp32_peak(acb200_ctx* ctx, double* tflops);   /* kernels launched through this context so far */
 
 #ifdef __cplusplus
 }
