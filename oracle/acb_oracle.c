@@ -114,6 +114,11 @@ void orc_default_controller_params(orc_controller_params* c) {
     c->energy = make_pid_config(0.12, 0.03, 0.03, 10.0, -0.5, 0.5);                                  /* hsa_agent.py:74-84 */
     c->balance = make_pid_config(0.06, 0.005, 0.03, 5.0, -np_radians(15.0), np_radians(15.0));      /* hsa_agent.py:86-100 */
     c->baseline_throttle = 0.1; c->load_factor_gain = 0.05; c->max_pitch_cmd_rad = np_radians(10.0); /* :104-110 */
+    /* GuidanceConfig defaults, config_loader.py:40-64 */
+    c->max_bank_angle_deg = 25.0;
+    c->lookahead_time = 1.2; c->lookahead_min = 12.0; c->lookahead_max = 30.0; c->proximity_scale_distance = 2.0;
+    c->los_max_bank_deg = 20.0; c->los_lead_angle_deg = 30.0;
+    c->turn_threshold_angle_deg = 60.0; c->turn_threshold_distance = 60.0; c->max_speed_reduction = 0.15; c->min_speed = 14.0;
 }
 
 /* ------------------------------------------------------------------------------------------
@@ -392,6 +397,97 @@ static void attitude_agent(const orc_controller_params* C, orc_pid_state ang[3],
     rate_agent(C, rate, rc, throttle, s, dt, surf);
 }
 
+/* HSAAgent.compute_action, controllers/hsa_agent.py:119-231.  outer = heading, energy, balance PIDs.
+ * d = airspeed, altitude, ground_speed, heading of the CURRENT state (what get_state() hands the agent). */
+static void hsa_agent(const orc_controller_params* C, orc_pid_state outer[3], orc_pid_state ang[3], orc_pid_state rate[3],
+                      double heading_cmd, double speed_cmd, double altitude_cmd, const double s[12], const double d[4],
+                      double dt, double surf[4]) {
+    const float fdt = (float)dt;
+    /* :147-160 */
+    const double heading_error = orc_wrap_angle(heading_cmd - d[3]);
+    const double virtual_setpoint = d[3] + heading_error;
+    double roll_angle = (double)orc_pid_compute(&C->heading, &outer[0], (float)virtual_setpoint, (float)d[3], fdt);
+    roll_angle = np_clip(roll_angle, -C->max_bank_rad, C->max_bank_rad);
+    /* :167-186 */
+    const double g = 9.81, h = d[1], V = d[0];
+    const double E_specific = g * h + 0.5 * np_sq(V);
+    const double E_specific_cmd = g * altitude_cmd + 0.5 * np_sq(speed_cmd);
+    const double E_balance = g * h - 0.5 * np_sq(V);
+    const double E_balance_cmd = g * altitude_cmd - 0.5 * np_sq(speed_cmd);
+    /* :192-197 */
+    const double throttle_adjustment = (double)orc_pid_compute(&C->energy, &outer[1], (float)E_specific_cmd, (float)E_specific, fdt);
+    double throttle = C->baseline_throttle + throttle_adjustment;
+    throttle = np_clip(throttle, 0.0, 1.0);
+    /* :203-213 */
+    double pitch_angle = (double)orc_pid_compute(&C->balance, &outer[2], (float)E_balance_cmd, (float)E_balance, fdt);
+    const double cos_roll = cos(roll_angle);
+    if (fabs(cos_roll) > 0.01) {
+        const double load_factor = 1.0 / cos_roll;
+        pitch_angle += C->load_factor_gain * (load_factor - 1.0);
+    }
+    pitch_angle = np_clip(pitch_angle, -C->max_pitch_cmd_rad, C->max_pitch_cmd_rad);
+    /* :216-229: yaw command = current yaw */
+    const double att[3] = {roll_angle, pitch_angle, s[8]};
+    attitude_agent(C, ang, rate, att, throttle, s, dt, surf);
+}
+
+/* WaypointAgent.compute_action, controllers/waypoint_agent.py:81-242 -> (heading, speed, altitude) for the HSA level.
+ * wp = north, east, down, speed (NaN = None). */
+static void waypoint_guidance(const orc_controller_params* C, int guidance, const double wp[4], const double s[12],
+                              const double d[4], double hsa_cmd[3]) {
+    const double e0 = wp[0] - s[0], e1 = wp[1] - s[1];                           /* :244-253 */
+    const double horizontal_distance = np_norm2(e0, e1);                          /* :117 */
+    const double airspeed = d[0], heading = d[3];
+    double heading_cmd;
+    if (guidance == 0) { /* LOS :121-146 */
+        heading_cmd = atan2(e1, e0);
+        const double V = py_max(airspeed, 10.0);
+        const double max_bank = np_radians(C->los_max_bank_deg);
+        const double turn_radius = np_sq(V) / (9.81 * tan(max_bank));
+        double heading_error = heading_cmd - heading;
+        heading_error = atan2(sin(heading_error), cos(heading_error));
+        const double anticipation_dist = turn_radius * fabs(heading_error) / np_radians(90.0);
+        const double lead_angle_rad = np_radians(C->los_lead_angle_deg);
+        if (horizontal_distance < anticipation_dist && fabs(heading_error) > np_radians(20.0)) {
+            const double blend = 1.0 - (horizontal_distance / anticipation_dist);
+            heading_cmd = heading_cmd + blend * lead_angle_rad * np_sign(heading_error);
+            heading_cmd = atan2(sin(heading_cmd), cos(heading_cmd));
+        }
+    } else { /* pure pursuit :148-182 */
+        const double V = py_max(airspeed, 10.0);
+        const double max_bank = np_radians(C->max_bank_angle_deg);
+        const double turn_radius = np_sq(V) / (9.81 * tan(max_bank));
+        double lookahead_dist = C->lookahead_time * V;
+        const double proximity_dist = C->proximity_scale_distance * turn_radius;
+        if (horizontal_distance < proximity_dist) {
+            const double scale = 0.6 + 0.4 * (horizontal_distance / proximity_dist);
+            lookahead_dist *= scale;
+        }
+        lookahead_dist = np_clip(lookahead_dist, C->lookahead_min, C->lookahead_max);
+        if (horizontal_distance > 1.0) {
+            const double dir0 = e0 / horizontal_distance, dir1 = e1 / horizontal_distance;
+            const double effective = (horizontal_distance < lookahead_dist) ? horizontal_distance : lookahead_dist; /* min(a,b) */
+            heading_cmd = atan2(dir1 * effective, dir0 * effective);
+        } else {
+            heading_cmd = atan2(e1, e0);
+        }
+    }
+    heading_cmd = atan2(sin(heading_cmd), cos(heading_cmd));                      /* :189 */
+    /* :207-232 */
+    const double altitude_cmd = -wp[2];
+    double speed_cmd = (wp[3] != wp[3]) ? airspeed : wp[3];
+    const double heading_to_wp = atan2(e1, e0);
+    double heading_error = fabs(heading_to_wp - heading);
+    heading_error = fabs(atan2(sin(heading_error), cos(heading_error)));
+    const double threshold_angle = np_radians(C->turn_threshold_angle_deg);
+    if (horizontal_distance < C->turn_threshold_distance && heading_error > threshold_angle) {
+        const double reduction = C->max_speed_reduction * (1.0 - horizontal_distance / C->turn_threshold_distance);
+        speed_cmd = speed_cmd * (1.0 - reduction);
+        speed_cmd = py_max(speed_cmd, C->min_speed);
+    }
+    hsa_cmd[0] = heading_cmd; hsa_cmd[1] = speed_cmd; hsa_cmd[2] = altitude_cmd;
+}
+
 /* ------------------------------------------------------------------------------------------
  * batched drivers: physics and cascade
  * ---------------------------------------------------------------------------------------- */
@@ -459,6 +555,97 @@ int orc_step_cascade(const orc_aircraft_params* P, const orc_controller_params* 
             orc_derived(s, d);
             for (int f = 0; f < 4; ++f) derived[(int64_t)f * n + i] = d[f];
         }
+    }
+    return K;
+}
+
+static inline void outer_load(const float* p, int64_t n, int64_t i, orc_pid_state outer[3]) {
+    for (int k = 0; k < 3; ++k) {
+        memset(&outer[k], 0, sizeof outer[k]);
+        outer[k].integral = p[(int64_t)(k * 3 + 0) * n + i];
+        outer[k].error_prev = p[(int64_t)(k * 3 + 1) * n + i];
+        outer[k].derivative_filtered = p[(int64_t)(k * 3 + 2) * n + i];
+    }
+}
+static inline void outer_store(float* p, int64_t n, int64_t i, const orc_pid_state outer[3]) {
+    for (int k = 0; k < 3; ++k) {
+        p[(int64_t)(k * 3 + 0) * n + i] = outer[k].integral;
+        p[(int64_t)(k * 3 + 1) * n + i] = outer[k].error_prev;
+        p[(int64_t)(k * 3 + 2) * n + i] = outer[k].derivative_filtered;
+    }
+}
+
+/* one aircraft, levels 1-2: agent on the current state, then set_controls + step */
+static void guided_step_one(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, int64_t i, double* state,
+                            const double hsa_cmd[3], float* pid, float* pid_outer, double* surfaces_out, double* derived,
+                            double dt_ctrl, int K, double h) {
+    double s[12], time, surf[4], c[4], d[4];
+    orc_pid_state rate[3], ang[3], outer[3];
+    for (int f = 0; f < 12; ++f) s[f] = state[(int64_t)f * n + i];
+    time = state[12 * n + i];
+    for (int a = 0; a < 3; ++a) { pid_load(pid, n, i, 0, a, &rate[a]); pid_load(pid, n, i, 1, a, &ang[a]); }
+    outer_load(pid_outer, n, i, outer);
+    orc_derived(s, d);
+    hsa_agent(C, outer, ang, rate, hsa_cmd[0], hsa_cmd[1], hsa_cmd[2], s, d, dt_ctrl, surf);
+    for (int a = 0; a < 3; ++a) { pid_store(pid, n, i, 0, a, &rate[a]); pid_store(pid, n, i, 1, a, &ang[a]); }
+    outer_store(pid_outer, n, i, outer);
+    clip_controls(surf, c);
+    backend_step(P, s, &time, c, K, h);
+    for (int f = 0; f < 12; ++f) state[(int64_t)f * n + i] = s[f];
+    state[12 * n + i] = time;
+    if (surfaces_out) for (int f = 0; f < 4; ++f) surfaces_out[(int64_t)f * n + i] = surf[f];
+    if (derived) {
+        orc_derived(s, d);
+        for (int f = 0; f < 4; ++f) derived[(int64_t)f * n + i] = d[f];
+    }
+}
+
+int orc_step_hsa(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state, const double* cmd,
+                 float* pid, float* pid_outer, double* surfaces_out, double* derived, double dt_ctrl, double dt,
+                 double dt_physics, int nthreads) {
+    double h;
+    const int K = substep_count(P, dt, dt_physics, &h);
+    if (K < 0) return -1;
+    const int nt = resolve_threads(nthreads);
+    (void)nt;
+#pragma omp parallel for num_threads(nt) schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        const double hc[3] = {cmd[i], cmd[n + i], cmd[2 * n + i]};
+        guided_step_one(P, C, n, i, state, hc, pid, pid_outer, surfaces_out, derived, dt_ctrl, K, h);
+    }
+    return K;
+}
+
+int orc_step_waypoint(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state,
+                      const double* waypoints, int n_wp, int32_t* wp_index, int guidance, double acceptance_radius, int loop,
+                      float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
+                      double dt_ctrl, double dt, double dt_physics, int nthreads) {
+    double h;
+    const int K = substep_count(P, dt, dt_physics, &h);
+    if (K < 0) return -1;
+    if (n_wp < 1) return -2;
+    const int nt = resolve_threads(nthreads);
+    (void)nt;
+#pragma omp parallel for num_threads(nt) schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        int32_t idx = wp_index[i];
+        if (idx >= n_wp) continue;                               /* mission complete: the demo stops stepping (:196-203) */
+        /* MissionPlanner.update, mission_planner.py:128-171: 3-D distance < acceptance radius -> next waypoint */
+        const double* wp = waypoints + (int64_t)idx * 4;
+        const double dist = np_norm3(wp[0] - state[i], wp[1] - state[n + i], wp[2] - state[2 * n + i]);
+        if (dist < acceptance_radius) {
+            idx += 1;
+            if (idx >= n_wp && loop) idx = 0;
+            wp_index[i] = idx;
+            if (idx >= n_wp) continue;
+            wp = waypoints + (int64_t)idx * 4;
+        }
+        double s[12], d[4], hc[3];
+        for (int f = 0; f < 12; ++f) s[f] = state[(int64_t)f * n + i];
+        orc_derived(s, d);
+        waypoint_guidance(C, guidance, wp, s, d, hc);
+        if (hsa_cmd_out) for (int f = 0; f < 3; ++f) hsa_cmd_out[(int64_t)f * n + i] = hc[f];
+        guided_step_one(P, C, n, i, state, hc, pid, pid_outer, surfaces_out, derived, dt_ctrl, K, h);
     }
     return K;
 }

@@ -65,6 +65,11 @@ typedef struct {
     /* hsa_agent.py:38-108 + config_loader.py:40-109 */
     orc_pid_config heading, energy, balance;
     double max_bank_rad, baseline_throttle, load_factor_gain, max_pitch_cmd_rad;
+    /* GuidanceConfig, config_loader.py:40-64 (waypoint_agent.py:33-74); angles in degrees as in the config */
+    double max_bank_angle_deg;       /* hsa.max_bank_angle, used by pure pursuit  waypoint_agent.py:53,150 */
+    double lookahead_time, lookahead_min, lookahead_max, proximity_scale_distance;
+    double los_max_bank_deg, los_lead_angle_deg;
+    double turn_threshold_angle_deg, turn_threshold_distance, max_speed_reduction, min_speed;
 } orc_controller_params;
 
 void orc_default_aircraft_params(orc_aircraft_params* p);
@@ -95,6 +100,21 @@ int orc_step_surface(const orc_aircraft_params* P, int64_t n, double* state, con
 int orc_step_cascade(const orc_aircraft_params* P, const orc_controller_params* C, int level, int64_t n,
                      double* state, const double* cmd, float* pid, double* surfaces_out, double* derived,
                      double dt_ctrl, double dt, double dt_physics, int nthreads);
+
+/* level 2 = HSAAgent (hsa_agent.py:119-231): cmd[3][n] = heading, speed, altitude.
+ * pid_outer[9][n] float: (k*3 + {integral,error_prev,derivative_filtered}), k 0=heading 1=energy 2=balance. */
+int orc_step_hsa(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state, const double* cmd,
+                 float* pid, float* pid_outer, double* surfaces_out, double* derived, double dt_ctrl, double dt,
+                 double dt_physics, int nthreads);
+
+/* level 1 = MissionPlanner.update + WaypointAgent.compute_action + sim.step, the loop of
+ * examples/03_waypoint_square_demo.py:147-209.  waypoints[n_wp][4] = north, east, down, speed (NaN = keep the current
+ * airspeed), one mission shared by the fleet; wp_index[n] = current waypoint (n_wp = mission complete: the aircraft is
+ * left untouched, as the demo stops stepping); loop != 0 wraps to waypoint 0 instead.  guidance: 0 LOS, 1 pure pursuit. */
+int orc_step_waypoint(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state,
+                      const double* waypoints, int n_wp, int32_t* wp_index, int guidance, double acceptance_radius, int loop,
+                      float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
+                      double dt_ctrl, double dt, double dt_physics, int nthreads);
 
 /* ---- rate-tracking environment (learned_controllers/envs/rate_env.py) ---- */
 

@@ -53,6 +53,10 @@ class ControllerParams(C.Structure):
         ("heading", PidConfig), ("energy", PidConfig), ("balance", PidConfig),
         ("max_bank_rad", C.c_double), ("baseline_throttle", C.c_double), ("load_factor_gain", C.c_double),
         ("max_pitch_cmd_rad", C.c_double),
+        ("max_bank_angle_deg", C.c_double), ("lookahead_time", C.c_double), ("lookahead_min", C.c_double),
+        ("lookahead_max", C.c_double), ("proximity_scale_distance", C.c_double), ("los_max_bank_deg", C.c_double),
+        ("los_lead_angle_deg", C.c_double), ("turn_threshold_angle_deg", C.c_double),
+        ("turn_threshold_distance", C.c_double), ("max_speed_reduction", C.c_double), ("min_speed", C.c_double),
     ]
 
 
@@ -110,6 +114,11 @@ def lib() -> C.CDLL:
         L.orc_step_cascade.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.c_int, C.c_int64,
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_double, C.c_double, C.c_double, C.c_int]
+        L.orc_step_hsa.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.c_int64, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int]
+        L.orc_step_waypoint.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.c_int64, C.c_void_p,
+                                        C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int]
         L.orc_env_reset.argtypes = [C.POINTER(AircraftParams), C.POINTER(EnvConfig), C.POINTER(EnvBuffers),
                                     C.c_void_p, C.c_int]
         L.orc_env_step.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.POINTER(EnvConfig),
@@ -193,6 +202,39 @@ def step_cascade(params, cparams, level, state, cmd, pid, dt, dt_ctrl=None, dt_p
                                dt if dt_ctrl is None else dt_ctrl, dt, dt_physics, nthreads)
     if k < 0:
         raise ValueError(f"step_cascade failed ({k})")
+    return k
+
+
+GUIDANCE_LOS, GUIDANCE_PP = 0, 1
+
+
+def step_hsa(params, cparams, state, cmd, pid, pid_outer, dt, dt_ctrl=None, dt_physics=0.001, surfaces_out=None,
+             derived_out=None, nthreads=0) -> int:
+    """HSAAgent.compute_action + set_controls + step; cmd [3][n] = heading, speed, altitude."""
+    n = state.shape[1]
+    _chk(state, np.float64, (13, n)); _chk(cmd, np.float64, (3, n)); _chk(pid, np.float32, (18, n)); _chk(pid_outer, np.float32, (9, n))
+    k = lib().orc_step_hsa(C.byref(params), C.byref(cparams), n, state.ctypes.data, cmd.ctypes.data, pid.ctypes.data,
+                           pid_outer.ctypes.data, _ptr(surfaces_out), _ptr(derived_out), dt if dt_ctrl is None else dt_ctrl, dt,
+                           dt_physics, nthreads)
+    if k < 0:
+        raise ValueError(f"step_hsa failed ({k})")
+    return k
+
+
+def step_waypoint(params, cparams, state, waypoints, wp_index, pid, pid_outer, dt, guidance=GUIDANCE_PP, acceptance_radius=40.0,
+                  loop=False, dt_ctrl=None, dt_physics=0.001, surfaces_out=None, derived_out=None, hsa_cmd_out=None,
+                  nthreads=0) -> int:
+    """MissionPlanner.update + WaypointAgent.compute_action + step; waypoints [n_wp][4] = north, east, down, speed."""
+    n = state.shape[1]
+    _chk(state, np.float64, (13, n)); _chk(waypoints, np.float64); _chk(wp_index, np.int32, (n,))
+    _chk(pid, np.float32, (18, n)); _chk(pid_outer, np.float32, (9, n))
+    assert waypoints.ndim == 2 and waypoints.shape[1] == 4
+    k = lib().orc_step_waypoint(C.byref(params), C.byref(cparams), n, state.ctypes.data, waypoints.ctypes.data,
+                                waypoints.shape[0], wp_index.ctypes.data, guidance, acceptance_radius, int(loop),
+                                pid.ctypes.data, pid_outer.ctypes.data, _ptr(surfaces_out), _ptr(derived_out),
+                                _ptr(hsa_cmd_out), dt if dt_ctrl is None else dt_ctrl, dt, dt_physics, nthreads)
+    if k < 0:
+        raise ValueError(f"step_waypoint failed ({k})")
     return k
 
 

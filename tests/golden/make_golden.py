@@ -296,11 +296,98 @@ def gen_env(pool):
     np.savez_compressed(os.path.join(HERE, "rate_env.npz"), **out)
 
 
+# ------------------------------------------------------------------------------------------------
+def _hsa_worker(args):
+    """HSAAgent closed loop through the backend (tests/test_control_integration.py:435-540 shape)."""
+    from controllers.hsa_agent import HSAAgent
+    s0, cmd_seq, hold, steps, dt, every = args
+    b = SimulationAircraftBackend({"aircraft_type": "rc_plane"})
+    agent = HSAAgent(ControllerConfig())
+    state = b.reset(make_state(s0))
+    S, U = [], []
+    for t in range(steps):
+        c = cmd_seq[t // hold]
+        cmd = ControlCommand(mode=ControlMode.HSA, heading=c[0], speed=c[1], altitude=c[2])
+        surf = agent.compute_action(cmd, state, dt)
+        b.set_controls(surf)
+        state = b.step(dt)
+        if (t + 1) % every == 0:
+            S.append(state_vec(b)); U.append(surf.to_array())
+    return np.array(S), np.array(U)
+
+
+def _mission_worker(args):
+    """examples/03_waypoint_square_demo.py:147-209: MissionPlanner.update -> WaypointAgent -> Simplified6DOF.step(DT)
+    directly (one RK4 step per control step), square mission, LOS or pure-pursuit guidance."""
+    from controllers.mission_planner import MissionPlanner
+    from controllers.types import Waypoint
+    from controllers.waypoint_agent import WaypointAgent
+    from simulation.simplified_6dof import AircraftParams, Simplified6DOF
+    s0, wps, guidance, radius, steps, dt, every = args
+    sim = Simplified6DOF(AircraftParams())
+    sim.reset(make_state(s0))
+    agent = WaypointAgent(ControllerConfig(), guidance_type=guidance)
+    mission = MissionPlanner([Waypoint(north=w[0], east=w[1], down=w[2], speed=None if np.isnan(w[3]) else float(w[3]))
+                              for w in wps], acceptance_radius=radius)
+    mission.start()
+    S, U, IDX, HC = [], [], [], []
+    surf = ControlSurfaces()
+    hc = np.zeros(3)
+    for t in range(steps):
+        state = sim.get_state()
+        mission.update(state)
+        if not mission.is_complete():
+            cmd = mission.get_waypoint_command()
+            surf = agent.compute_action(cmd, state, dt)
+            sim.set_controls(surf)
+            sim.step(dt)
+        if (t + 1) % every == 0:
+            S.append(np.concatenate([sim._state, [sim._time]])); U.append(surf.to_array())
+            IDX.append(mission.current_waypoint_index)
+            HC.append(agent.last_heading_cmd if agent.last_heading_cmd is not None else 0.0)
+    return np.array(S), np.array(U), np.array(IDX), np.array(HC)
+
+
+def gen_guidance(pool):
+    """Levels 2 (HSA) and 1 (waypoint mission) -- BASELINE config C5's controller."""
+    rng = np.random.default_rng(2024)
+    n, steps, dt, every, hold = 8, 3000, 0.01, 10, 1000
+    s0 = np.zeros((13, n)); s0[2] = -rng.uniform(80, 120, n); s0[3] = rng.uniform(14, 20, n); s0[8] = rng.uniform(-0.5, 0.5, n)
+    s0[:, 0] = 0.0; s0[2, 0] = -100.0; s0[3, 0] = 20.0                    # level 100 m / 20 m/s (conftest level_flight_state)
+    nseg = steps // hold
+    cmd = np.zeros((nseg, 3, n))
+    cmd[:, 0] = rng.uniform(-np.pi, np.pi, (nseg, n))                      # heading
+    cmd[:, 1] = rng.uniform(14, 20, (nseg, n))                             # speed
+    cmd[:, 2] = rng.uniform(80, 130, (nseg, n))                            # altitude
+    cmd[:, :, 0] = [[np.radians(45.0)], [15.0], [120.0]]                   # test_control_integration.py: heading 45 deg, climb to 120 m
+    res = pool.map(_hsa_worker, [(s0[:, i], cmd[:, :, i], hold, steps, dt, every) for i in range(n)])
+    np.savez(os.path.join(HERE, "hsa_agent.npz"), s0=s0, cmd=cmd, hold=hold, steps=steps, dt=dt, every=every,
+             states=np.stack([r[0] for r in res], axis=2), surfaces=np.stack([r[1] for r in res], axis=2))
+    print("hsa_agent", res[0][0].shape)
+
+    # square mission of the demo (configs/missions/square_pattern.yaml: 300 m, 100 m altitude, 15 m/s, radius 40 m),
+    # one waypoint without a speed (None -> current airspeed)
+    size, alt, spd, radius = 300.0, 100.0, 15.0, 40.0
+    wps = np.array([[0, 0, -alt, spd], [size, 0, -alt, spd], [size, size, -alt, np.nan], [0, size, -alt, spd], [0, 0, -alt, spd]])
+    n, steps, every = 8, 9000, 25
+    s0 = np.zeros((13, n)); s0[2] = -alt; s0[3] = spd
+    s0[0, 1:] = rng.uniform(-20, 20, n - 1); s0[1, 1:] = rng.uniform(-20, 20, n - 1)       # C5: +-20 m, +-10 deg jitter
+    s0[8, 1:] = rng.uniform(-np.radians(10), np.radians(10), n - 1)
+    for guidance in ("PP", "LOS"):
+        res = pool.map(_mission_worker, [(s0[:, i], wps, guidance, radius, steps, dt, every) for i in range(n)])
+        np.savez(os.path.join(HERE, f"waypoint_{guidance.lower()}.npz"), s0=s0, waypoints=wps, guidance=0 if guidance == "LOS" else 1,
+                 acceptance_radius=radius, steps=steps, dt=dt, every=every,
+                 states=np.stack([r[0] for r in res], axis=2), surfaces=np.stack([r[1] for r in res], axis=2),
+                 wp_index=np.stack([r[2] for r in res], axis=1), heading_cmd=np.stack([r[3] for r in res], axis=1))
+        print("waypoint", guidance, "final waypoint index per aircraft", res[0][2][-1], [int(r[2][-1]) for r in res])
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env"]
+    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "guidance"]
     with mp.Pool(8) as pool:
         if "pid" in which: gen_pid_kat()
         if "dyn" in which: gen_dynamics_kat()
         if "open" in which: gen_open_loop(pool)
         if "cascade" in which: gen_cascade(pool)
         if "env" in which: gen_env(pool)
+        if "guidance" in which: gen_guidance(pool)

@@ -171,3 +171,51 @@ def test_rate_env_episodes():
             if ctrl == 1:   # the PID-composed action must be the reference's float32 action bit for bit
                 assert np.array_equal(env.prev_action[:, 0], acts[t]), ctx
         assert bool(term[0]) or bool(trunc[0]) or T == 500
+
+
+def test_hsa_agent_trajectories():
+    """Level 2: HSAAgent (heading PID -> bank, TECS energy/balance PIDs -> throttle/pitch) closed loop, 3000 control steps."""
+    g = _load("hsa_agent.npz")
+    P, Cp = orc.default_aircraft_params(), orc.default_controller_params()
+    state = np.ascontiguousarray(g["s0"]); n = state.shape[1]
+    hold, steps, dt, every = int(g["hold"]), int(g["steps"]), float(g["dt"]), int(g["every"])
+    pid = np.zeros((18, n), np.float32); outer = np.zeros((9, n), np.float32); surf = np.zeros((4, n))
+    worst = 0.0
+    alive = np.ones(n, bool)
+    for t in range(steps):
+        orc.step_hsa(P, Cp, state, np.ascontiguousarray(g["cmd"][t // hold]), pid, outer, dt, surfaces_out=surf)
+        if (t + 1) % every:
+            continue
+        k = (t + 1) // every - 1
+        gs = g["states"][k]
+        alive &= ~((-gs[2] < 5.0) | (np.abs(gs[6]) > np.radians(120)) | (np.abs(gs[7]) > np.radians(80)))
+        e = max(rel_err(state[:, alive], gs[:, alive]), rel_err(surf[:, alive], g["surfaces"][k][:, alive]))
+        worst = max(worst, e)
+        assert e <= TOL, f"hsa: step {t + 1} rel err {e:.3e}"
+    assert alive.sum() >= n // 2
+    print(f"hsa_agent: worst rel err over {steps} steps = {worst:.3e}, {int(alive.sum())}/{n} in envelope")
+
+
+@pytest.mark.parametrize("name", ["waypoint_pp", "waypoint_los"])
+def test_waypoint_mission_trajectories(name):
+    """Level 1: MissionPlanner + WaypointAgent + direct physics step (examples/03_waypoint_square_demo.py), 9000 steps."""
+    g = _load(name + ".npz")
+    P, Cp = orc.default_aircraft_params(), orc.default_controller_params()
+    state = np.ascontiguousarray(g["s0"]); n = state.shape[1]
+    steps, dt, every = int(g["steps"]), float(g["dt"]), int(g["every"])
+    wps = np.ascontiguousarray(g["waypoints"]); idx = np.zeros(n, np.int32)
+    pid = np.zeros((18, n), np.float32); outer = np.zeros((9, n), np.float32); surf = np.zeros((4, n)); hc = np.zeros((3, n))
+    worst = 0.0
+    for t in range(steps):
+        orc.step_waypoint(P, Cp, state, wps, idx, pid, outer, dt, guidance=int(g["guidance"]),
+                          acceptance_radius=float(g["acceptance_radius"]), dt_physics=dt, surfaces_out=surf, hsa_cmd_out=hc)
+        if (t + 1) % every:
+            continue
+        k = (t + 1) // every - 1
+        assert np.array_equal(idx, g["wp_index"][k]), f"{name}: waypoint index at step {t + 1}"
+        e = max(rel_err(state, g["states"][k]), rel_err(surf, g["surfaces"][k]))
+        worst = max(worst, e)
+        assert e <= TOL, f"{name}: step {t + 1} rel err {e:.3e}"
+        assert rel_err(hc[0], g["heading_cmd"][k]) <= 1e-9
+    assert idx.max() >= 3
+    print(f"{name}: worst rel err over {steps} steps = {worst:.3e}; waypoint indices {idx.tolist()}")
