@@ -13,6 +13,8 @@ LEVEL_WAYPOINT, LEVEL_HSA, LEVEL_ATTITUDE, LEVEL_RATE, LEVEL_SURFACE = 1, 2, 3, 
 CTRL_EXTERNAL, CTRL_RATE_PID, CTRL_ATTITUDE_PID, CTRL_RESIDUAL = 0, 1, 2, 3
 CMD_STEP, CMD_RAMP, CMD_SINE, CMD_RANDOM = 0, 1, 2, 3
 OBS_DIM, STATE_FIELDS, CTRL_FIELDS, DERIVED_FIELDS, PID_FIELDS, STATS_FIELDS = 18, 13, 4, 4, 18, 16
+OUTER_PID_FIELDS = 9
+GUIDANCE_LOS, GUIDANCE_PP = 0, 1
 
 AIRCRAFT_FIELDS = [
     "mass", "inertia_xx", "inertia_yy", "inertia_zz", "wing_area", "wing_span", "chord",
@@ -42,7 +44,19 @@ class PidStateC(C.Structure):
 class ControllerParamsC(C.Structure):
     _fields_ = [("rate", PidConfigC * 3), ("angle", PidConfigC * 3),
                 ("max_roll_rate", C.c_double), ("max_pitch_rate", C.c_double), ("max_yaw_rate", C.c_double),
-                ("max_roll", C.c_double), ("max_pitch", C.c_double)]
+                ("max_roll", C.c_double), ("max_pitch", C.c_double),
+                ("heading", PidConfigC), ("energy", PidConfigC), ("balance", PidConfigC),
+                ("max_bank", C.c_double), ("baseline_throttle", C.c_double), ("load_factor_gain", C.c_double),
+                ("max_pitch_cmd", C.c_double), ("max_bank_angle_deg", C.c_double), ("lookahead_time", C.c_double),
+                ("lookahead_min", C.c_double), ("lookahead_max", C.c_double), ("proximity_scale_distance", C.c_double),
+                ("los_max_bank_deg", C.c_double), ("los_lead_angle_deg", C.c_double),
+                ("turn_threshold_angle_deg", C.c_double), ("turn_threshold_distance", C.c_double),
+                ("max_speed_reduction", C.c_double), ("min_speed", C.c_double)]
+
+
+class MissionC(C.Structure):
+    _fields_ = [("waypoints", C.c_void_p), ("n_waypoints", C.c_int32), ("guidance", C.c_int32), ("wp_index", C.c_void_p),
+                ("loop", C.c_int32), ("_pad", C.c_int32), ("acceptance_radius", C.c_double)]
 
 
 class FleetC(C.Structure):
@@ -70,7 +84,7 @@ SYMBOLS = [
     "acb200_version", "acb200_create", "acb200_destroy", "acb200_last_error", "acb200_set_stream",
     "acb200_synchronize", "acb200_default_aircraft_params", "acb200_cessna_aircraft_params",
     "acb200_default_controller_params", "acb200_set_aircraft_params", "acb200_set_controller_params",
-    "acb200_fleet_reset", "acb200_step_surface", "acb200_step_cascade", "acb200_env_reset", "acb200_env_step",
+    "acb200_fleet_reset", "acb200_step_surface", "acb200_step_cascade", "acb200_step_hsa", "acb200_step_waypoint", "acb200_env_reset", "acb200_env_step",
     "acb200_env_step_host", "acb200_set_host_chunks", "acb200_pid_compute_f32", "acb200_pid_reset", "acb200_kernel_info",
     "acb200_launch_count", "acb200_measure_fp32_peak",
 ]
@@ -103,6 +117,8 @@ def load() -> C.CDLL:
     L.acb200_fleet_reset.argtypes = [vp, P(FleetC), vp, vp]
     L.acb200_step_surface.argtypes = [vp, P(FleetC), vp, dbl, dbl]
     L.acb200_step_cascade.argtypes = [vp, P(FleetC), i32, vp, dbl, dbl, dbl, vp]
+    L.acb200_step_hsa.argtypes = [vp, P(FleetC), vp, vp, dbl, dbl, dbl, vp]
+    L.acb200_step_waypoint.argtypes = [vp, P(FleetC), vp, P(MissionC), dbl, dbl, dbl, vp, vp]
     L.acb200_env_reset.argtypes = [vp, P(EnvC), P(EnvConfigC), vp]
     L.acb200_env_step.argtypes = [vp, P(EnvC), P(EnvConfigC), vp]
     L.acb200_env_step_host.argtypes = [vp, P(EnvC), P(EnvConfigC), vp, vp, vp, vp, vp, vp, vp]

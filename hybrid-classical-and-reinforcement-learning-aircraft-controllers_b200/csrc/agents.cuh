@@ -59,4 +59,89 @@ __device__ __forceinline__ void attitude_agent(const CtrlParams<T>& C, PidMem (&
     rate_agent(C, rate, pc, qc, rc, throttle, s[9], s[10], s[11], dt, surf);     // :142-152
 }
 
+// HSAAgent.compute_action (controllers/hsa_agent.py:119-231).  outer = heading, energy, balance PID memory.
+// d = airspeed, altitude, ground_speed, heading of the current state (what get_state() hands the agent).
+template <typename T>
+__device__ __forceinline__ void hsa_agent(const CtrlParams<T>& C, PidMem (&outer)[3], PidMem (&ang)[3], PidMem (&rate)[3],
+                                          T heading_cmd, T speed_cmd, T altitude_cmd, const T (&s)[12], const T (&d)[4], float dt,
+                                          T (&surf)[4]) {
+    using M = Math<T>;
+    // :147-160 heading error wrapped, fed to the PID as a virtual setpoint
+    const T heading_error = wrap_angle(heading_cmd - d[3]);
+    const T virtual_setpoint = d[3] + heading_error;
+    T roll_angle = (T)pid_compute(C.heading, outer[0], (float)virtual_setpoint, (float)d[3], dt);
+    roll_angle = np_clip(roll_angle, -C.max_bank, C.max_bank);
+    // :167-186 TECS specific energies
+    const T g = T(9.81), h = d[1], V = d[0];
+    const T half_v2 = T(0.5) * M::sq(V), half_vc2 = T(0.5) * M::sq(speed_cmd);
+    const T e_specific = g * h + half_v2, e_specific_cmd = g * altitude_cmd + half_vc2;
+    const T e_balance = g * h - half_v2, e_balance_cmd = g * altitude_cmd - half_vc2;
+    // :192-197 total energy -> throttle
+    const T throttle_adjustment = (T)pid_compute(C.energy, outer[1], (float)e_specific_cmd, (float)e_specific, dt);
+    const T throttle = np_clip(C.baseline_throttle + throttle_adjustment, T(0), T(1));
+    // :203-213 energy balance -> pitch, load-factor compensation in the turn
+    T pitch_angle = (T)pid_compute(C.balance, outer[2], (float)e_balance_cmd, (float)e_balance, dt);
+    const T cos_roll = M::cos(roll_angle);
+    if (M::abs(cos_roll) > T(0.01)) {
+        const T load_factor = M::div(T(1), cos_roll);
+        pitch_angle = pitch_angle + C.load_factor_gain * (load_factor - T(1));
+    }
+    pitch_angle = np_clip(pitch_angle, -C.max_pitch_cmd, C.max_pitch_cmd);
+    // :216-229 yaw command = current yaw
+    attitude_agent(C, ang, rate, roll_angle, pitch_angle, s[8], throttle, s, dt, surf);
+}
+
+// WaypointAgent.compute_action (controllers/waypoint_agent.py:81-242) up to the HSA command it issues.
+// wp = north, east, down, speed (NaN = None).  hsa = heading, speed, altitude.
+template <typename T>
+__device__ __forceinline__ void waypoint_guidance(const CtrlParams<T>& C, int guidance, const T (&wp)[4], const T (&s)[12],
+                                                  const T (&d)[4], T (&hsa)[3]) {
+    using M = Math<T>;
+    const T e0 = wp[0] - s[0], e1 = wp[1] - s[1];                        // :244-253
+    const T horizontal_distance = M::norm2(e0, e1);                     // :117
+    const T airspeed = d[0], heading = d[3];
+    const T V = py_max(airspeed, T(10));
+    T heading_cmd;
+    if (guidance == ACB200_GUIDANCE_LOS) {                               // :121-146
+        heading_cmd = M::atan2(e1, e0);
+        const T turn_radius = M::div(M::sq(V), T(9.81) * M::tan(C.los_max_bank));
+        T heading_error = heading_cmd - heading;
+        heading_error = M::atan2(M::sin(heading_error), M::cos(heading_error));
+        const T anticipation_dist = M::div(turn_radius * M::abs(heading_error), C.rad90);
+        if (horizontal_distance < anticipation_dist && M::abs(heading_error) > C.rad20) {
+            const T blend = T(1) - M::div(horizontal_distance, anticipation_dist);
+            heading_cmd = heading_cmd + blend * C.los_lead_angle * np_sign(heading_error);
+            heading_cmd = M::atan2(M::sin(heading_cmd), M::cos(heading_cmd));
+        }
+    } else {                                                             // pure pursuit :148-182
+        const T turn_radius = M::div(M::sq(V), T(9.81) * M::tan(C.pp_max_bank));
+        T lookahead_dist = C.lookahead_time * V;
+        const T proximity_dist = C.proximity_scale_distance * turn_radius;
+        if (horizontal_distance < proximity_dist) {
+            const T scale = T(0.6) + T(0.4) * M::div(horizontal_distance, proximity_dist);
+            lookahead_dist = lookahead_dist * scale;
+        }
+        lookahead_dist = np_clip(lookahead_dist, C.lookahead_min, C.lookahead_max);
+        if (horizontal_distance > T(1)) {
+            const T dir0 = M::div(e0, horizontal_distance), dir1 = M::div(e1, horizontal_distance);
+            const T effective = (horizontal_distance < lookahead_dist) ? horizontal_distance : lookahead_dist;
+            heading_cmd = M::atan2(dir1 * effective, dir0 * effective);
+        } else {
+            heading_cmd = M::atan2(e1, e0);
+        }
+    }
+    heading_cmd = M::atan2(M::sin(heading_cmd), M::cos(heading_cmd));  // :189
+    // :207-232 altitude and speed commands, slowing down into sharp turns
+    T speed_cmd = (wp[3] != wp[3]) ? airspeed : wp[3];
+    const T heading_to_wp = M::atan2(e1, e0);
+    T heading_error = M::abs(heading_to_wp - heading);
+    heading_error = M::abs(M::atan2(M::sin(heading_error), M::cos(heading_error)));
+    if (horizontal_distance < C.turn_threshold_distance && heading_error > C.turn_threshold_angle) {
+        const T reduction = C.max_speed_reduction * (T(1) - M::div(horizontal_distance, C.turn_threshold_distance));
+        speed_cmd = speed_cmd * (T(1) - reduction);
+        speed_cmd = py_max(speed_cmd, C.min_speed);
+    }
+    hsa[0] = heading_cmd; hsa[1] = speed_cmd; hsa[2] = -wp[2];
+}
+
 }  // namespace acb

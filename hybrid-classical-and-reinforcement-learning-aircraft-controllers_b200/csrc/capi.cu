@@ -190,6 +190,16 @@ void acb200_default_controller_params(acb200_controller_params* c) {
     c->angle[0] = pid_cfg(8.0, 2.0, 0.3, il, -c->max_roll_rate, c->max_roll_rate);
     c->angle[1] = pid_cfg(6.0, 1.5, 0.2, il, -c->max_pitch_rate, c->max_pitch_rate);
     c->angle[2] = pid_cfg(1.6, 0.15, 0.01, il, -c->max_yaw_rate, c->max_yaw_rate);
+    // HSAConfig / TECSConfig / GuidanceConfig defaults, controllers/config_loader.py:40-83; hsa_agent.py:57-108
+    c->max_bank = host_radians(25.0);
+    c->heading = pid_cfg(1.0, 0.05, 0.2, il, -c->max_bank, c->max_bank);
+    c->energy = pid_cfg(0.12, 0.03, 0.03, 10.0, -0.5, 0.5);
+    c->balance = pid_cfg(0.06, 0.005, 0.03, 5.0, -host_radians(15.0), host_radians(15.0));
+    c->baseline_throttle = 0.1; c->load_factor_gain = 0.05; c->max_pitch_cmd = host_radians(10.0);
+    c->max_bank_angle_deg = 25.0;
+    c->lookahead_time = 1.2; c->lookahead_min = 12.0; c->lookahead_max = 30.0; c->proximity_scale_distance = 2.0;
+    c->los_max_bank_deg = 20.0; c->los_lead_angle_deg = 30.0;
+    c->turn_threshold_angle_deg = 60.0; c->turn_threshold_distance = 60.0; c->max_speed_reduction = 0.15; c->min_speed = 14.0;
 }
 
 // AircraftParams.__post_init__, simplified_6dof.py:119-143
@@ -257,6 +267,42 @@ int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const
                                           (float*)surfaces_out, ctx->stream);
     ctx->launches += 1;
     return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "step_cascade");
+}
+
+static int step_guided_impl(acb200_ctx* ctx, const acb200_fleet* f, float* pid_outer, const void* cmd, const acb200_mission* m,
+                            double dt_ctrl, double dt, double dt_physics, void* surfaces_out, void* hsa_cmd_out) {
+    int rc = check_fleet(ctx, f, true);
+    if (rc) return rc;
+    if (!pid_outer) return fail(ctx, ACB200_ENULL, "pid_outer is NULL");
+    if (m) {
+        if (!m->waypoints || !m->wp_index) return fail(ctx, ACB200_ENULL, "mission.waypoints / wp_index is NULL");
+        if (m->n_waypoints < 1) return fail(ctx, ACB200_EVALUE, "mission needs at least one waypoint");
+        if (m->guidance != ACB200_GUIDANCE_LOS && m->guidance != ACB200_GUIDANCE_PP) return fail(ctx, ACB200_EVALUE, "unknown guidance type");
+    } else if (!cmd) {
+        return fail(ctx, ACB200_ENULL, "cmd is NULL");
+    }
+    int K; double h;
+    if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
+    cudaSetDevice(ctx->device);
+    const cudaError_t e =
+        (f->precision == 64)
+            ? Launch<double>::step_guided(ctx->aircraft, ctx->controller, typed<double>(*f), pid_outer, (const double*)cmd, m, dt_ctrl, K,
+                                          h, (double*)surfaces_out, (double*)hsa_cmd_out, ctx->stream)
+            : Launch<float>::step_guided(ctx->aircraft, ctx->controller, typed<float>(*f), pid_outer, (const float*)cmd, m, dt_ctrl, K, h,
+                                         (float*)surfaces_out, (float*)hsa_cmd_out, ctx->stream);
+    ctx->launches += 1;
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "step_guided");
+}
+
+int acb200_step_hsa(acb200_ctx* ctx, const acb200_fleet* f, float* pid_outer, const void* cmd, double dt_ctrl, double dt,
+                    double dt_physics, void* surfaces_out) {
+    return step_guided_impl(ctx, f, pid_outer, cmd, nullptr, dt_ctrl, dt, dt_physics, surfaces_out, nullptr);
+}
+
+int acb200_step_waypoint(acb200_ctx* ctx, const acb200_fleet* f, float* pid_outer, const acb200_mission* m, double dt_ctrl,
+                         double dt, double dt_physics, void* surfaces_out, void* hsa_cmd_out) {
+    if (!m) return fail(ctx, ACB200_ENULL, "mission is NULL");
+    return step_guided_impl(ctx, f, pid_outer, nullptr, m, dt_ctrl, dt, dt_physics, surfaces_out, hsa_cmd_out);
 }
 
 int acb200_env_reset(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const uint8_t* mask) {

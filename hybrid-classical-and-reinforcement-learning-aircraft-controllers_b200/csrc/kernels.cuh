@@ -139,6 +139,93 @@ __global__ void __launch_bounds__(kBlock) step_cascade_kernel(const __grid_const
     }
 }
 
+// ---- levels 2 and 1: HSAAgent / (MissionPlanner + WaypointAgent) + set_controls + step ---------------------
+__device__ __forceinline__ void load_outer(const float* p, int64_t n, int64_t i, PidMem (&m)[3]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        m[k].integral = ldf(p, k * 3 + 0, n, i); m[k].error_prev = ldf(p, k * 3 + 1, n, i); m[k].derivative_filtered = ldf(p, k * 3 + 2, n, i);
+    }
+}
+__device__ __forceinline__ void store_outer(float* p, int64_t n, int64_t i, const PidMem (&m)[3]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        stf(p, k * 3 + 0, n, i, m[k].integral); stf(p, k * 3 + 1, n, i, m[k].error_prev); stf(p, k * 3 + 2, n, i, m[k].derivative_filtered);
+    }
+}
+
+template <typename T> struct MissionPtrs {
+    const T* waypoints;
+    int32_t n_waypoints, guidance;
+    int32_t* wp_index;
+    int32_t loop;
+    T acceptance_radius;
+};
+
+template <typename T, int LEVEL>
+__global__ void __launch_bounds__(kBlock) step_guided_kernel(const __grid_constant__ DynParams<T> P,
+                                                             const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
+                                                             float* __restrict__ pid_outer, const T* __restrict__ cmd,
+                                                             MissionPtrs<T> M, float dt_ctrl, int K, T h,
+                                                             T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out) {
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.n) return;
+    T s[12], time, hc[3], surf[4], c[4], d[4];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s[k] = ldf(f.state, k, f.n, i);
+    time = ldf(f.state, 12, f.n, i);
+    derived_outputs(s, d);
+    if (LEVEL == ACB200_LEVEL_WAYPOINT) {
+        int32_t idx = M.wp_index[i];
+        if (idx >= M.n_waypoints) return;                 // mission complete: examples/03_waypoint_square_demo.py:196-203 stops stepping
+        T wp[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
+        // MissionPlanner.update (mission_planner.py:128-171): 3-D distance below the acceptance radius -> next waypoint
+        if (Math<T>::norm3(wp[0] - s[0], wp[1] - s[1], wp[2] - s[2]) < M.acceptance_radius) {
+            idx += 1;
+            if (idx >= M.n_waypoints && M.loop) idx = 0;
+            M.wp_index[i] = idx;
+            if (idx >= M.n_waypoints) return;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
+        }
+        waypoint_guidance(C, M.guidance, wp, s, d, hc);
+        if (hsa_cmd_out) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) stf(hsa_cmd_out, k, f.n, i, hc[k]);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) hc[k] = ldf(cmd, k, f.n, i);
+    }
+    PidMem rate[3], ang[3], outer[3];
+    load_pid(f.pid, f.n, i, 0, rate);
+    load_pid(f.pid, f.n, i, 1, ang);
+    load_outer(pid_outer, f.n, i, outer);
+    hsa_agent(C, outer, ang, rate, hc[0], hc[1], hc[2], s, d, dt_ctrl, surf);
+    store_pid(f.pid, f.n, i, 0, rate);
+    store_pid(f.pid, f.n, i, 1, ang);
+    store_outer(pid_outer, f.n, i, outer);
+    clip_controls(surf, c);
+    backend_step(P, s, time, c, K, h);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) stf(f.state, k, f.n, i, s[k]);
+    stf(f.state, 12, f.n, i, time);
+    if (surfaces_out) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(surfaces_out, k, f.n, i, surf[k]);
+    }
+    if (f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.controls, k, f.n, i, c[k]);
+    }
+    if (f.derived) {
+        derived_outputs(s, d);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stf(f.derived, k, f.n, i, d[k]);
+    }
+}
+
 // ---- env memory <-> registers ----------------------------------------------------------------------
 template <typename T> __device__ __forceinline__ void env_gather(const EnvPtrs<T>& B, int64_t i, EnvRegs<T>& e) {
     const int64_t n = B.f.n;
@@ -435,6 +522,25 @@ cudaError_t Launch<T>::step_cascade(const acb200_aircraft_params& ap, const acb2
 }
 
 template <typename T>
+cudaError_t Launch<T>::step_guided(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const FleetPtrs<T>& f,
+                                   float* pid_outer, const T* cmd, const acb200_mission* m, double dt_ctrl, int K, double h,
+                                   T* surfaces_out, T* hsa_cmd_out, cudaStream_t st) {
+    if (f.n <= 0) return cudaSuccess;
+    const DynParams<T> P = make_dyn_params<T>(ap);
+    const CtrlParams<T> C = make_ctrl_params<T>(cp);
+    MissionPtrs<T> M{nullptr, 0, 0, nullptr, 0, T(0)};
+    if (m) {
+        M = MissionPtrs<T>{(const T*)m->waypoints, m->n_waypoints, m->guidance, m->wp_index, m->loop, (T)m->acceptance_radius};
+        step_guided_kernel<T, ACB200_LEVEL_WAYPOINT><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K, (T)h,
+                                                                                       surfaces_out, hsa_cmd_out);
+    } else {
+        step_guided_kernel<T, ACB200_LEVEL_HSA><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K, (T)h,
+                                                                                  surfaces_out, hsa_cmd_out);
+    }
+    return cudaGetLastError();
+}
+
+template <typename T>
 cudaError_t Launch<T>::env_reset(const EnvPtrs<T>& e, const acb200_env_config& cfg, const uint8_t* mask, cudaStream_t st) {
     if (e.f.n <= 0) return cudaSuccess;
     env_reset_kernel<T><<<grid_for(e.f.n), kBlock, 0, st>>>(e, make_env_const<T>(cfg, 1, cfg.dt), mask);
@@ -457,6 +563,8 @@ template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, Kerne
     else if (!strcmp(name, "step_cascade_rate")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_RATE>;
     else if (!strcmp(name, "step_cascade_attitude")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE>;
     else if (!strcmp(name, "env_step")) fn = (const void*)env_step_kernel<T>;
+    else if (!strcmp(name, "step_hsa")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_HSA>;
+    else if (!strcmp(name, "step_waypoint")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_WAYPOINT>;
     else if (!strcmp(name, "env_reset")) fn = (const void*)env_reset_kernel<T>;
     else if (!strcmp(name, "fleet_reset")) fn = (const void*)fleet_reset_kernel<T>;
     if (!fn) return cudaErrorInvalidValue;

@@ -50,6 +50,9 @@ template <typename T> struct Launch {
                                     cudaStream_t st);
     static cudaError_t step_cascade(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const FleetPtrs<T>& f,
                                     int level, const T* cmd, double dt_ctrl, int K, double h, T* surfaces_out, cudaStream_t st);
+    static cudaError_t step_guided(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const FleetPtrs<T>& f,
+                                   float* pid_outer, const T* cmd, const acb200_mission* m /* NULL: level 2 */, double dt_ctrl, int K,
+                                   double h, T* surfaces_out, T* hsa_cmd_out, cudaStream_t st);
     static cudaError_t env_reset(const EnvPtrs<T>& e, const acb200_env_config& cfg, const uint8_t* mask, cudaStream_t st);
     static cudaError_t env_step(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const EnvPtrs<T>& e,
                                 const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,

@@ -43,6 +43,12 @@ template <typename T> struct CtrlParams {
     acb200_pid_config rate[3];
     acb200_pid_config angle[3];
     T max_roll_rate, max_pitch_rate, max_yaw_rate, max_roll, max_pitch;
+    // HSA / waypoint levels (hsa_agent.py:38-108, waypoint_agent.py:33-74); angles pre-converted with np.radians
+    acb200_pid_config heading, energy, balance;
+    T max_bank, baseline_throttle, load_factor_gain, max_pitch_cmd;
+    T pp_max_bank, los_max_bank, los_lead_angle, turn_threshold_angle, rad90, rad20;
+    T lookahead_time, lookahead_min, lookahead_max, proximity_scale_distance;
+    T turn_threshold_distance, max_speed_reduction, min_speed;
 };
 
 static inline double host_radians(double deg) { return deg * (3.141592653589793 / 180.0); }  // np.radians
@@ -96,6 +102,15 @@ template <typename T> static inline CtrlParams<T> make_ctrl_params(const acb200_
     for (int i = 0; i < 3; ++i) { o.rate[i] = c.rate[i]; o.angle[i] = c.angle[i]; }
     o.max_roll_rate = (T)c.max_roll_rate; o.max_pitch_rate = (T)c.max_pitch_rate; o.max_yaw_rate = (T)c.max_yaw_rate;
     o.max_roll = (T)c.max_roll; o.max_pitch = (T)c.max_pitch;
+    o.heading = c.heading; o.energy = c.energy; o.balance = c.balance;
+    o.max_bank = (T)c.max_bank; o.baseline_throttle = (T)c.baseline_throttle; o.load_factor_gain = (T)c.load_factor_gain;
+    o.max_pitch_cmd = (T)c.max_pitch_cmd;
+    o.pp_max_bank = (T)host_radians(c.max_bank_angle_deg); o.los_max_bank = (T)host_radians(c.los_max_bank_deg);
+    o.los_lead_angle = (T)host_radians(c.los_lead_angle_deg); o.turn_threshold_angle = (T)host_radians(c.turn_threshold_angle_deg);
+    o.rad90 = (T)host_radians(90.0); o.rad20 = (T)host_radians(20.0);
+    o.lookahead_time = (T)c.lookahead_time; o.lookahead_min = (T)c.lookahead_min; o.lookahead_max = (T)c.lookahead_max;
+    o.proximity_scale_distance = (T)c.proximity_scale_distance; o.turn_threshold_distance = (T)c.turn_threshold_distance;
+    o.max_speed_reduction = (T)c.max_speed_reduction; o.min_speed = (T)c.min_speed;
     return o;
 }
 

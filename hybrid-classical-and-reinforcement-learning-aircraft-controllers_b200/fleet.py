@@ -49,6 +49,9 @@ class AircraftFleet:
         self.controls = torch.zeros((4, n), **kw)
         self.derived = torch.zeros((4, n), **kw)
         self.pid = torch.zeros((18, n), device=self.device, dtype=torch.float32)
+        self.pid_outer = torch.zeros((9, n), device=self.device, dtype=torch.float32)   # heading, energy, balance PIDs
+        self.wp_index = torch.zeros((n,), device=self.device, dtype=torch.int32)
+        self._mission = None
         self._pending = torch.zeros((4, n), **kw)
         self.c = _cabi.FleetC(n=n, precision=precision, state=self.state.data_ptr(), controls=self.controls.data_ptr(),
                               derived=self.derived.data_ptr(), pid=self.pid.data_ptr())
@@ -67,6 +70,11 @@ class AircraftFleet:
         if mask is not None:
             mask = mask.to(self.device, torch.uint8).contiguous()
         self.ctx.check(self.ctx.lib.acb200_fleet_reset(self.ctx.handle, C.byref(self.c), _ptr(mask), _ptr(initial_state)))
+        if mask is None:                       # agent.reset() / mission.start() of the outer levels
+            self.pid_outer.zero_(); self.wp_index.zero_()
+        else:
+            m = mask.bool()
+            self.pid_outer[:, m] = 0; self.wp_index[m] = 0
         return self.state
 
     def set_controls(self, surfaces: torch.Tensor):
@@ -99,6 +107,40 @@ class AircraftFleet:
     def step_attitude(self, cmd: torch.Tensor, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None):
         """AttitudeAgent cascade; cmd = roll, pitch, yaw (NaN = None, +inf = hold current yaw), throttle."""
         return self._cascade(_cabi.LEVEL_ATTITUDE, cmd, dt, dt_ctrl, surfaces_out)
+
+    def step_hsa(self, cmd: torch.Tensor, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None):
+        """HSAAgent.compute_action (hsa_agent.py:119-231) + set_controls + step(dt); cmd [3][n] = heading, speed, altitude."""
+        self._bind_stream()
+        cmd = cmd.to(self.device, self.dtype).contiguous()
+        assert cmd.shape == (3, self.n)
+        self.ctx.check(self.ctx.lib.acb200_step_hsa(self.ctx.handle, C.byref(self.c), _ptr(self.pid_outer), _ptr(cmd),
+                                                    dt if dt_ctrl is None else dt_ctrl, dt, self.dt_physics, _ptr(surfaces_out)))
+        return self.state
+
+    def set_mission(self, waypoints, acceptance_radius: float = 40.0, guidance: str = "PP", loop: bool = False):
+        """MissionPlanner(waypoints, acceptance_radius).start() for every aircraft (mission_planner.py:56-93).
+        waypoints [n_wp][4] = north, east, down, speed (NaN = None); guidance 'LOS' | 'PP' (waypoint_agent.py:33-52)."""
+        wp = torch.as_tensor(waypoints).to(self.device, self.dtype).contiguous()
+        assert wp.ndim == 2 and wp.shape[1] == 4 and wp.shape[0] >= 1
+        g = {"LOS": _cabi.GUIDANCE_LOS, "PP": _cabi.GUIDANCE_PP, "PURE_PURSUIT": _cabi.GUIDANCE_PP}[guidance.upper()]
+        self.waypoints = wp
+        self.wp_index.zero_()
+        self._mission = _cabi.MissionC(waypoints=wp.data_ptr(), n_waypoints=wp.shape[0], guidance=g,
+                                       wp_index=self.wp_index.data_ptr(), loop=int(loop), acceptance_radius=acceptance_radius)
+
+    def step_waypoint(self, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None, hsa_cmd_out=None):
+        """One pass of the loop of examples/03_waypoint_square_demo.py:147-209: MissionPlanner.update,
+        WaypointAgent.compute_action, set_controls, step(dt).  Aircraft whose mission is complete are left untouched."""
+        if self._mission is None:
+            raise RuntimeError("set_mission() first")
+        self._bind_stream()
+        self.ctx.check(self.ctx.lib.acb200_step_waypoint(self.ctx.handle, C.byref(self.c), _ptr(self.pid_outer),
+                                                         C.byref(self._mission), dt if dt_ctrl is None else dt_ctrl, dt,
+                                                         self.dt_physics, _ptr(surfaces_out), _ptr(hsa_cmd_out)))
+        return self.state
+
+    def mission_complete(self) -> torch.Tensor:
+        return self.wp_index >= self._mission.n_waypoints
 
     def get_state(self):
         return self.state

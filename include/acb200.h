@@ -95,7 +95,32 @@ typedef struct {
     acb200_pid_config angle[3];   /* roll_angle_gains, pitch_angle_gains, yaw_gains; output +-max rate  attitude_agent.py:43-64 */
     double max_roll_rate, max_pitch_rate, max_yaw_rate;   /* rad/s */
     double max_roll, max_pitch;                           /* rad   */
+    /* HSAAgent, controllers/hsa_agent.py:38-108 with HSAConfig / TECSConfig (config_loader.py:66-83) */
+    acb200_pid_config heading;    /* out +-max_bank   */
+    acb200_pid_config energy;     /* out +-0.5 throttle */
+    acb200_pid_config balance;    /* out +-max_pitch_command */
+    double max_bank, baseline_throttle, load_factor_gain, max_pitch_cmd;   /* rad, -, -, rad (10 deg, hsa_agent.py:108) */
+    /* WaypointAgent, controllers/waypoint_agent.py:33-74 with GuidanceConfig (config_loader.py:40-64); degrees as configured */
+    double max_bank_angle_deg;
+    double lookahead_time, lookahead_min, lookahead_max, proximity_scale_distance;
+    double los_max_bank_deg, los_lead_angle_deg;
+    double turn_threshold_angle_deg, turn_threshold_distance, max_speed_reduction, min_speed;
 } acb200_controller_params;
+
+/* guidance_type of WaypointAgent (waypoint_agent.py:121-186) */
+enum { ACB200_GUIDANCE_LOS = 0, ACB200_GUIDANCE_PP = 1 };
+#define ACB200_OUTER_PID_FIELDS 9   /* (k*3 + {integral, error_prev, derivative_filtered}); k 0 heading, 1 energy, 2 balance */
+
+/* MissionPlanner (controllers/mission_planner.py:128-205) for the whole fleet: one waypoint list, one index per aircraft. */
+typedef struct {
+    const void* waypoints;     /* real[n_waypoints][4]: north, east, down, speed (NaN = None: keep the current airspeed) */
+    int32_t n_waypoints;
+    int32_t guidance;          /* ACB200_GUIDANCE_* */
+    int32_t* wp_index;         /* [n] current waypoint; == n_waypoints: mission complete, the aircraft is no longer stepped */
+    int32_t loop;              /* != 0: after the last waypoint continue with waypoint 0 */
+    int32_t _pad;
+    double acceptance_radius;  /* 3-D distance, mission_planner.py:173-186 */
+} acb200_mission;
 
 /* The aircraft fleet: what N SimulationAircraftBackend objects hold. */
 typedef struct {
@@ -181,6 +206,15 @@ int acb200_step_surface(acb200_ctx* ctx, const acb200_fleet* f, const void* ctrl
  * surfaces_out real[4][n] nullable. */
 int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const void* cmd, double dt_ctrl,
                         double dt, double dt_physics, void* surfaces_out);
+
+/* level 2: surfaces = HSAAgent.compute_action(cmd, state, dt_ctrl) (hsa_agent.py:119-231); set_controls; step(dt).
+ * cmd real[3][n] = heading, speed, altitude.  pid_outer float[9][n].  f->pid holds the inner attitude/rate loops. */
+int acb200_step_hsa(acb200_ctx* ctx, const acb200_fleet* f, float* pid_outer, const void* cmd, double dt_ctrl, double dt,
+                    double dt_physics, void* surfaces_out);
+/* level 1: the loop body of examples/03_waypoint_square_demo.py:147-209 for every aircraft: MissionPlanner.update,
+ * WaypointAgent.compute_action (waypoint_agent.py:81-242), set_controls, step(dt).  hsa_cmd_out real[3][n] nullable. */
+int acb200_step_waypoint(acb200_ctx* ctx, const acb200_fleet* f, float* pid_outer, const acb200_mission* m, double dt_ctrl,
+                         double dt, double dt_physics, void* surfaces_out, void* hsa_cmd_out);
 
 /* ---- rate-tracking environment ---- */
 int acb200_env_reset(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const uint8_t* mask);
