@@ -79,6 +79,19 @@ class EnvConfigC(C.Structure):
                 ("residual_scale", C.c_double), ("seed", C.c_uint64), ("id_offset", C.c_int64)]
 
 
+_FP = C.POINTER(C.c_float)
+
+
+class LstmPolicyWeightsC(C.Structure):
+    _fields_ = [(k, _FP) for k in (
+        "embed_w", "embed_b", "l0_w_ih", "l0_b_ih", "l0_b_hh", "l1_w_ih", "l1_b_ih", "l1_b_hh", "proj_w", "proj_b",
+        "actor_w_ih", "actor_w_hh", "actor_b_ih", "actor_b_hh", "pi0_w", "pi0_b", "pi1_w", "pi1_b", "action_w", "action_b")]
+
+
+class MlpPolicyWeightsC(C.Structure):
+    _fields_ = [(k, _FP) for k in ("pi0_w", "pi0_b", "pi1_w", "pi1_b", "pi2_w", "pi2_b", "action_w", "action_b")]
+
+
 # every symbol include/acb200.h declares (tests/test_cabi_symbols.py checks the header against this)
 SYMBOLS = [
     "acb200_version", "acb200_create", "acb200_destroy", "acb200_last_error", "acb200_set_stream",
@@ -87,6 +100,8 @@ SYMBOLS = [
     "acb200_fleet_reset", "acb200_step_surface", "acb200_step_cascade", "acb200_step_hsa", "acb200_step_waypoint", "acb200_env_reset", "acb200_env_step",
     "acb200_env_step_host", "acb200_set_host_chunks", "acb200_pid_compute_f32", "acb200_pid_reset", "acb200_kernel_info",
     "acb200_launch_count", "acb200_measure_fp32_peak",
+    "acb200_policy_create_lstm", "acb200_policy_create_mlp", "acb200_policy_destroy", "acb200_policy_state_bytes",
+    "acb200_policy_forward", "acb200_policy_state_export", "acb200_policy_state_import", "acb200_policy_info",
 ]
 
 _lib = None
@@ -128,6 +143,14 @@ def load() -> C.CDLL:
     L.acb200_kernel_info.argtypes = [i32, C.c_char_p, P(i32), P(i32), P(i32)]
     L.acb200_launch_count.argtypes = [vp]; L.acb200_launch_count.restype = i64
     L.acb200_measure_fp32_peak.argtypes = [vp, P(dbl)]
+    L.acb200_policy_create_lstm.argtypes = [vp, P(LstmPolicyWeightsC), P(vp)]
+    L.acb200_policy_create_mlp.argtypes = [vp, P(MlpPolicyWeightsC), P(vp)]
+    L.acb200_policy_destroy.argtypes = [vp]; L.acb200_policy_destroy.restype = None
+    L.acb200_policy_state_bytes.argtypes = [vp, i64, P(C.c_size_t), P(C.c_size_t)]
+    L.acb200_policy_forward.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp]
+    L.acb200_policy_state_export.argtypes = [vp, vp, i64, vp, vp, vp, vp]
+    L.acb200_policy_state_import.argtypes = [vp, vp, i64, vp, vp, vp, vp]
+    L.acb200_policy_info.argtypes = [vp, P(dbl), P(C.c_size_t), P(i32)]
     _lib = L
     return L
 

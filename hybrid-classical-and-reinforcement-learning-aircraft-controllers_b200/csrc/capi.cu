@@ -7,26 +7,13 @@
 
 #include <string>
 
+#include "ctx.h"
 #include "kernels.h"
 #include "params.cuh"
 #include "pid.cuh"
 
 using namespace acb;
 
-struct acb200_ctx {
-    int device;
-    cudaStream_t stream;
-    acb200_aircraft_params aircraft;
-    acb200_controller_params controller;
-    int64_t launches;
-    std::string error;
-    // env_step_host pipeline: worker streams and their events, created on first use
-    static const int kPipe = 3;
-    cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr};
-    cudaEvent_t pipe_done[kPipe] = {nullptr, nullptr, nullptr};
-    cudaEvent_t fork = nullptr;
-    int host_chunks = 0;   // 0 = automatic
-};
 
 namespace {
 

@@ -1,0 +1,23 @@
+// ctx.h -- the library context shared by the translation units behind the C ABI (capi.cu, policy.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/acb200.h"
+
+struct acb200_ctx {
+    int device;
+    cudaStream_t stream;
+    acb200_aircraft_params aircraft;
+    acb200_controller_params controller;
+    int64_t launches;
+    std::string error;
+    // env_step_host pipeline: worker streams and their events, created on first use
+    static const int kPipe = 3;
+    cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pipe_done[kPipe] = {nullptr, nullptr, nullptr};
+    cudaEvent_t fork = nullptr;
+    int host_chunks = 0;   // 0 = automatic
+};

@@ -1,0 +1,527 @@
+// policy.cu -- learned rate policy, actor forward as ONE fused tcgen05 kernel per call.
+//
+// Reference path: model.predict(obs, state, deterministic=True) (controllers/learned_rate_agent.py:220-227) through
+// LSTMFeaturesExtractor (learned_controllers/networks/lstm_policy.py:13-97), sb3-contrib's stateful actor LSTM, the
+// pi-MLP of LSTMPolicy.get_policy_kwargs (lstm_policy.py:107-136) and the action head; SimpleMLPPolicy
+// (lstm_policy.py:145-164) runs through the same kernel with a shorter layer table.
+//
+// One CTA owns 128 aircraft for the whole chain.  Activations never leave the SM: each layer's A operand is a bf16
+// buffer in shared memory (X / Y ping-pong), its accumulator is one of two 256-column tensor-memory buffers, and the
+// epilogue threads (one per aircraft row) turn accumulator columns into the next layer's operand -- bias, ReLU or
+// LSTM gates in fp32 -- while the MMA thread already runs the next chunk into the other buffer.  Weights stream from
+// L2 as prepacked stages through a two-deep bulk-copy ring.  The recurrent state h travels as a ready-made operand
+// tile (one bulk load, one bulk store per tile); c is fp32, read and written by the row's own thread.
+#include <math.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "ctx.h"
+#include "policy.cuh"
+
+using namespace acbp;
+
+namespace {
+
+// barrier slots inside the 128-byte barrier block
+enum { B_FULL = 0, B_EMPTY = 2, B_ACC_FULL = 4, B_ACC_EMPTY = 6, B_ACT = 8, B_HFULL = 9, B_COUNT = 10 };
+
+__global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __grid_constant__ PolicyParams P) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* act = smem;
+    const uint32_t smem_base = smem_u32(smem);
+    const uint32_t bar0 = smem_base + kBarOff;
+    auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kBarOff + 8 * B_COUNT);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) { mbar_init(bar(B_FULL + s), 1); mbar_init(bar(B_EMPTY + s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kTile); }
+        mbar_init(bar(B_ACT), kTile);
+        mbar_init(bar(B_HFULL), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 5) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 4) {
+        // ================= weight producer: streams the packed stages in consumption order =================
+        if (lane == 0) {
+            const uint8_t* src = P.weights;
+            uint32_t it = 0;
+            for (int l = 0; l < P.n_layers; ++l) {
+                const LayerDesc& L = P.L[l];
+                const uint32_t bytes = (uint32_t)L.N_c * (uint32_t)L.K_s * 2u;
+                const int n_stage = L.n_chunks * (L.K / L.K_s);
+                for (int i = 0; i < n_stage; ++i, ++it) {
+                    const uint32_t s = it % kStages, use = it / kStages;
+                    if (use > 0) mbar_wait(bar(B_EMPTY + s), (use - 1) & 1, P.error_flag, 100 + l);
+                    mbar_expect_tx(bar(B_FULL + s), bytes);
+                    bulk_g2s(smem_base + kStageOff + s * kStageBytes, src, bytes, bar(B_FULL + s));
+                    src += bytes;
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ================= MMA issuer: one thread drives the tensor core for the whole chain =================
+        if (lane == 0) {
+            uint32_t it = 0, chunk_it = 0;
+            for (int l = 0; l < P.n_layers; ++l) {
+                const LayerDesc& L = P.L[l];
+                mbar_wait(bar(B_ACT), l & 1, P.error_flag, 200 + l);       // operand of layer l is complete
+                if (P.recurrent_layer >= 0) {
+                    if (l == P.recurrent_layer - 1) {                      // X's h region is idle from here on
+                        mbar_expect_tx(bar(B_HFULL), kHTileBytes);
+                        bulk_g2s(smem_base + kHOff, P.h_state + tile * (int64_t)kHTileBytes, kHTileBytes, bar(B_HFULL));
+                    }
+                    if (l == P.recurrent_layer + 1) {                      // Y holds h' as a finished operand tile
+                        bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
+                        bulk_commit();
+                    }
+                }
+                tc_fence_after();
+                const uint32_t idesc = instr_desc_bf16(L.N_c);
+                const uint32_t lbo_b = (uint32_t)L.N_c * 16u;
+                const int stages_per_chunk = L.K / L.K_s, mma_per_stage = L.K_s / 16;
+                for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
+                    const uint32_t a = chunk_it & 1, use = chunk_it >> 1;
+                    if (use > 0) {
+                        mbar_wait(bar(B_ACC_EMPTY + a), (use - 1) & 1, P.error_flag, 300 + l);
+                        tc_fence_after();
+                    }
+                    const uint32_t d_tmem = tmem_base + a * 256u;
+                    for (int ks = 0; ks < stages_per_chunk; ++ks, ++it) {
+                        const uint32_t s = it % kStages;
+                        mbar_wait(bar(B_FULL + s), (it / kStages) & 1, P.error_flag, 400 + l);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_base + L.in_off + (uint32_t)(ks * L.K_s / 8) * kKChunkBytes;
+                        const uint32_t b_addr = smem_base + kStageOff + s * kStageBytes;
+                        for (int k = 0; k < mma_per_stage; ++k) {
+                            const uint64_t ad = smem_desc(a_addr + (uint32_t)k * 2u * kKChunkBytes, kKChunkBytes, 128);
+                            const uint64_t bd = smem_desc(b_addr + (uint32_t)k * 2u * lbo_b, lbo_b, 128);
+                            umma_bf16(d_tmem, ad, bd, idesc, (ks | k) != 0);
+                        }
+                        umma_commit(bar(B_EMPTY + s));                   // stage free once these MMAs have read it
+                    }
+                    umma_commit(bar(B_ACC_FULL + a));                    // accumulator chunk complete
+                }
+            }
+            if (P.recurrent_layer >= 0) bulk_wait_all();
+        }
+    } else {
+        // ================= epilogue: thread r owns aircraft row r of the tile =================
+        const int row = threadIdx.x;
+        const int64_t e = tile * kTile + row;
+        const bool valid = e < P.n;
+        const bool fresh = valid && P.episode_start != nullptr && P.episode_start[e] != 0;
+        const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+
+        {   // observation -> X as [hi | lo | hi | 0] bf16 columns (64 wide) against [W_hi | W_hi | W_lo | 0]:
+            // x*W ~ (hi+lo)*W_hi + hi*W_lo keeps 16 mantissa bits of both (altitude ~100 m enters unnormalised)
+            float o[ACB200_POLICY_OBS];
+            if (valid) {
+                const float2* src = reinterpret_cast<const float2*>(P.obs + e * ACB200_POLICY_OBS);
+#pragma unroll
+                for (int q = 0; q < ACB200_POLICY_OBS / 2; ++q) { const float2 t = __ldg(src + q); o[2 * q] = t.x; o[2 * q + 1] = t.y; }
+            } else {
+#pragma unroll
+                for (int q = 0; q < ACB200_POLICY_OBS; ++q) o[q] = 0.f;
+            }
+            float col[64];
+#pragma unroll
+            for (int q = 0; q < ACB200_POLICY_OBS; ++q) {
+                const float hi = __bfloat162float(__float2bfloat16_rn(o[q]));
+                col[q] = hi;
+                col[ACB200_POLICY_OBS + q] = o[q] - hi;
+                col[2 * ACB200_POLICY_OBS + q] = hi;
+            }
+#pragma unroll
+            for (int q = 3 * ACB200_POLICY_OBS; q < 64; ++q) col[q] = 0.f;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                float t[16];
+#pragma unroll
+                for (int q = 0; q < 16; ++q) t[q] = col[16 * g + q];
+                store_row16(act, P.L[0].in_off, 16 * g, row, t);
+            }
+            fence_async_smem();
+            mbar_arrive(bar(B_ACT));
+        }
+
+        uint32_t chunk_it = 0;
+        for (int l = 0; l < P.n_layers; ++l) {
+            const LayerDesc& L = P.L[l];
+            for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
+                const uint32_t a = chunk_it & 1;
+                mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
+                __syncwarp();
+                tc_fence_after();
+                const uint32_t t0 = tmem_base + lane_base + a * 256u;
+                const float* bias = P.bias + L.bias_off + c * L.N_c;
+                if (L.epi == EPI_RELU) {
+                    for (int j = 0; j < L.N_c; j += 16) {
+                        uint32_t v[16]; float b[16], h[16];
+                        tmem_ld16_issue(t0 + j, v);
+                        load_bias16(bias + j, b);
+                        tmem_ld_wait(v);
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) h[q] = fmaxf(__uint_as_float(v[q]) + b[q], 0.f);
+                        store_row16(act, L.out_off, c * L.N_c + j, row, h);
+                    }
+                } else if (L.epi == EPI_LSTM0) {
+                    // h0 = c0 = 0 on every call (lstm_policy.py:86): c = sig(i) tanh(g), h = sig(o) tanh(c); f unused
+                    const int U = L.N_c / 3;
+                    for (int j = 0; j < U; j += 16) {
+                        uint32_t vi[16], vg[16], vo[16]; float bi[16], bg[16], bo[16], h[16];
+                        tmem_ld16_issue(t0 + j, vi);
+                        tmem_ld16_issue(t0 + U + j, vg);
+                        tmem_ld16_issue(t0 + 2 * U + j, vo);
+                        load_bias16(bias + j, bi); load_bias16(bias + U + j, bg); load_bias16(bias + 2 * U + j, bo);
+                        tmem_ld_wait(vi); tmem_ld_wait(vg); tmem_ld_wait(vo);
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) {
+                            const float cc = sigmoid_fast(__uint_as_float(vi[q]) + bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]);
+                            h[q] = sigmoid_fast(__uint_as_float(vo[q]) + bo[q]) * tanh_fast(cc);
+                        }
+                        store_row16(act, L.out_off, c * U + j, row, h);
+                    }
+                } else if (L.epi == EPI_LSTM) {
+                    const int U = L.N_c / 4;
+                    float* cst = P.c_state + (tile * kHidden + (int64_t)c * U) * kTile + row;
+                    for (int j = 0; j < U; j += 16) {
+                        uint32_t vi[16], vf[16], vg[16], vo[16]; float bi[16], bf[16], bg[16], bo[16], h[16], cp[16];
+                        tmem_ld16_issue(t0 + j, vi);
+                        tmem_ld16_issue(t0 + U + j, vf);
+                        tmem_ld16_issue(t0 + 2 * U + j, vg);
+                        tmem_ld16_issue(t0 + 3 * U + j, vo);
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) cp[q] = (valid && !fresh) ? cst[(int64_t)(j + q) * kTile] : 0.f;
+                        load_bias16(bias + j, bi); load_bias16(bias + U + j, bf);
+                        load_bias16(bias + 2 * U + j, bg); load_bias16(bias + 3 * U + j, bo);
+                        tmem_ld_wait(vi); tmem_ld_wait(vf); tmem_ld_wait(vg); tmem_ld_wait(vo);
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) {
+                            const float cn = fmaf(sigmoid_fast(__uint_as_float(vf[q]) + bf[q]), cp[q],
+                                                  sigmoid_fast(__uint_as_float(vi[q]) + bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]));
+                            h[q] = sigmoid_fast(__uint_as_float(vo[q]) + bo[q]) * tanh_fast(cn);
+                            if (valid) cst[(int64_t)(j + q) * kTile] = cn;
+                        }
+                        store_row16(act, L.out_off, c * U + j, row, h);
+                    }
+                } else {   // EPI_HEAD: mean action, clipped to the action space (rate_env.py:128-138)
+                    uint32_t v[16];
+                    tmem_ld16_issue(t0, v);
+                    tmem_ld_wait(v);
+                    if (valid) {
+                        float4 o;
+                        o.x = fminf(fmaxf(__uint_as_float(v[0]) + __ldg(bias + 0), -1.f), 1.f);
+                        o.y = fminf(fmaxf(__uint_as_float(v[1]) + __ldg(bias + 1), -1.f), 1.f);
+                        o.z = fminf(fmaxf(__uint_as_float(v[2]) + __ldg(bias + 2), -1.f), 1.f);
+                        o.w = fminf(fmaxf(__uint_as_float(v[3]) + __ldg(bias + 3), 0.f), 1.f);
+                        reinterpret_cast<float4*>(P.action)[e] = o;
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(bar(B_ACC_EMPTY + a));
+            }
+            if (l == P.recurrent_layer - 1) {
+                // h_prev has landed behind the features; a fresh episode starts from zeros ((1 - episode_start) * h)
+                mbar_wait(bar(B_HFULL), 0, P.error_flag, 600);
+                if (fresh || !valid) {
+                    const uint4 z = make_uint4(0, 0, 0, 0);
+                    for (int kc = 0; kc < kHidden / 8; ++kc)
+                        *reinterpret_cast<uint4*>(act + kHOff + (uint32_t)kc * kKChunkBytes + (uint32_t)row * 16) = z;
+                }
+            }
+            fence_async_smem();
+            mbar_arrive(bar(B_ACT));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ---- recurrent state <-> (n, 256) f32 ---------------------------------------------------------------------------
+__global__ void state_export_kernel(int64_t n, const __nv_bfloat16* h_state, const float* c_state, float* h_out, float* c_out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over n * 256, unit fastest
+    if (i >= n * kHidden) return;
+    const int64_t e = i / kHidden; const int u = (int)(i % kHidden);
+    const int64_t tile = e / kTile; const int r = (int)(e % kTile);
+    if (h_out) h_out[i] = __bfloat162float(h_state[((tile * (kHidden / 8) + u / 8) * kTile + r) * 8 + u % 8]);
+    if (c_out) c_out[i] = c_state[(tile * kHidden + u) * kTile + r];
+}
+__global__ void state_import_kernel(int64_t n, const float* h_in, const float* c_in, __nv_bfloat16* h_state, float* c_state) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * kHidden) return;
+    const int64_t e = i / kHidden; const int u = (int)(i % kHidden);
+    const int64_t tile = e / kTile; const int r = (int)(e % kTile);
+    if (h_in) h_state[((tile * (kHidden / 8) + u / 8) * kTile + r) * 8 + u % 8] = __float2bfloat16_rn(h_in[i]);
+    if (c_in) c_state[(tile * kHidden + u) * kTile + r] = c_in[i];
+}
+
+}  // namespace
+
+// =====================================================================================================================
+// Host side: layer tables, weight packing, the C ABI
+// =====================================================================================================================
+struct acb200_policy {
+    int kind = 0;
+    PolicyParams params{};          // layer table + device pointers of the packed weights / biases
+    uint8_t* d_weights = nullptr;
+    float* d_bias = nullptr;
+    int* d_error = nullptr;
+    size_t weight_bytes = 0;
+    double flops_per_aircraft = 0.0;   // algorithmic: 2 * out * in over the layers, h0 = 0 products excluded
+    int device = 0;
+};
+
+namespace {
+
+int pfail(acb200_ctx* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->error = msg;
+    return code;
+}
+
+uint16_t bf16_bits(float x) {   // round to nearest even, like __float2bfloat16_rn
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+
+// A layer as the packer sees it: a dense [n_chunks * N_c][K] matrix in EXECUTION order (rows permuted so that one
+// chunk holds every gate of its units, columns padded / duplicated), and its bias in the same row order.
+struct HostLayer {
+    LayerDesc d;
+    std::vector<float> w, b;
+    double real_flops;
+};
+
+HostLayer make_layer(int epi, int K, int K_s, int N_c, int n_chunks, uint32_t in_off, uint32_t out_off) {
+    HostLayer h;
+    h.d = LayerDesc{epi, K, K_s, N_c, n_chunks, in_off, out_off, 0};
+    h.w.assign((size_t)N_c * n_chunks * K, 0.f);
+    h.b.assign((size_t)N_c * n_chunks, 0.f);
+    h.real_flops = 0.0;
+    return h;
+}
+
+// Linear(in -> out): rows as they are; obs_split lays the columns out for the split observation operand
+HostLayer dense_layer(int epi, const float* W, const float* B, int out, int in, int N_c, int K, int K_s, uint32_t in_off,
+                      uint32_t out_off, bool obs_split) {
+    HostLayer h = make_layer(epi, K, K_s, N_c, (out + N_c - 1) / N_c, in_off, out_off);
+    for (int n = 0; n < out; ++n) {
+        for (int k = 0; k < in; ++k) {
+            h.w[(size_t)n * K + k] = W[(size_t)n * in + k];
+            if (obs_split) {   // operand columns [obs_hi | obs_lo | obs_hi] against [W_hi | W_hi | W_lo]
+                uint32_t hb = (uint32_t)bf16_bits(W[(size_t)n * in + k]) << 16;
+                float w_hi;
+                memcpy(&w_hi, &hb, 4);
+                h.w[(size_t)n * K + k] = w_hi;
+                h.w[(size_t)n * K + in + k] = w_hi;
+                h.w[(size_t)n * K + 2 * in + k] = W[(size_t)n * in + k] - w_hi;
+            }
+        }
+        h.b[n] = B[n];
+    }
+    h.real_flops = 2.0 * out * in;
+    return h;
+}
+
+// nn.LSTM cell, gate rows i,f,g,o of `hidden` each.  Chunk c holds units [c*U, (c+1)*U) of every gate it needs:
+// stateless (h0 = c0 = 0): i,g,o (3 gates, W_hh and the f gate drop out); stateful: i,f,g,o over [W_ih | W_hh].
+HostLayer lstm_layer(bool stateful, const float* W_ih, const float* W_hh, const float* b_ih, const float* b_hh, int in, int U,
+                     uint32_t in_off, uint32_t out_off) {
+    const int gates = stateful ? 4 : 3, K = stateful ? in + kHidden : in;
+    static const int kStateless[3] = {0, 2, 3};
+    HostLayer h = make_layer(stateful ? EPI_LSTM : EPI_LSTM0, K, 64, gates * U, kHidden / U, in_off, out_off);
+    for (int c = 0; c < kHidden / U; ++c)
+        for (int g = 0; g < gates; ++g)
+            for (int u = 0; u < U; ++u) {
+                const int src = (stateful ? g : kStateless[g]) * kHidden + c * U + u;
+                const size_t dst = (size_t)(c * gates + g) * U + u;
+                for (int k = 0; k < in; ++k) h.w[dst * K + k] = W_ih[(size_t)src * in + k];
+                if (stateful)
+                    for (int k = 0; k < kHidden; ++k) h.w[dst * K + in + k] = W_hh[(size_t)src * kHidden + k];
+                h.b[dst] = b_ih[src] + b_hh[src];
+            }
+    h.real_flops = 2.0 * gates * kHidden * K;
+    return h;
+}
+
+int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& layers, acb200_policy** out) {
+    std::vector<uint16_t> packed;
+    std::vector<float> bias;
+    p->params.n_layers = (int)layers.size();
+    p->params.recurrent_layer = -1;
+    for (size_t l = 0; l < layers.size(); ++l) {
+        HostLayer& h = layers[l];
+        LayerDesc& d = h.d;
+        if (d.K % 16 || d.K % d.K_s || d.K_s % 16 || d.N_c % 16 || d.N_c > 256 ||
+            (uint32_t)d.N_c * d.K_s * 2u > kStageBytes)
+            return pfail(ctx, ACB200_EVALUE, "policy: bad layer geometry");
+        d.bias_off = (int)bias.size();
+        bias.insert(bias.end(), h.b.begin(), h.b.end());
+        if (d.epi == EPI_LSTM) p->params.recurrent_layer = (int)l;
+        for (int c = 0; c < d.n_chunks; ++c)
+            for (int ks = 0; ks < d.K / d.K_s; ++ks)
+                for (int kk = 0; kk < d.K_s / 8; ++kk)
+                    for (int n = 0; n < d.N_c; ++n)
+                        for (int j = 0; j < 8; ++j)
+                            packed.push_back(bf16_bits(h.w[(size_t)(c * d.N_c + n) * d.K + ks * d.K_s + kk * 8 + j]));
+        p->params.L[l] = d;
+        p->flops_per_aircraft += h.real_flops;
+    }
+    p->weight_bytes = packed.size() * 2;
+    p->device = ctx->device;
+    cudaSetDevice(ctx->device);
+    cudaError_t e;
+    if ((e = cudaMalloc(&p->d_weights, p->weight_bytes)) != cudaSuccess ||
+        (e = cudaMalloc(&p->d_bias, bias.size() * sizeof(float))) != cudaSuccess ||
+        (e = cudaMalloc(&p->d_error, sizeof(int))) != cudaSuccess ||
+        (e = cudaMemcpy(p->d_weights, packed.data(), p->weight_bytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(p->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemset(p->d_error, 0, sizeof(int))) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess) {
+        acb200_policy_destroy(p);
+        return pfail(ctx, ACB200_ECUDA, std::string("policy upload: ") + cudaGetErrorString(e));
+    }
+    p->params.weights = p->d_weights;
+    p->params.bias = p->d_bias;
+    p->params.error_flag = p->d_error;
+    *out = p;
+    return ACB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int acb200_policy_create_lstm(acb200_ctx* ctx, const acb200_lstm_policy_weights* w, acb200_policy** out) {
+    if (!ctx || !w || !out) return ACB200_ENULL;
+    const float* const* ptrs = reinterpret_cast<const float* const*>(w);
+    for (size_t i = 0; i < sizeof(*w) / sizeof(float*); ++i)
+        if (!ptrs[i]) return pfail(ctx, ACB200_ENULL, "policy: NULL weight pointer");
+    const uint32_t X = 0, Y = kXBytes, X2 = kHOff;
+    std::vector<HostLayer> L;
+    L.push_back(dense_layer(EPI_RELU, w->embed_w, w->embed_b, 128, ACB200_POLICY_OBS, 128, 64, 64, X, Y, true));
+    L.push_back(lstm_layer(false, w->l0_w_ih, nullptr, w->l0_b_ih, w->l0_b_hh, 128, 64, Y, X));
+    L.push_back(lstm_layer(false, w->l1_w_ih, nullptr, w->l1_b_ih, w->l1_b_hh, 256, 64, X, Y));
+    L.push_back(dense_layer(EPI_RELU, w->proj_w, w->proj_b, 128, 256, 128, 256, 128, Y, X, false));
+    L.push_back(lstm_layer(true, w->actor_w_ih, w->actor_w_hh, w->actor_b_ih, w->actor_b_hh, 128, 64, X, Y));
+    L.push_back(dense_layer(EPI_RELU, w->pi0_w, w->pi0_b, 128, 256, 128, 256, 128, Y, X, false));
+    L.push_back(dense_layer(EPI_RELU, w->pi1_w, w->pi1_b, 64, 128, 64, 128, 128, X, X2, false));
+    L.push_back(dense_layer(EPI_HEAD, w->action_w, w->action_b, ACB200_POLICY_ACT, 64, 16, 64, 64, X2, X, false));
+    acb200_policy* p = new acb200_policy();
+    p->kind = ACB200_POLICY_LSTM;
+    return finish_policy(ctx, p, L, out);
+}
+
+int acb200_policy_create_mlp(acb200_ctx* ctx, const acb200_mlp_policy_weights* w, acb200_policy** out) {
+    if (!ctx || !w || !out) return ACB200_ENULL;
+    const float* const* ptrs = reinterpret_cast<const float* const*>(w);
+    for (size_t i = 0; i < sizeof(*w) / sizeof(float*); ++i)
+        if (!ptrs[i]) return pfail(ctx, ACB200_ENULL, "policy: NULL weight pointer");
+    const uint32_t X = 0, Y = kXBytes, X2 = kHOff;
+    std::vector<HostLayer> L;
+    L.push_back(dense_layer(EPI_RELU, w->pi0_w, w->pi0_b, 256, ACB200_POLICY_OBS, 256, 64, 64, X, Y, true));
+    L.push_back(dense_layer(EPI_RELU, w->pi1_w, w->pi1_b, 128, 256, 128, 256, 128, Y, X, false));
+    L.push_back(dense_layer(EPI_RELU, w->pi2_w, w->pi2_b, 64, 128, 64, 128, 128, X, X2, false));
+    L.push_back(dense_layer(EPI_HEAD, w->action_w, w->action_b, ACB200_POLICY_ACT, 64, 16, 64, 64, X2, X, false));
+    acb200_policy* p = new acb200_policy();
+    p->kind = ACB200_POLICY_MLP;
+    return finish_policy(ctx, p, L, out);
+}
+
+void acb200_policy_destroy(acb200_policy* p) {
+    if (!p) return;
+    cudaSetDevice(p->device);
+    cudaFree(p->d_weights);
+    cudaFree(p->d_bias);
+    cudaFree(p->d_error);
+    delete p;
+}
+
+int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes, size_t* c_bytes) {
+    if (!p) return ACB200_ENULL;
+    if (n < 0) return ACB200_EVALUE;
+    const size_t tiles = (size_t)((n + kTile - 1) / kTile);
+    const bool rec = p->params.recurrent_layer >= 0;
+    if (h_bytes) *h_bytes = rec ? tiles * kHTileBytes : 0;
+    if (c_bytes) *c_bytes = rec ? tiles * (size_t)kHidden * kTile * sizeof(float) : 0;
+    return ACB200_OK;
+}
+
+int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
+                          void* h_state, void* c_state, float* action_out) {
+    if (!ctx || !p || !obs || !action_out) return pfail(ctx, ACB200_ENULL, "policy_forward: NULL argument");
+    if (n < 0) return pfail(ctx, ACB200_EVALUE, "policy_forward: n < 0");
+    if (n == 0) return ACB200_OK;
+    const bool rec = p->params.recurrent_layer >= 0;
+    if (rec && (!h_state || !c_state)) return pfail(ctx, ACB200_ENULL, "policy_forward: recurrent policy needs h_state and c_state");
+    if (((uintptr_t)obs & 7) || ((uintptr_t)action_out & 15) || (rec && (((uintptr_t)h_state & 15) || ((uintptr_t)c_state & 3))))
+        return pfail(ctx, ACB200_EVALUE, "policy_forward: misaligned buffer");
+    cudaSetDevice(ctx->device);
+    PolicyParams P = p->params;
+    P.obs = obs; P.episode_start = episode_start;
+    P.h_state = static_cast<uint8_t*>(h_state); P.c_state = static_cast<float*>(c_state);
+    P.action = action_out; P.n = n;
+    const int64_t tiles = (n + kTile - 1) / kTile;
+    policy_forward_kernel<<<(unsigned)tiles, kThreads, kSmemBytes, ctx->stream>>>(P);
+    ctx->launches += 1;
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return pfail(ctx, ACB200_ECUDA, std::string("policy_forward_kernel: ") + cudaGetErrorString(e));
+    return ACB200_OK;
+}
+
+int acb200_policy_state_export(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const void* h_state, const void* c_state,
+                               float* h_out, float* c_out) {
+    if (!ctx || !p || !h_state || !c_state) return ACB200_ENULL;
+    if (p->params.recurrent_layer < 0) return pfail(ctx, ACB200_ENOSUP, "policy has no recurrent state");
+    if (n <= 0) return n < 0 ? ACB200_EVALUE : ACB200_OK;
+    cudaSetDevice(ctx->device);
+    const int64_t total = n * kHidden;
+    state_export_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(n, static_cast<const __nv_bfloat16*>(h_state),
+                                                                                 static_cast<const float*>(c_state), h_out, c_out);
+    ctx->launches += 1;
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? ACB200_OK : pfail(ctx, ACB200_ECUDA, std::string("state_export_kernel: ") + cudaGetErrorString(e));
+}
+
+int acb200_policy_state_import(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const float* h_in, const float* c_in,
+                               void* h_state, void* c_state) {
+    if (!ctx || !p || !h_state || !c_state) return ACB200_ENULL;
+    if (p->params.recurrent_layer < 0) return pfail(ctx, ACB200_ENOSUP, "policy has no recurrent state");
+    if (n <= 0) return n < 0 ? ACB200_EVALUE : ACB200_OK;
+    cudaSetDevice(ctx->device);
+    const int64_t total = n * kHidden;
+    state_import_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(n, h_in, c_in, static_cast<__nv_bfloat16*>(h_state),
+                                                                                 static_cast<float*>(c_state));
+    ctx->launches += 1;
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? ACB200_OK : pfail(ctx, ACB200_ECUDA, std::string("state_import_kernel: ") + cudaGetErrorString(e));
+}
+
+int acb200_policy_info(const acb200_policy* p, double* flops_per_aircraft, size_t* weight_bytes, int* smem_bytes) {
+    if (!p) return ACB200_ENULL;
+    if (flops_per_aircraft) *flops_per_aircraft = p->flops_per_aircraft;
+    if (weight_bytes) *weight_bytes = p->weight_bytes;
+    if (smem_bytes) *smem_bytes = (int)kSmemBytes;
+    return ACB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,191 @@
+// policy.cuh -- device-side building blocks of the fused policy-forward kernel (row a20): raw sm_100a PTX for
+// mbarriers, bulk (TMA) copies, tensor-memory management and tcgen05.mma, plus the layer table the kernel walks.
+//
+// Operand layout (no tensor map needed): every A/B operand sits in shared memory as the UMMA "K-major, no swizzle"
+// canonical layout -- 8-row x 16-byte core matrices, each 128 contiguous bytes:
+//     element (row, k)  ->  ((k / 8) * ROWS + row) * 16 bytes + (k % 8) * 2 bytes          (bf16)
+// so the stride between the two K-halves of one MMA (leading-dimension byte offset) is ROWS*16 and the stride between
+// 8-row groups (stride-dimension byte offset) is 128.  Activations are written in this layout by the epilogue
+// threads (one thread per aircraft row, one 16-byte store per 8 outputs), weights are packed into it on the host
+// once, so a weight stage is ONE contiguous cp.async.bulk from L2.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace acbp {
+
+constexpr int kTile = 128;               // aircraft per CTA == UMMA M == tensor-memory lanes
+constexpr int kMaxLayers = 8;
+constexpr int kStages = 2;               // weight ring depth
+constexpr uint32_t kStageBytes = 32768;
+constexpr uint32_t kXBytes = 98304;      // activation buffer X: up to K = 384 (features 128 | h 256)
+constexpr uint32_t kYBytes = 65536;      // activation buffer Y: up to K = 256
+constexpr uint32_t kStageOff = kXBytes + kYBytes;
+constexpr uint32_t kBarOff = kStageOff + kStages * kStageBytes;
+constexpr uint32_t kSmemBytes = kBarOff + 128;
+constexpr uint32_t kKChunkBytes = kTile * 16;   // one 8-wide K slab of an activation buffer (2048 B)
+constexpr int kHidden = 256;
+constexpr uint32_t kHTileBytes = kHidden * kTile * 2;   // one tile of h, bf16, already in operand layout
+constexpr uint32_t kHOff = 16 * kKChunkBytes;           // h sits behind the 128 feature columns in X
+constexpr int kThreads = 192;            // warps 0-3 epilogue (row = thread), warp 4 weight producer, warp 5 MMA issuer
+constexpr uint32_t kTmemCols = 512;      // two accumulator buffers of 256 fp32 columns
+
+enum Epilogue : int { EPI_RELU = 0, EPI_LSTM0 = 1, EPI_LSTM = 2, EPI_HEAD = 3 };
+
+struct LayerDesc {
+    int epi;
+    int K;          // operand depth as executed (multiple of 16)
+    int K_s;        // depth of one weight stage
+    int N_c;        // accumulator columns per chunk (multiple of 16, <= 256)
+    int n_chunks;
+    uint32_t in_off, out_off;   // byte offsets of the A operand / of output column 0 inside the activation area
+    int bias_off;   // float offset into the bias array (permuted like the packed rows)
+};
+
+struct PolicyParams {
+    int n_layers;
+    int recurrent_layer;      // index of the EPI_LSTM layer, -1 if none
+    LayerDesc L[kMaxLayers];
+    const uint8_t* weights;   // packed stages in consumption order
+    const float* bias;
+    const float* obs;         // [n][18]
+    const uint8_t* episode_start;
+    uint8_t* h_state;         // [tiles][32][128][8] bf16
+    float* c_state;           // [tiles][256][128]
+    float* action;            // [n][4]
+    int64_t n;
+    int* error_flag;
+};
+
+// ---- shared-memory addresses, mbarriers -------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug must end as a trapped kernel with a code in *err, not as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* err, int code) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 4000000000LL) {   // about two seconds
+            if (err) *err = code;
+            __threadfence_system();
+            __trap();
+        }
+    }
+}
+
+// ---- bulk asynchronous copies (TMA engine, 1-D) ---------------------------------------------------------------------
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// generic-proxy writes to shared memory -> visible to the async proxy (UMMA operand reads, bulk stores)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ---- tensor memory + tcgen05 ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {   // whole warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {    // whole warp, the allocating one
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_NONE, descriptor version 1 (sm_100)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+// instruction descriptor: D = f32, A = B = bf16, both K-major, M = 128
+__device__ __forceinline__ uint32_t instr_desc_bf16(int n_cols) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((uint32_t)(kTile >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// mbarrier arrive once every tcgen05 operation this thread issued so far has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// 16 consecutive fp32 accumulator columns of this thread's lane (32x32b: lane = 32 * (warp % 4) + laneid)
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+// wait for the loads; the registers are operands so that no use can be scheduled above the wait
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                   "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+                 :
+                 : "memory");
+}
+
+// ---- gate arithmetic (fp32; one MUFU per transcendental) ---------------------------------------------------------------
+__device__ __forceinline__ float tanh_fast(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+// 16 consecutive output columns of one row -> two 16-byte stores in operand layout
+__device__ __forceinline__ void store_row16(uint8_t* act, uint32_t out_off, int k0, int row, const float (&h)[16]) {
+    uint4 a = make_uint4(pack_bf16(h[0], h[1]), pack_bf16(h[2], h[3]), pack_bf16(h[4], h[5]), pack_bf16(h[6], h[7]));
+    uint4 b = make_uint4(pack_bf16(h[8], h[9]), pack_bf16(h[10], h[11]), pack_bf16(h[12], h[13]), pack_bf16(h[14], h[15]));
+    uint8_t* p = act + out_off + (uint32_t)(k0 >> 3) * kKChunkBytes + (uint32_t)row * 16;
+    *reinterpret_cast<uint4*>(p) = a;
+    *reinterpret_cast<uint4*>(p + kKChunkBytes) = b;
+}
+__device__ __forceinline__ void load_bias16(const float* b, float (&out)[16]) {
+    const float4* p = reinterpret_cast<const float4*>(b);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float4 t = __ldg(p + q);
+        out[4 * q] = t.x; out[4 * q + 1] = t.y; out[4 * q + 2] = t.z; out[4 * q + 3] = t.w;
+    }
+}
+
+}  // namespace acbp

@@ -232,6 +232,55 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_
 /* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 64k aircraft per chunk) */
 int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 
+/* ---- learned rate policy, actor forward (row a20) -------------------------------------------------------------
+ * Replaces: model.predict(obs, state=lstm_state, deterministic=True) at controllers/learned_rate_agent.py:220-227
+ * with the network of learned_controllers/networks/lstm_policy.py:13-164 (LSTMFeaturesExtractor + sb3-contrib's
+ * stateful actor LSTM + pi-MLP [128,64] + action_net; or SimpleMLPPolicy's pi-MLP [256,128,64] + action_net).
+ * One fused tcgen05 kernel per call: bf16 operands, fp32 accumulation in tensor memory, gates in fp32.
+ * All weight pointers are HOST fp32 arrays in torch's own layouts (Linear.weight [out][in]; nn.LSTM weight_ih
+ * [4*256][in], weight_hh [4*256][256], gate order i,f,g,o); they are packed once, at creation. */
+typedef struct acb200_policy acb200_policy;
+enum { ACB200_POLICY_LSTM = 0, ACB200_POLICY_MLP = 1 };
+#define ACB200_POLICY_OBS 18
+#define ACB200_POLICY_ACT 4
+#define ACB200_POLICY_HIDDEN 256
+#define ACB200_POLICY_TILE 128 /* aircraft per thread block; recurrent state buffers are sized in whole tiles */
+
+typedef struct acb200_lstm_policy_weights {
+    const float *embed_w, *embed_b;                      /* features_extractor.embedding.0     [128][18], [128] */
+    const float *l0_w_ih, *l0_b_ih, *l0_b_hh;            /* features_extractor.lstm  *_l0  [1024][128], [1024] x2 */
+    const float *l1_w_ih, *l1_b_ih, *l1_b_hh;            /* features_extractor.lstm  *_l1  [1024][256], [1024] x2 */
+    const float *proj_w, *proj_b;                        /* features_extractor.output_proj.0  [128][256], [128] */
+    const float *actor_w_ih, *actor_w_hh;                /* lstm_actor *_l0     [1024][128], [1024][256] */
+    const float *actor_b_ih, *actor_b_hh;                /*                     [1024] x2 */
+    const float *pi0_w, *pi0_b, *pi1_w, *pi1_b;          /* mlp_extractor.policy_net.0 [128][256], .2 [64][128] */
+    const float *action_w, *action_b;                    /* action_net [4][64], [4] */
+} acb200_lstm_policy_weights;
+/* (the extractor LSTM's weight_hh_l0/l1 multiply h0 = 0 on every call, lstm_policy.py:86, and are not needed) */
+
+typedef struct acb200_mlp_policy_weights {
+    const float *pi0_w, *pi0_b, *pi1_w, *pi1_b, *pi2_w, *pi2_b; /* policy_net.0 [256][18], .2 [128][256], .4 [64][128] */
+    const float *action_w, *action_b;                           /* action_net [4][64], [4] */
+} acb200_mlp_policy_weights;
+
+int acb200_policy_create_lstm(acb200_ctx* ctx, const acb200_lstm_policy_weights* w, acb200_policy** out);
+int acb200_policy_create_mlp(acb200_ctx* ctx, const acb200_mlp_policy_weights* w, acb200_policy** out);
+void acb200_policy_destroy(acb200_policy* p);
+/* bytes of the recurrent-state buffers for n aircraft (0, 0 for the MLP policy): h as bf16 tiles, c as f32 tiles */
+int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes, size_t* c_bytes);
+/* obs f32[n][18] (row-major, what acb200_env_step writes), episode_start u8[n] or NULL (state zeroed where set,
+ * sb3-contrib's (1 - episode_start) * state), h_state / c_state device buffers of acb200_policy_state_bytes (updated
+ * in place; NULL for the MLP policy), action_out f32[n][4] clipped to the action space (rate_env.py:128-138). */
+int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
+                          void* h_state, void* c_state, float* action_out);
+/* recurrent state <-> the (n, 256) f32 arrays of SB3's lstm_states; all device pointers */
+int acb200_policy_state_export(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const void* h_state, const void* c_state,
+                               float* h_out, float* c_out);
+int acb200_policy_state_import(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const float* h_in, const float* c_in,
+                               void* h_state, void* c_state);
+/* algorithmic FLOPs (2*M*N*K over the layers as executed) and packed weight bytes per 128-aircraft tile */
+int acb200_policy_info(const acb200_policy* p, double* flops_per_aircraft, size_t* weight_bytes, int* smem_bytes);
+
 /* ---- host-side PID core (the same fp32 arithmetic as the kernels; mirrors PIDController::compute/reset) ---- */
 float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt);
 void acb200_pid_reset(acb200_pid_state* st);
