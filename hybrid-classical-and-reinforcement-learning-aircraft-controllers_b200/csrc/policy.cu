@@ -9,7 +9,7 @@
 // buffer in shared memory (X / Y ping-pong), its accumulator is one of two 256-column tensor-memory buffers, and the
 // epilogue threads (one per aircraft row) turn accumulator columns into the next layer's operand -- bias, ReLU or
 // LSTM gates in fp32 -- while the MMA thread already runs the next chunk into the other buffer.  Weights stream from
-// L2 as prepacked stages through a two-deep bulk-copy ring.  The recurrent state h travels as a ready-made operand
+// L2 as prepacked stages through a three-slot bulk-copy ring; every bias sits in shared memory for the whole chain.  The recurrent state h travels as a ready-made operand
 // tile (one bulk load, one bulk store per tile); c is fp32, read and written by the row's own thread.
 #include <math.h>
 #include <string.h>
@@ -25,11 +25,12 @@ using namespace acbp;
 namespace {
 
 // barrier slots inside the 128-byte barrier block
-enum { B_FULL = 0, B_EMPTY = 2, B_ACC_FULL = 4, B_ACC_EMPTY = 6, B_ACT = 8, B_HFULL = 9, B_COUNT = 10 };
+enum { B_FULL = 0, B_EMPTY = 4, B_ACC_FULL = 8, B_ACC_EMPTY = 10, B_ACT = 12, B_HFULL = 13, B_BIAS = 14, B_COUNT = 15 };
 
 __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __grid_constant__ PolicyParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* act = smem;
+    const float* sbias = reinterpret_cast<const float*>(smem + kBiasOff);
     const uint32_t smem_base = smem_u32(smem);
     const uint32_t bar0 = smem_base + kBarOff;
     auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
@@ -40,20 +41,23 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(bar(B_FULL + s), 1); mbar_init(bar(B_EMPTY + s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kTile); }
-        mbar_init(bar(B_ACT), kTile);
+        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kEpiThreads); }
+        mbar_init(bar(B_ACT), kEpiThreads);
         mbar_init(bar(B_HFULL), 1);
+        mbar_init(bar(B_BIAS), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 5) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    if (warp == kEpiWarps + 1) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 4) {
-        // ================= weight producer: streams the packed stages in consumption order =================
+    if (warp == kEpiWarps) {
+        // ================= producer: biases once, then the packed weight stages in consumption order =================
         if (lane == 0) {
+            mbar_expect_tx(bar(B_BIAS), (uint32_t)P.n_bias * 4u);
+            bulk_g2s(smem_base + kBiasOff, P.bias, (uint32_t)P.n_bias * 4u, bar(B_BIAS));
             const uint8_t* src = P.weights;
             uint32_t it = 0;
             for (int l = 0; l < P.n_layers; ++l) {
@@ -69,7 +73,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 }
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == kEpiWarps + 1) {
         // ================= MMA issuer: one thread drives the tensor core for the whole chain =================
         if (lane == 0) {
             uint32_t it = 0, chunk_it = 0;
@@ -116,14 +120,17 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             if (P.recurrent_layer >= 0) bulk_wait_all();
         }
     } else {
-        // ================= epilogue: thread r owns aircraft row r of the tile =================
-        const int row = threadIdx.x;
+        // ================= epilogue: 8 warps; warp w reads tensor-memory lanes 32*(w%4).., i.e. aircraft row
+        // 32*(w%4)+lane, and takes half (w/4) of every chunk's columns =================
+        const int half = warp >> 2;
+        const int row = (warp & 3) * 32 + lane;
         const int64_t e = tile * kTile + row;
         const bool valid = e < P.n;
         const bool fresh = valid && P.episode_start != nullptr && P.episode_start[e] != 0;
-        const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+        const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
 
-        {   // observation -> X as [hi | lo | hi | 0] bf16 columns (64 wide) against [W_hi | W_hi | W_lo | 0]:
+        if (half == 0) {
+            // observation -> X as [hi | lo | hi | 0] bf16 columns (64 wide) against [W_hi | W_hi | W_lo | 0]:
             // x*W ~ (hi+lo)*W_hi + hi*W_lo keeps 16 mantissa bits of both (altitude ~100 m enters unnormalised)
             float o[ACB200_POLICY_OBS];
             if (valid) {
@@ -151,22 +158,24 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 for (int q = 0; q < 16; ++q) t[q] = col[16 * g + q];
                 store_row16(act, P.L[0].in_off, 16 * g, row, t);
             }
-            fence_async_smem();
-            mbar_arrive(bar(B_ACT));
         }
+        fence_async_smem();
+        mbar_arrive(bar(B_ACT));
+        mbar_wait(bar(B_BIAS), 0, P.error_flag, 700);
 
         uint32_t chunk_it = 0;
         for (int l = 0; l < P.n_layers; ++l) {
             const LayerDesc& L = P.L[l];
             for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
                 const uint32_t a = chunk_it & 1;
-                mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
-                __syncwarp();
-                tc_fence_after();
                 const uint32_t t0 = tmem_base + lane_base + a * 256u;
-                const float* bias = P.bias + L.bias_off + c * L.N_c;
+                const float* bias = sbias + L.bias_off + c * L.N_c;
                 if (L.epi == EPI_RELU) {
-                    for (int j = 0; j < L.N_c; j += 16) {
+                    const int w = L.N_c >> 1, j0 = half * w;
+                    mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
+                    __syncwarp();
+                    tc_fence_after();
+                    for (int j = j0; j < j0 + w; j += 16) {
                         uint32_t v[16]; float b[16], h[16];
                         tmem_ld16_issue(t0 + j, v);
                         load_bias16(bias + j, b);
@@ -177,8 +186,11 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     }
                 } else if (L.epi == EPI_LSTM0) {
                     // h0 = c0 = 0 on every call (lstm_policy.py:86): c = sig(i) tanh(g), h = sig(o) tanh(c); f unused
-                    const int U = L.N_c / 3;
-                    for (int j = 0; j < U; j += 16) {
+                    const int U = L.N_c / 3, w = U >> 1, j0 = half * w;
+                    mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
+                    __syncwarp();
+                    tc_fence_after();
+                    for (int j = j0; j < j0 + w; j += 16) {
                         uint32_t vi[16], vg[16], vo[16]; float bi[16], bg[16], bo[16], h[16];
                         tmem_ld16_issue(t0 + j, vi);
                         tmem_ld16_issue(t0 + U + j, vg);
@@ -187,45 +199,58 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                         tmem_ld_wait(vi); tmem_ld_wait(vg); tmem_ld_wait(vo);
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {
-                            const float cc = sigmoid_fast(__uint_as_float(vi[q]) + bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]);
-                            h[q] = sigmoid_fast(__uint_as_float(vo[q]) + bo[q]) * tanh_fast(cc);
+                            const float cc = sigmoid_half(__uint_as_float(vi[q]), bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]);
+                            h[q] = sigmoid_half(__uint_as_float(vo[q]), bo[q]) * tanh_fast(cc);
                         }
                         store_row16(act, L.out_off, c * U + j, row, h);
                     }
                 } else if (L.epi == EPI_LSTM) {
-                    const int U = L.N_c / 4;
-                    float* cst = P.c_state + (tile * kHidden + (int64_t)c * U) * kTile + row;
-                    for (int j = 0; j < U; j += 16) {
-                        uint32_t vi[16], vf[16], vg[16], vo[16]; float bi[16], bf[16], bg[16], bo[16], h[16], cp[16];
+                    const int U = L.N_c / 4, w = U >> 1, j0 = half * w;   // w == 32 here: two groups of 16 units
+                    float* cst = P.c_state + (tile * kHidden + (int64_t)c * U + j0) * kTile + row;
+                    float cp[32];
+                    const bool carry = valid && !fresh;
+#pragma unroll
+                    for (int q = 0; q < 32; ++q) cp[q] = (carry && q < w) ? cst[(int64_t)q * kTile] : 0.f;   // before the wait
+                    mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
+                    __syncwarp();
+                    tc_fence_after();
+#pragma unroll
+                    for (int g = 0; g < 2; ++g) {
+                        if (g * 16 >= w) break;
+                        const int j = j0 + g * 16;
+                        uint32_t vi[16], vf[16], vg[16], vo[16]; float bi[16], bf[16], bg[16], bo[16], h[16];
                         tmem_ld16_issue(t0 + j, vi);
                         tmem_ld16_issue(t0 + U + j, vf);
                         tmem_ld16_issue(t0 + 2 * U + j, vg);
                         tmem_ld16_issue(t0 + 3 * U + j, vo);
-#pragma unroll
-                        for (int q = 0; q < 16; ++q) cp[q] = (valid && !fresh) ? cst[(int64_t)(j + q) * kTile] : 0.f;
                         load_bias16(bias + j, bi); load_bias16(bias + U + j, bf);
                         load_bias16(bias + 2 * U + j, bg); load_bias16(bias + 3 * U + j, bo);
                         tmem_ld_wait(vi); tmem_ld_wait(vf); tmem_ld_wait(vg); tmem_ld_wait(vo);
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {
-                            const float cn = fmaf(sigmoid_fast(__uint_as_float(vf[q]) + bf[q]), cp[q],
-                                                  sigmoid_fast(__uint_as_float(vi[q]) + bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]));
-                            h[q] = sigmoid_fast(__uint_as_float(vo[q]) + bo[q]) * tanh_fast(cn);
-                            if (valid) cst[(int64_t)(j + q) * kTile] = cn;
+                            const float cn = fmaf(sigmoid_half(__uint_as_float(vf[q]), bf[q]), cp[g * 16 + q],
+                                                  sigmoid_half(__uint_as_float(vi[q]), bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]));
+                            h[q] = sigmoid_half(__uint_as_float(vo[q]), bo[q]) * tanh_fast(cn);
+                            if (valid) cst[(int64_t)(g * 16 + q) * kTile] = cn;
                         }
                         store_row16(act, L.out_off, c * U + j, row, h);
                     }
                 } else {   // EPI_HEAD: mean action, clipped to the action space (rate_env.py:128-138)
-                    uint32_t v[16];
-                    tmem_ld16_issue(t0, v);
-                    tmem_ld_wait(v);
-                    if (valid) {
-                        float4 o;
-                        o.x = fminf(fmaxf(__uint_as_float(v[0]) + __ldg(bias + 0), -1.f), 1.f);
-                        o.y = fminf(fmaxf(__uint_as_float(v[1]) + __ldg(bias + 1), -1.f), 1.f);
-                        o.z = fminf(fmaxf(__uint_as_float(v[2]) + __ldg(bias + 2), -1.f), 1.f);
-                        o.w = fminf(fmaxf(__uint_as_float(v[3]) + __ldg(bias + 3), 0.f), 1.f);
-                        reinterpret_cast<float4*>(P.action)[e] = o;
+                    mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
+                    __syncwarp();
+                    tc_fence_after();
+                    if (half == 0) {
+                        uint32_t v[16];
+                        tmem_ld16_issue(t0, v);
+                        tmem_ld_wait(v);
+                        if (valid) {
+                            float4 o;
+                            o.x = fminf(fmaxf(__uint_as_float(v[0]) + bias[0], -1.f), 1.f);
+                            o.y = fminf(fmaxf(__uint_as_float(v[1]) + bias[1], -1.f), 1.f);
+                            o.z = fminf(fmaxf(__uint_as_float(v[2]) + bias[2], -1.f), 1.f);
+                            o.w = fminf(fmaxf(__uint_as_float(v[3]) + bias[3], 0.f), 1.f);
+                            reinterpret_cast<float4*>(P.action)[e] = o;
+                        }
                     }
                 }
                 tc_fence_before();
@@ -236,7 +261,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 mbar_wait(bar(B_HFULL), 0, P.error_flag, 600);
                 if (fresh || !valid) {
                     const uint4 z = make_uint4(0, 0, 0, 0);
-                    for (int kc = 0; kc < kHidden / 8; ++kc)
+                    for (int kc = half * (kHidden / 16); kc < (half + 1) * (kHidden / 16); ++kc)
                         *reinterpret_cast<uint4*>(act + kHOff + (uint32_t)kc * kKChunkBytes + (uint32_t)row * 16) = z;
                 }
             }
@@ -247,7 +272,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) {
+    if (warp == kEpiWarps + 1) {
         __syncwarp();
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
@@ -348,7 +373,7 @@ HostLayer lstm_layer(bool stateful, const float* W_ih, const float* W_hh, const 
                      uint32_t in_off, uint32_t out_off) {
     const int gates = stateful ? 4 : 3, K = stateful ? in + kHidden : in;
     static const int kStateless[3] = {0, 2, 3};
-    HostLayer h = make_layer(stateful ? EPI_LSTM : EPI_LSTM0, K, 64, gates * U, kHidden / U, in_off, out_off);
+    HostLayer h = make_layer(stateful ? EPI_LSTM : EPI_LSTM0, K, 32, gates * U, kHidden / U, in_off, out_off);
     for (int c = 0; c < kHidden / U; ++c)
         for (int g = 0; g < gates; ++g)
             for (int u = 0; u < U; ++u) {
@@ -357,10 +382,21 @@ HostLayer lstm_layer(bool stateful, const float* W_ih, const float* W_hh, const 
                 for (int k = 0; k < in; ++k) h.w[dst * K + k] = W_ih[(size_t)src * in + k];
                 if (stateful)
                     for (int k = 0; k < kHidden; ++k) h.w[dst * K + in + k] = W_hh[(size_t)src * kHidden + k];
-                h.b[dst] = b_ih[src] + b_hh[src];
+                const bool sigmoid_gate = (stateful ? g : kStateless[g]) != 2;        // i, f, o; g is the tanh gate
+                h.b[dst] = (sigmoid_gate ? 0.5f : 1.0f) * (b_ih[src] + b_hh[src]);   // see sigmoid_half()
             }
     h.real_flops = 2.0 * gates * kHidden * K;
     return h;
+}
+
+int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& layers, acb200_policy** out);
+
+int build_policy(acb200_ctx* ctx, int kind, std::vector<HostLayer>& layers, acb200_policy** out) {
+    acb200_policy* p = new acb200_policy();
+    p->kind = kind;
+    const int rc = finish_policy(ctx, p, layers, out);
+    if (rc != ACB200_OK) acb200_policy_destroy(p);
+    return rc;
 }
 
 int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& layers, acb200_policy** out) {
@@ -377,6 +413,8 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         d.bias_off = (int)bias.size();
         bias.insert(bias.end(), h.b.begin(), h.b.end());
         if (d.epi == EPI_LSTM) p->params.recurrent_layer = (int)l;
+        if ((d.epi == EPI_LSTM && d.N_c != 256) || (d.epi == EPI_LSTM0 && d.N_c % 96) || (d.epi == EPI_RELU && d.N_c % 32))
+            return pfail(ctx, ACB200_EVALUE, "policy: chunk width does not split over the two epilogue halves");
         for (int c = 0; c < d.n_chunks; ++c)
             for (int ks = 0; ks < d.K / d.K_s; ++ks)
                 for (int kk = 0; kk < d.K_s / 8; ++kk)
@@ -386,6 +424,9 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         p->params.L[l] = d;
         p->flops_per_aircraft += h.real_flops;
     }
+    while (bias.size() % 4) bias.push_back(0.f);   // bulk copies move multiples of 16 bytes
+    if (bias.size() > (size_t)kMaxBias) return pfail(ctx, ACB200_EVALUE, "policy: too many bias values");
+    p->params.n_bias = (int)bias.size();
     p->weight_bytes = packed.size() * 2;
     p->device = ctx->device;
     cudaSetDevice(ctx->device);
@@ -397,7 +438,6 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         (e = cudaMemcpy(p->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMemset(p->d_error, 0, sizeof(int))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess) {
-        acb200_policy_destroy(p);
         return pfail(ctx, ACB200_ECUDA, std::string("policy upload: ") + cudaGetErrorString(e));
     }
     p->params.weights = p->d_weights;
@@ -421,14 +461,12 @@ int acb200_policy_create_lstm(acb200_ctx* ctx, const acb200_lstm_policy_weights*
     L.push_back(dense_layer(EPI_RELU, w->embed_w, w->embed_b, 128, ACB200_POLICY_OBS, 128, 64, 64, X, Y, true));
     L.push_back(lstm_layer(false, w->l0_w_ih, nullptr, w->l0_b_ih, w->l0_b_hh, 128, 64, Y, X));
     L.push_back(lstm_layer(false, w->l1_w_ih, nullptr, w->l1_b_ih, w->l1_b_hh, 256, 64, X, Y));
-    L.push_back(dense_layer(EPI_RELU, w->proj_w, w->proj_b, 128, 256, 128, 256, 128, Y, X, false));
+    L.push_back(dense_layer(EPI_RELU, w->proj_w, w->proj_b, 128, 256, 128, 256, 64, Y, X, false));
     L.push_back(lstm_layer(true, w->actor_w_ih, w->actor_w_hh, w->actor_b_ih, w->actor_b_hh, 128, 64, X, Y));
-    L.push_back(dense_layer(EPI_RELU, w->pi0_w, w->pi0_b, 128, 256, 128, 256, 128, Y, X, false));
+    L.push_back(dense_layer(EPI_RELU, w->pi0_w, w->pi0_b, 128, 256, 128, 256, 64, Y, X, false));
     L.push_back(dense_layer(EPI_RELU, w->pi1_w, w->pi1_b, 64, 128, 64, 128, 128, X, X2, false));
     L.push_back(dense_layer(EPI_HEAD, w->action_w, w->action_b, ACB200_POLICY_ACT, 64, 16, 64, 64, X2, X, false));
-    acb200_policy* p = new acb200_policy();
-    p->kind = ACB200_POLICY_LSTM;
-    return finish_policy(ctx, p, L, out);
+    return build_policy(ctx, ACB200_POLICY_LSTM, L, out);
 }
 
 int acb200_policy_create_mlp(acb200_ctx* ctx, const acb200_mlp_policy_weights* w, acb200_policy** out) {
@@ -438,13 +476,11 @@ int acb200_policy_create_mlp(acb200_ctx* ctx, const acb200_mlp_policy_weights* w
         if (!ptrs[i]) return pfail(ctx, ACB200_ENULL, "policy: NULL weight pointer");
     const uint32_t X = 0, Y = kXBytes, X2 = kHOff;
     std::vector<HostLayer> L;
-    L.push_back(dense_layer(EPI_RELU, w->pi0_w, w->pi0_b, 256, ACB200_POLICY_OBS, 256, 64, 64, X, Y, true));
-    L.push_back(dense_layer(EPI_RELU, w->pi1_w, w->pi1_b, 128, 256, 128, 256, 128, Y, X, false));
+    L.push_back(dense_layer(EPI_RELU, w->pi0_w, w->pi0_b, 256, ACB200_POLICY_OBS, 256, 64, 32, X, Y, true));
+    L.push_back(dense_layer(EPI_RELU, w->pi1_w, w->pi1_b, 128, 256, 128, 256, 64, Y, X, false));
     L.push_back(dense_layer(EPI_RELU, w->pi2_w, w->pi2_b, 64, 128, 64, 128, 128, X, X2, false));
     L.push_back(dense_layer(EPI_HEAD, w->action_w, w->action_b, ACB200_POLICY_ACT, 64, 16, 64, 64, X2, X, false));
-    acb200_policy* p = new acb200_policy();
-    p->kind = ACB200_POLICY_MLP;
-    return finish_policy(ctx, p, L, out);
+    return build_policy(ctx, ACB200_POLICY_MLP, L, out);
 }
 
 void acb200_policy_destroy(acb200_policy* p) {

@@ -17,18 +17,22 @@ namespace acbp {
 
 constexpr int kTile = 128;               // aircraft per CTA == UMMA M == tensor-memory lanes
 constexpr int kMaxLayers = 8;
-constexpr int kStages = 2;               // weight ring depth
-constexpr uint32_t kStageBytes = 32768;
+constexpr int kStages = 3;               // weight ring depth
+constexpr uint32_t kStageBytes = 16384;
 constexpr uint32_t kXBytes = 98304;      // activation buffer X: up to K = 384 (features 128 | h 256)
 constexpr uint32_t kYBytes = 65536;      // activation buffer Y: up to K = 256
-constexpr uint32_t kStageOff = kXBytes + kYBytes;
+constexpr int kMaxBias = 3072;           // every layer's bias, fp32, resident for the whole chain
+constexpr uint32_t kBiasOff = kXBytes + kYBytes;
+constexpr uint32_t kStageOff = kBiasOff + kMaxBias * 4;
 constexpr uint32_t kBarOff = kStageOff + kStages * kStageBytes;
-constexpr uint32_t kSmemBytes = kBarOff + 128;
+constexpr uint32_t kSmemBytes = kBarOff + 256;
 constexpr uint32_t kKChunkBytes = kTile * 16;   // one 8-wide K slab of an activation buffer (2048 B)
 constexpr int kHidden = 256;
 constexpr uint32_t kHTileBytes = kHidden * kTile * 2;   // one tile of h, bf16, already in operand layout
 constexpr uint32_t kHOff = 16 * kKChunkBytes;           // h sits behind the 128 feature columns in X
-constexpr int kThreads = 192;            // warps 0-3 epilogue (row = thread), warp 4 weight producer, warp 5 MMA issuer
+constexpr int kEpiWarps = 8;             // two warps per tensor-memory lane quarter: each takes half of a chunk's columns
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = kEpiThreads + 64;   // + warp 8: weight producer, warp 9: MMA issuer
 constexpr uint32_t kTmemCols = 512;      // two accumulator buffers of 256 fp32 columns
 
 enum Epilogue : int { EPI_RELU = 0, EPI_LSTM0 = 1, EPI_LSTM = 2, EPI_HEAD = 3 };
@@ -48,7 +52,8 @@ struct PolicyParams {
     int recurrent_layer;      // index of the EPI_LSTM layer, -1 if none
     LayerDesc L[kMaxLayers];
     const uint8_t* weights;   // packed stages in consumption order
-    const float* bias;
+    const float* bias;        // [n_bias] in execution order; sigmoid gates hold 0.5 * b
+    int n_bias;
     const float* obs;         // [n][18]
     const uint8_t* episode_start;
     uint8_t* h_state;         // [tiles][32][128][8] bf16
@@ -84,9 +89,12 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // Bounded wait: a protocol bug must end as a trapped kernel with a code in *err, not as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* err, int code) {
     if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
+    long long t0 = 0;
+    uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 4000000000LL) {   // about two seconds
+        if ((++spins & 0xFFFu) != 0) continue;
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 4000000000LL) {   // about two seconds
             if (err) *err = code;
             __threadfence_system();
             __trap();
@@ -165,7 +173,8 @@ __device__ __forceinline__ float tanh_fast(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+// sigmoid(z) with z = 2 * (0.5 * acc + 0.5 * b): the bias array holds 0.5 * b for these gates, so one FFMA feeds the MUFU
+__device__ __forceinline__ float sigmoid_half(float acc, float half_b) { return fmaf(0.5f, tanh_fast(fmaf(acc, 0.5f, half_b)), 0.5f); }
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
@@ -179,11 +188,11 @@ __device__ __forceinline__ void store_row16(uint8_t* act, uint32_t out_off, int 
     *reinterpret_cast<uint4*>(p) = a;
     *reinterpret_cast<uint4*>(p + kKChunkBytes) = b;
 }
-__device__ __forceinline__ void load_bias16(const float* b, float (&out)[16]) {
+__device__ __forceinline__ void load_bias16(const float* b, float (&out)[16]) {   // shared memory, warp-uniform address
     const float4* p = reinterpret_cast<const float4*>(b);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-        const float4 t = __ldg(p + q);
+        const float4 t = p[q];
         out[4 * q] = t.x; out[4 * q + 1] = t.y; out[4 * q + 2] = t.z; out[4 * q + 3] = t.w;
     }
 }

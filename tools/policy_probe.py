@@ -45,6 +45,9 @@ def bench(kind, n, iters=20):
     print(f"bench {kind} n={n}: {ms:.3f} ms/forward, {n/ms*1e3:.3e} aircraft/s, {fl/ms/1e9:.1f} TFLOP/s", flush=True)
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "bench":
+        bench("lstm", 262144, iters=int(sys.argv[2]) if len(sys.argv) > 2 else 5)
+        sys.exit(0)
     run("mlp", 128); run("mlp", 300)
     run("lstm", 128); run("lstm", 300, steps=5); run("lstm", 640, scale=2.5, steps=5)
     bench("mlp", 262144); bench("lstm", 262144)
