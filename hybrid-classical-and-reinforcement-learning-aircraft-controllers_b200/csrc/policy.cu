@@ -12,6 +12,8 @@
 // L2 as prepacked stages through a three-slot bulk-copy ring; every bias sits in shared memory for the whole chain.  The recurrent state h travels as a ready-made operand
 // tile (one bulk load, one bulk store per tile); c is fp32, read and written by the row's own thread.
 #include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -36,7 +38,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
     auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kBarOff + 8 * B_COUNT);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     const int64_t tile = blockIdx.x;
 
     if (threadIdx.x == 0) {
@@ -67,6 +69,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 for (int i = 0; i < n_stage; ++i, ++it) {
                     const uint32_t s = it % kStages, use = it / kStages;
                     if (use > 0) mbar_wait(bar(B_EMPTY + s), (use - 1) & 1, P.error_flag, 100 + l);
+                    if (P.debug & 1) { mbar_arrive(bar(B_FULL + s)); continue; }
                     mbar_expect_tx(bar(B_FULL + s), bytes);
                     bulk_g2s(smem_base + kStageOff + s * kStageBytes, src, bytes, bar(B_FULL + s));
                     src += bytes;
@@ -74,51 +77,71 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             }
         }
     } else if (warp == kEpiWarps + 1) {
-        // ================= MMA issuer: one thread drives the tensor core for the whole chain =================
-        if (lane == 0) {
-            uint32_t it = 0, chunk_it = 0;
-            for (int l = 0; l < P.n_layers; ++l) {
-                const LayerDesc& L = P.L[l];
-                mbar_wait(bar(B_ACT), l & 1, P.error_flag, 200 + l);       // operand of layer l is complete
-                if (P.recurrent_layer >= 0) {
-                    if (l == P.recurrent_layer - 1) {                      // X's h region is idle from here on
-                        mbar_expect_tx(bar(B_HFULL), kHTileBytes);
-                        bulk_g2s(smem_base + kHOff, P.h_state + tile * (int64_t)kHTileBytes, kHTileBytes, bar(B_HFULL));
-                    }
-                    if (l == P.recurrent_layer + 1) {                      // Y holds h' as a finished operand tile
-                        bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
-                        bulk_commit();
-                    }
+        // ================= MMA issuer: the whole warp walks the chain (so that addresses and descriptors stay in
+        // uniform registers); one elected lane issues the tensor-core instructions =================
+        const bool leader = lane == 0;
+        uint32_t slot = 0, slot_phase = 0, chunk_it = 0;
+        const bool tr = (P.debug & 4) && blockIdx.x == 0 && leader;
+        int ti = 0;
+        if (tr) P.trace[ti++] = clock64();
+        for (int l = 0; l < P.n_layers; ++l) {
+            const LayerDesc& L = P.L[l];
+            mbar_wait(bar(B_ACT), l & 1, P.error_flag, 200 + l);       // operand of layer l is complete
+            if (tr) P.trace[ti++] = clock64();
+            if (P.recurrent_layer >= 0 && leader) {
+                if (l == P.recurrent_layer - 1) {                      // X's h region is idle from here on
+                    mbar_expect_tx(bar(B_HFULL), kHTileBytes);
+                    bulk_g2s(smem_base + kHOff, P.h_state + tile * (int64_t)kHTileBytes, kHTileBytes, bar(B_HFULL));
                 }
-                tc_fence_after();
-                const uint32_t idesc = instr_desc_bf16(L.N_c);
-                const uint32_t lbo_b = (uint32_t)L.N_c * 16u;
-                const int stages_per_chunk = L.K / L.K_s, mma_per_stage = L.K_s / 16;
-                for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
-                    const uint32_t a = chunk_it & 1, use = chunk_it >> 1;
-                    if (use > 0) {
-                        mbar_wait(bar(B_ACC_EMPTY + a), (use - 1) & 1, P.error_flag, 300 + l);
-                        tc_fence_after();
-                    }
-                    const uint32_t d_tmem = tmem_base + a * 256u;
-                    for (int ks = 0; ks < stages_per_chunk; ++ks, ++it) {
-                        const uint32_t s = it % kStages;
-                        mbar_wait(bar(B_FULL + s), (it / kStages) & 1, P.error_flag, 400 + l);
-                        tc_fence_after();
-                        const uint32_t a_addr = smem_base + L.in_off + (uint32_t)(ks * L.K_s / 8) * kKChunkBytes;
-                        const uint32_t b_addr = smem_base + kStageOff + s * kStageBytes;
-                        for (int k = 0; k < mma_per_stage; ++k) {
-                            const uint64_t ad = smem_desc(a_addr + (uint32_t)k * 2u * kKChunkBytes, kKChunkBytes, 128);
-                            const uint64_t bd = smem_desc(b_addr + (uint32_t)k * 2u * lbo_b, lbo_b, 128);
-                            umma_bf16(d_tmem, ad, bd, idesc, (ks | k) != 0);
-                        }
-                        umma_commit(bar(B_EMPTY + s));                   // stage free once these MMAs have read it
-                    }
-                    umma_commit(bar(B_ACC_FULL + a));                    // accumulator chunk complete
+                if (l == P.recurrent_layer + 1) {                      // Y holds h' as a finished operand tile
+                    bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
+                    bulk_commit();
                 }
             }
-            if (P.recurrent_layer >= 0) bulk_wait_all();
+            tc_fence_after();
+            const uint32_t idesc = instr_desc_bf16(L.N_c);
+            const uint32_t lbo_b = (uint32_t)L.N_c * 16u;
+            const int stages_per_chunk = L.K / L.K_s, mma_per_stage = L.K_s / 16;
+            // descriptors advance in their low word only (addresses stay below 2^18): +2 K slabs per MMA
+            const uint64_t a_desc0 = smem_desc(smem_base + L.in_off, kKChunkBytes, 128);
+            const uint64_t b_desc0 = smem_desc(smem_base + kStageOff, lbo_b, 128);
+            const uint32_t a_step = (2u * kKChunkBytes) >> 4, b_step = (2u * lbo_b) >> 4;
+            for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
+                const uint32_t a = chunk_it & 1, use = chunk_it >> 1;
+                if (use > 0) {
+                    mbar_wait(bar(B_ACC_EMPTY + a), (use - 1) & 1, P.error_flag, 300 + l);
+                    tc_fence_after();
+                }
+                if (tr) P.trace[ti++] = clock64();
+                const uint32_t d_tmem = tmem_base + a * 256u;
+                uint64_t a_desc = a_desc0;
+                uint32_t accumulate = 0;
+                for (int ks = 0; ks < stages_per_chunk; ++ks) {
+                    mbar_wait(bar(B_FULL + slot), slot_phase, P.error_flag, 400 + l);
+                    tc_fence_after();
+                    if (leader) {
+                        uint64_t b_desc = b_desc0 + (uint64_t)(slot * (kStageBytes >> 4));
+                        if (mma_per_stage == 2) {
+#pragma unroll
+                            for (int k = 0; k < 2; ++k) { umma_bf16(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
+                        } else if (mma_per_stage == 4) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) { umma_bf16(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
+                        } else {
+                            for (int k = 0; k < mma_per_stage; ++k) { umma_bf16(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
+                        }
+                        umma_commit(bar(B_EMPTY + slot));            // stage free once these MMAs have read it
+                    }
+                    __syncwarp();
+                    a_desc += (uint64_t)(mma_per_stage * a_step);
+                    accumulate = 1;
+                    if (++slot == kStages) { slot = 0; slot_phase ^= 1; }
+                }
+                if (leader) umma_commit(bar(B_ACC_FULL + a));        // accumulator chunk complete
+                if (tr) P.trace[ti++] = clock64();
+            }
         }
+        if (P.recurrent_layer >= 0 && leader) bulk_wait_all();
     } else {
         // ================= epilogue: 8 warps; warp w reads tensor-memory lanes 32*(w%4).., i.e. aircraft row
         // 32*(w%4)+lane, and takes half (w/4) of every chunk's columns =================
@@ -164,13 +187,21 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         mbar_wait(bar(B_BIAS), 0, P.error_flag, 700);
 
         uint32_t chunk_it = 0;
+        const bool tr = (P.debug & 4) && blockIdx.x == 0 && threadIdx.x == 0;
+        int ti = 1024;
+        if (tr) P.trace[ti++] = clock64();
         for (int l = 0; l < P.n_layers; ++l) {
             const LayerDesc& L = P.L[l];
             for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
                 const uint32_t a = chunk_it & 1;
                 const uint32_t t0 = tmem_base + lane_base + a * 256u;
+                if (tr) P.trace[ti++] = clock64();
                 const float* bias = sbias + L.bias_off + c * L.N_c;
-                if (L.epi == EPI_RELU) {
+                if (P.debug & 2) {
+                    mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
+                    __syncwarp();
+                    tc_fence_after();
+                } else if (L.epi == EPI_RELU) {
                     const int w = L.N_c >> 1, j0 = half * w;
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
@@ -255,6 +286,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 }
                 tc_fence_before();
                 mbar_arrive(bar(B_ACC_EMPTY + a));
+                if (tr) P.trace[ti++] = clock64();
             }
             if (l == P.recurrent_layer - 1) {
                 // h_prev has landed behind the features; a fresh episode starts from zeros ((1 - episode_start) * h)
@@ -516,11 +548,26 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
     P.obs = obs; P.episode_start = episode_start;
     P.h_state = static_cast<uint8_t*>(h_state); P.c_state = static_cast<float*>(c_state);
     P.action = action_out; P.n = n;
+    static const int debug = getenv("ACB200_POLICY_DEBUG") ? atoi(getenv("ACB200_POLICY_DEBUG")) : 0;
+    P.debug = debug;
+    static long long* trace = nullptr;
+    if ((debug & 4) && !trace) { cudaMalloc(&trace, 2048 * sizeof(long long)); cudaMemset(trace, 0, 2048 * sizeof(long long)); }
+    P.trace = trace;
     const int64_t tiles = (n + kTile - 1) / kTile;
     policy_forward_kernel<<<(unsigned)tiles, kThreads, kSmemBytes, ctx->stream>>>(P);
     ctx->launches += 1;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return pfail(ctx, ACB200_ECUDA, std::string("policy_forward_kernel: ") + cudaGetErrorString(e));
+    if ((debug & 4) && getenv("ACB200_POLICY_TRACE")) {   // development aid: dump block 0's time line
+        static int dumped = 0;
+        if (dumped++ == 3) {
+            std::vector<long long> h(2048);
+            cudaStreamSynchronize(ctx->stream);
+            cudaMemcpy(h.data(), trace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
+            FILE* f = fopen(getenv("ACB200_POLICY_TRACE"), "w");
+            if (f) { for (size_t i = 0; i < h.size(); ++i) if (h[i]) fprintf(f, "%zu %lld\n", i, h[i]); fclose(f); }
+        }
+    }
     return ACB200_OK;
 }
 

@@ -61,6 +61,8 @@ struct PolicyParams {
     float* action;            // [n][4]
     int64_t n;
     int* error_flag;
+    long long* trace;         // debug & 4: clock64 stamps of block 0 ([0..1023] MMA thread, [1024..2047] epilogue thread 0)
+    int debug;                // timing experiments only (ACB200_POLICY_DEBUG): 1 = no weight traffic, 2 = no gate math
 };
 
 // ---- shared-memory addresses, mbarriers -------------------------------------------------------------------------
