@@ -322,7 +322,18 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=50)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4"],
+                    help="c3 (default, BASELINE metric): 2^20 aircraft, cascaded PID; c4: 262144 aircraft, learned LSTM policy")
+    ap.add_argument("--ref-envs-c4", type=int, default=4096, help="aircraft in the bounded CPU sample of --workload c4")
     args = ap.parse_args()
+    if args.workload == "c4":
+        from tools import bench_c4
+        if args.envs == 1 << 20:
+            args.envs = 262144
+        args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+        if args.steps == 1000:
+            args.steps = 200 if args.impl == "b200" else 5
+        return bench_c4.run_reference(args) if args.impl == "reference" else bench_c4.run_gpu(args, ROOT, ClockSampler)
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args)

@@ -147,7 +147,7 @@ def load() -> C.CDLL:
     L.acb200_policy_create_mlp.argtypes = [vp, P(MlpPolicyWeightsC), P(vp)]
     L.acb200_policy_destroy.argtypes = [vp]; L.acb200_policy_destroy.restype = None
     L.acb200_policy_state_bytes.argtypes = [vp, i64, P(C.c_size_t), P(C.c_size_t)]
-    L.acb200_policy_forward.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp]
+    L.acb200_policy_forward.argtypes = [vp, vp, i64, vp, vp, vp, vp, vp, vp]
     L.acb200_policy_state_export.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     L.acb200_policy_state_import.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     L.acb200_policy_info.argtypes = [vp, P(dbl), P(C.c_size_t), P(i32)]

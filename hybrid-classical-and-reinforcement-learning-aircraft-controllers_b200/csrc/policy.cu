@@ -149,7 +149,8 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         const int row = (warp & 3) * 32 + lane;
         const int64_t e = tile * kTile + row;
         const bool valid = e < P.n;
-        const bool fresh = valid && P.episode_start != nullptr && P.episode_start[e] != 0;
+        const bool fresh = valid && ((P.episode_start != nullptr && P.episode_start[e] != 0) ||
+                                     (P.episode_start_b != nullptr && P.episode_start_b[e] != 0));
         const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
 
         if (half == 0) {
@@ -535,7 +536,7 @@ int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes
 }
 
 int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
-                          void* h_state, void* c_state, float* action_out) {
+                          const uint8_t* episode_start_b, void* h_state, void* c_state, float* action_out) {
     if (!ctx || !p || !obs || !action_out) return pfail(ctx, ACB200_ENULL, "policy_forward: NULL argument");
     if (n < 0) return pfail(ctx, ACB200_EVALUE, "policy_forward: n < 0");
     if (n == 0) return ACB200_OK;
@@ -545,7 +546,7 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
         return pfail(ctx, ACB200_EVALUE, "policy_forward: misaligned buffer");
     cudaSetDevice(ctx->device);
     PolicyParams P = p->params;
-    P.obs = obs; P.episode_start = episode_start;
+    P.obs = obs; P.episode_start = episode_start; P.episode_start_b = episode_start_b;
     P.h_state = static_cast<uint8_t*>(h_state); P.c_state = static_cast<float*>(c_state);
     P.action = action_out; P.n = n;
     static const int debug = getenv("ACB200_POLICY_DEBUG") ? atoi(getenv("ACB200_POLICY_DEBUG")) : 0;

@@ -55,7 +55,8 @@ struct PolicyParams {
     const float* bias;        // [n_bias] in execution order; sigmoid gates hold 0.5 * b
     int n_bias;
     const float* obs;         // [n][18]
-    const uint8_t* episode_start;
+    const uint8_t* episode_start;     // either flag set: fresh episode
+    const uint8_t* episode_start_b;
     uint8_t* h_state;         // [tiles][32][128][8] bf16
     float* c_state;           // [tiles][256][128]
     float* action;            // [n][4]

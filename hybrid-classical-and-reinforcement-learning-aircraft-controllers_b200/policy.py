@@ -102,22 +102,30 @@ class LearnedPolicyB200:
         if self.recurrent:
             self.h_state.zero_(); self.c_state.zero_()
 
-    def forward(self, obs: torch.Tensor, episode_start: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
-        """obs: CUDA f32 [n, 18] (``BatchedRateControlEnv.obs``); episode_start: CUDA u8/bool [n] or None.
+    def _flags(self, t):
+        if t is None:
+            return None
+        t = t if t.dtype == torch.uint8 else t.to(torch.uint8)
+        if not (t.is_cuda and t.is_contiguous() and t.numel() == self.n):
+            raise ValueError("episode_start must be a contiguous CUDA tensor of n flags")
+        return t
+
+    def forward(self, obs: torch.Tensor, episode_start=None, out: Optional[torch.Tensor] = None):
+        """obs: CUDA f32 [n, 18] (``BatchedRateControlEnv.obs``); episode_start: CUDA u8/bool [n], a pair of them
+        (the env's ``terminated`` and ``truncated``: a fresh episode where either is set) or None.
         Returns the clipped mean action, CUDA f32 [n, 4]; the recurrent state advances in place."""
         if not (obs.is_cuda and obs.dtype == torch.float32 and obs.is_contiguous() and tuple(obs.shape) == (self.n, OBS_DIM)):
             raise ValueError(f"obs must be a contiguous CUDA float32 tensor of shape ({self.n}, {OBS_DIM})")
-        es = None
-        if episode_start is not None:
-            es = episode_start if episode_start.dtype == torch.uint8 else episode_start.to(torch.uint8)
-            if not (es.is_cuda and es.is_contiguous() and es.numel() == self.n):
-                raise ValueError("episode_start must be a contiguous CUDA tensor of n flags")
+        if isinstance(episode_start, (tuple, list)):
+            es, es_b = self._flags(episode_start[0]), self._flags(episode_start[1])
+        else:
+            es, es_b = self._flags(episode_start), None
         out = self.action if out is None else out
         if not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and tuple(out.shape) == (self.n, ACT_DIM)):
             raise ValueError(f"out must be a contiguous CUDA float32 tensor of shape ({self.n}, {ACT_DIM})")
         self.ctx.check(self.lib.acb200_policy_forward(
             self.ctx.handle, self.handle, self.n, obs.data_ptr(), es.data_ptr() if es is not None else None,
-            self.h_state.data_ptr() if self.recurrent else None, self.c_state.data_ptr() if self.recurrent else None,
+            es_b.data_ptr() if es_b is not None else None, self.h_state.data_ptr() if self.recurrent else None, self.c_state.data_ptr() if self.recurrent else None,
             out.data_ptr()))
         return out
 
@@ -160,3 +168,36 @@ class LearnedPolicyB200:
             self.close()
         except Exception:
             pass
+
+
+def random_policy_state_dict(kind: str = "lstm", seed: int = 0) -> dict:
+    """Random-init weights of the reference architectures (torch's default initialisers under ``manual_seed(seed)``)
+    under stable-baselines3 parameter names -- BASELINE.json C4 ("random-init policy, torch seed 0"); there is no
+    checkpoint to load on a machine without network.  Only the initial values are drawn here; no arithmetic of the
+    forward path runs in torch."""
+    import torch.nn as nn
+    g = torch.random.get_rng_state()
+    torch.manual_seed(seed)
+    sd = {}
+
+    def put(prefix, mod):
+        for k, v in mod.state_dict().items():
+            sd[f"{prefix}.{k}"] = v.detach().clone()
+
+    if kind == "lstm":
+        put("features_extractor.embedding.0", nn.Linear(OBS_DIM, 128))
+        put("features_extractor.lstm", nn.LSTM(128, HIDDEN, num_layers=2, batch_first=True))
+        put("features_extractor.output_proj.0", nn.Linear(HIDDEN, 128))
+        put("lstm_actor", nn.LSTM(128, HIDDEN, num_layers=1))
+        put("mlp_extractor.policy_net.0", nn.Linear(HIDDEN, 128))
+        put("mlp_extractor.policy_net.2", nn.Linear(128, 64))
+        put("action_net", nn.Linear(64, ACT_DIM))
+    elif kind == "mlp":
+        put("mlp_extractor.policy_net.0", nn.Linear(OBS_DIM, 256))
+        put("mlp_extractor.policy_net.2", nn.Linear(256, 128))
+        put("mlp_extractor.policy_net.4", nn.Linear(128, 64))
+        put("action_net", nn.Linear(64, ACT_DIM))
+    else:
+        raise ValueError(f"unknown policy kind {kind!r}")
+    torch.random.set_rng_state(g)
+    return sd

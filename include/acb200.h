@@ -268,11 +268,12 @@ int acb200_policy_create_mlp(acb200_ctx* ctx, const acb200_mlp_policy_weights* w
 void acb200_policy_destroy(acb200_policy* p);
 /* bytes of the recurrent-state buffers for n aircraft (0, 0 for the MLP policy): h as bf16 tiles, c as f32 tiles */
 int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes, size_t* c_bytes);
-/* obs f32[n][18] (row-major, what acb200_env_step writes), episode_start u8[n] or NULL (state zeroed where set,
- * sb3-contrib's (1 - episode_start) * state), h_state / c_state device buffers of acb200_policy_state_bytes (updated
- * in place; NULL for the MLP policy), action_out f32[n][4] clipped to the action space (rate_env.py:128-138). */
+/* obs f32[n][18] (row-major, what acb200_env_step writes); episode_start / episode_start_b u8[n] or NULL: the state is
+ * zeroed where EITHER is set (sb3-contrib's (1 - episode_start) * state; two arrays so that the env's terminated and
+ * truncated outputs can be passed as they are); h_state / c_state device buffers of acb200_policy_state_bytes (updated
+ * in place; NULL for the MLP policy); action_out f32[n][4] clipped to the action space (rate_env.py:128-138). */
 int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
-                          void* h_state, void* c_state, float* action_out);
+                          const uint8_t* episode_start_b, void* h_state, void* c_state, float* action_out);
 /* recurrent state <-> the (n, 256) f32 arrays of SB3's lstm_states; all device pointers */
 int acb200_policy_state_export(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const void* h_state, const void* c_state,
                                float* h_out, float* c_out);

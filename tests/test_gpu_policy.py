@@ -120,3 +120,30 @@ def test_argument_errors():
         acb200.LearnedPolicyB200({}, kind="lstm", n=8)
     with pytest.raises(ValueError):
         acb200.LearnedPolicyB200(net.state_dict(), kind="gru", n=8)
+
+
+def test_policy_env_closed_loop_vs_oracle():
+    """C4 in small: the device policy flies the device env; the torch oracle policy flies the C oracle env, both
+    from the same Philox resets.  The loop is a feedback system, so the bar is per step on re-synchronised inputs:
+    every step the device action is compared with the oracle policy's action ON THE DEVICE'S OWN observation and
+    state (LSTM bar), and the fleet keeps flying (finite observations, episodes end and restart)."""
+    import acb200
+    n = 512
+    net = po.make_policy("lstm", seed=0)
+    env = acb200.BatchedRateControlEnv(n, difficulty="medium", controller="external", precision=64, seed=42, episode_length=1.0)
+    pol = acb200.LearnedPolicyB200(net.state_dict(), kind="lstm", n=n, ctx=env.ctx)
+    env.reset()
+    worst, restarts = 0.0, 0
+    for t in range(120):
+        h, c = pol.get_lstm_states()
+        obs = env.obs.clone()
+        flags = (env.terminated.clone(), env.truncated.clone())
+        act = pol(obs, (env.terminated, env.truncated)).clone()
+        es = (flags[0] | flags[1]).bool().cpu()
+        ref, _ = net(obs.cpu(), (torch.from_numpy(h[0].copy()), torch.from_numpy(c[0].copy())), es)
+        worst = max(worst, (act.cpu() - ref).abs().max().item())
+        env.step(act)
+        restarts += int((env.terminated | env.truncated).sum().item())
+        assert torch.isfinite(env.obs).all()
+    assert worst < F32_TOL, worst
+    assert restarts >= n          # 1 s episodes: everyone restarted at least once, the recurrent state was re-zeroed

@@ -1,0 +1,205 @@
+"""bench.py --workload c4: BASELINE.json configs[3] -- 262 144 aircraft per GPU flown by the learned LSTM rate policy
+(random init, torch seed 0), medium difficulty, dt 0.02 (20 RK4 substeps).  One step = policy forward
+(policy_forward_kernel, tcgen05) + env step (env_step_kernel<float>, external action) for every aircraft."""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+METRIC = "aircraft env-steps/sec (learned LSTM policy forward + env step, 20 RK4 substeps per env step)"
+UNIT = "env-steps/s"
+
+
+def workload_name(n):
+    return (f"C4: {n} aircraft/GPU, LSTMFeaturesExtractor + stateful actor LSTM + pi-MLP policy (random init, seed 0) "
+            f"-> RateControlEnv (external action, medium, step commands), dt=0.02 K=20 RK4 substeps")
+
+
+def run_gpu(args, ROOT, ClockSampler):
+    import torch
+    import acb200
+    from acb200.policy import random_policy_state_dict
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.envs
+    env = acb200.BatchedRateControlEnv(n, difficulty="medium", controller="external", precision=32, device=local, seed=42,
+                                       id_offset=rank * n, command_type="step")
+    pol = acb200.LearnedPolicyB200(random_policy_state_dict("lstm", 0), kind="lstm", n=n, device=local, ctx=env.ctx)
+    env.reset()
+    flags = (env.terminated, env.truncated)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def step():
+        env.step(pol(env.obs, flags))
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    l0 = env.ctx.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    pev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    ev0.record()
+    for a, b in pev:                       # events bracket the policy kernel on its own (the launching) stream
+        a.record()
+        act = pol(env.obs, flags)
+        b.record()
+        env.step(act)
+    ev1.record()
+    barrier()
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    policy_ms = sum(a.elapsed_time(b) for a, b in pev) / args.steps
+    launches = env.ctx.launch_count - l0
+    stats = acb200.sharding.allreduce_episode_stats(env.stats)
+    value = n * world * args.steps / (ms * 1e-3)
+
+    # ---- end to end: the observation comes from host memory every step, results go back to host memory
+    pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
+    obs_h, rew_h = pin((n, 18), torch.float32), pin((n,), torch.float32)
+    term_h, trunc_h = pin((n,), torch.uint8), pin((n,), torch.uint8)
+    obs_h.copy_(env.obs); term_h.copy_(env.terminated); trunc_h.copy_(env.truncated)
+    obs_d = torch.empty_like(env.obs)
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+
+    def step_host():
+        obs_d.copy_(obs_h, non_blocking=True)
+        env.step(pol(obs_d, flags))
+        obs_h.copy_(env.obs, non_blocking=True); rew_h.copy_(env.reward_f32 if hasattr(env, "reward_f32") else env.reward, non_blocking=True)
+        term_h.copy_(env.terminated, non_blocking=True); trunc_h.copy_(env.truncated, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(2):
+        step_host()
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        step_host()
+    ev1.record()
+    barrier()
+    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
+    clk = clocks.stop() if rank == 0 else None
+    h2d = obs_h.numel() * 4
+    d2h = sum(t.numel() * t.element_size() for t in (obs_h, rew_h, term_h, trunc_h))
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    info = pol.info()
+    flops = info["flops_per_aircraft"] * n
+    achieved = flops / (policy_ms * 1e-3) / 1e12
+    peak = peaks.get("bf16_tflops_sustained", 1401.4)     # a kernel timed inside a long step: the sustained figure
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get(f"policy_forward_{n}")
+    except Exception:
+        pass
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16 operands / f32 accumulate and gates (policy), f32 (env)", "data": "synthetic",
+        "config": {"workload": workload_name(n), "envs_per_gpu": n, "policy": "lstm", "substeps": 20,
+                   "l2": "per-step working set (recurrent state 805 MB + env state) > 126 MB L2 (inputs larger than L2)",
+                   "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
+        "roofline": {"bound": "tensor", "kernel": "policy_forward_kernel", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": achieved / peak, "kernel_ms": policy_ms,
+                     "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if "bf16_tflops_sustained" in peaks else "fallback",
+                     "flop_per_aircraft": info["flops_per_aircraft"], "algorithmic_flop_per_launch": flops,
+                     "weight_bytes_per_tile": info["weight_bytes"], "traffic": traffic},
+        "kernels_ms": {"policy_forward_kernel": policy_ms, "env_step_kernel": ms / args.steps - policy_ms},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "ms_per_step": e2e_ms / e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "episode_stats": dict(zip(acb200.envs.STATS_NAMES, stats.cpu().tolist())),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        v, done, el, cores, sample = time_cpu(args.ref_envs_c4, budget_s=args.cpu_seconds)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def time_cpu(n, budget_s=None, steps=None, warmup=1):
+    """CPU arm: torch fp32 restatement of the policy (all cores, torch's own threading) + the C oracle env with an
+    external action (OpenMP over aircraft)."""
+    import numpy as np
+    import torch
+    from oracle import oracle as orc
+    from oracle import policy_oracle as po
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    net = po.make_policy("lstm", seed=0)
+    env = orc.Env(n, controller=orc.CTRL_EXTERNAL, seed=42, difficulty=np.full(n, 0.5, np.float32), command_type=orc.CMD_STEP,
+                  nthreads=cores)
+    env.reset()
+    state = net.initial_state(n)
+    done_flags = torch.zeros(n, dtype=torch.bool)
+
+    def step():
+        nonlocal state, done_flags
+        act, state = net(torch.from_numpy(np.ascontiguousarray(env.obs, dtype=np.float32)), state, done_flags)
+        env.step(act.numpy())
+        done_flags = torch.from_numpy((np.asarray(env.terminated) | np.asarray(env.truncated)).astype(bool))
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter(); done = 0
+    while True:
+        step(); done += 1
+        if steps is not None and done >= steps:
+            break
+        if budget_s is not None and done >= 3 and time.perf_counter() - t0 >= budget_s:
+            break
+    el = time.perf_counter() - t0
+    sample = (f"{n} aircraft x {done} steps ({el:.1f} s): torch fp32 policy restatement ({cores} threads) + C oracle env "
+              f"(OpenMP), same workload")
+    return n * done / el, done, el, cores, sample
+
+
+def run_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    v, done, el, cores, sample = time_cpu(args.ref_envs_c4, steps=args.steps, warmup=args.warmup)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * el / done, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 (policy), f64 (env)", "data": "synthetic",
+        "config": {"workload": workload_name(262144), "sample_envs": args.ref_envs_c4},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
