@@ -43,8 +43,8 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(bar(B_FULL + s), 1); mbar_init(bar(B_EMPTY + s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kEpiThreads); }
-        mbar_init(bar(B_ACT), kEpiThreads);
+        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kEpiWarps); }   // one arrival per epilogue warp
+        mbar_init(bar(B_ACT), kEpiWarps);
         mbar_init(bar(B_HFULL), 1);
         mbar_init(bar(B_BIAS), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -184,7 +184,8 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             }
         }
         fence_async_smem();
-        mbar_arrive(bar(B_ACT));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_ACT));
         mbar_wait(bar(B_BIAS), 0, P.error_flag, 700);
 
         uint32_t chunk_it = 0;
@@ -286,7 +287,8 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     }
                 }
                 tc_fence_before();
-                mbar_arrive(bar(B_ACC_EMPTY + a));
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(B_ACC_EMPTY + a));
                 if (tr) P.trace[ti++] = clock64();
             }
             if (l == P.recurrent_layer - 1) {
@@ -299,7 +301,8 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 }
             }
             fence_async_smem();
-            mbar_arrive(bar(B_ACT));
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(B_ACT));
         }
     }
 
@@ -340,13 +343,32 @@ struct acb200_policy {
     PolicyParams params{};          // layer table + device pointers of the packed weights / biases
     uint8_t* d_weights = nullptr;
     float* d_bias = nullptr;
-    int* d_error = nullptr;
+    int* d_error = nullptr;            // mapped host memory: survives a trapped kernel
+    int* h_error = nullptr;
     size_t weight_bytes = 0;
     double flops_per_aircraft = 0.0;   // algorithmic: 2 * out * in over the layers, h0 = 0 products excluded
     int device = 0;
 };
 
 namespace {
+
+// The bounded waits of the kernel write a code here before they trap; the flag lives in mapped host memory so that it
+// can still be read (and is reported at exit) after the context is gone.
+int* g_last_error_flag = nullptr;
+void report_trap() {
+    if (g_last_error_flag && *g_last_error_flag)
+        fprintf(stderr, "acb200 policy_forward_kernel: bounded wait expired, code %d\n", *g_last_error_flag);
+}
+cudaError_t alloc_error_flag(int** dev, int** host) {
+    cudaError_t e = cudaHostAlloc(host, sizeof(int), cudaHostAllocMapped);
+    if (e != cudaSuccess) return e;
+    **host = 0;
+    if ((e = cudaHostGetDevicePointer(dev, *host, 0)) != cudaSuccess) return e;
+    static bool registered = false;
+    if (!registered) { atexit(report_trap); registered = true; }
+    g_last_error_flag = *host;
+    return cudaSuccess;
+}
 
 int pfail(acb200_ctx* ctx, int code, const std::string& msg) {
     if (ctx) ctx->error = msg;
@@ -466,10 +488,9 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
     cudaError_t e;
     if ((e = cudaMalloc(&p->d_weights, p->weight_bytes)) != cudaSuccess ||
         (e = cudaMalloc(&p->d_bias, bias.size() * sizeof(float))) != cudaSuccess ||
-        (e = cudaMalloc(&p->d_error, sizeof(int))) != cudaSuccess ||
+        (e = alloc_error_flag(&p->d_error, &p->h_error)) != cudaSuccess ||
         (e = cudaMemcpy(p->d_weights, packed.data(), p->weight_bytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMemcpy(p->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = cudaMemset(p->d_error, 0, sizeof(int))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess) {
         return pfail(ctx, ACB200_ECUDA, std::string("policy upload: ") + cudaGetErrorString(e));
     }
@@ -521,7 +542,7 @@ void acb200_policy_destroy(acb200_policy* p) {
     cudaSetDevice(p->device);
     cudaFree(p->d_weights);
     cudaFree(p->d_bias);
-    cudaFree(p->d_error);
+    if (p->h_error) { if (g_last_error_flag == p->h_error) g_last_error_flag = nullptr; cudaFreeHost(p->h_error); }
     delete p;
 }
 
