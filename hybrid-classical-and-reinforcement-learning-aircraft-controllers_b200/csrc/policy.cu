@@ -27,8 +27,13 @@ using namespace acbp;
 namespace {
 
 // barrier slots inside the 128-byte barrier block
-enum { B_FULL = 0, B_EMPTY = 4, B_ACC_FULL = 8, B_ACC_EMPTY = 10, B_ACT = 12, B_HFULL = 13, B_BIAS = 14, B_COUNT = 15 };
+enum { B_FULL = 0, B_EMPTY = 4, B_ACC_FULL = 8, B_ACC_EMPTY = 10, B_ACT = 12, B_HFULL = 13, B_BIAS = 14, B_HGO = 15, B_COUNT = 16 };   // B_HGO: h' may be stored (peer block of a pair)
 
+// CTA == 1: one thread block per 128-aircraft tile.  CTA == 2: a cluster of two blocks (an SM pair) works as one
+// 256-row tile: the leader's MMA warp issues cta_group::2 instructions for both, each block stages only HALF of every
+// weight stage (a 16 KB ring slot then carries twice the K depth: half the L2 traffic and half the ring round trips
+// per FLOP), epilogues and recurrent state stay per block.
+template <int CTA>
 __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __grid_constant__ PolicyParams P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* act = smem;
@@ -40,18 +45,31 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
     const int64_t tile = blockIdx.x;
+    constexpr bool kPair = CTA == 2;
+    const uint32_t rank = kPair ? cluster_ctarank() : 0u;      // 0: leader of the pair
+    // barriers the leader's MMA warp waits on collect arrivals from both blocks: address them in the leader
+    auto lead = [&](int i) { return kPair ? mapa(bar(i), 0) : bar(i); };
+    auto arrive_lead = [&](int i) { if (kPair) mbar_arrive_cluster(lead(i)); else mbar_arrive(bar(i)); };
+    // "the operand of layer k is complete" (one lane per epilogue warp).  The peer block's MMA warp is not in the issue
+    // chain, so it gets a single-use barrier for the one moment it cares about (h' ready to store; no phase it could miss).
+    auto signal_operand = [&](int k) {
+        arrive_lead(B_ACT);
+        if (kPair && P.recurrent_layer >= 0 && k == P.recurrent_layer + 1) mbar_arrive(bar(B_HGO));
+    };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(bar(B_FULL + s), 1); mbar_init(bar(B_EMPTY + s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kEpiWarps); }   // one arrival per epilogue warp
-        mbar_init(bar(B_ACT), kEpiWarps);
+        for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kEpiWarps * CTA); }   // one arrival per epilogue warp
+        mbar_init(bar(B_ACT), kEpiWarps * CTA);
+        mbar_init(bar(B_HGO), kEpiWarps);
         mbar_init(bar(B_HFULL), 1);
         mbar_init(bar(B_BIAS), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == kEpiWarps + 1) tmem_alloc(smem_u32(tmem_slot), kTmemCols);
+    if (warp == kEpiWarps + 1) tmem_alloc<CTA>(smem_u32(tmem_slot), kTmemCols);
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync();          // the leader's barriers exist before the peer arrives on them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -64,15 +82,22 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             uint32_t it = 0;
             for (int l = 0; l < P.n_layers; ++l) {
                 const LayerDesc& L = P.L[l];
-                const uint32_t bytes = (uint32_t)L.N_c * (uint32_t)L.K_s * 2u;
+                const uint32_t bytes = (uint32_t)(L.N_c / CTA) * (uint32_t)L.K_s * 2u;   // this block's share of a stage
                 const int n_stage = L.n_chunks * (L.K / L.K_s);
                 for (int i = 0; i < n_stage; ++i, ++it) {
                     const uint32_t s = it % kStages, use = it / kStages;
                     if (use > 0) mbar_wait(bar(B_EMPTY + s), (use - 1) & 1, P.error_flag, 100 + l);
-                    if (P.debug & 1) { mbar_arrive(bar(B_FULL + s)); continue; }
-                    mbar_expect_tx(bar(B_FULL + s), bytes);
-                    bulk_g2s(smem_base + kStageOff + s * kStageBytes, src, bytes, bar(B_FULL + s));
-                    src += bytes;
+                    if (P.debug & 1) { if (rank == 0) mbar_arrive(bar(B_FULL + s)); continue; }
+                    if (kPair) {
+                        // both halves complete on the LEADER's barrier (tensor-map copy, .cta_group::2): it expects both
+                        if (rank == 0) mbar_expect_tx(bar(B_FULL + s), 2u * bytes);
+                        tma_load_2d_pair(smem_base + kStageOff + s * kStageBytes, &P.wmap[l], 0, (2 * i + (int)rank) * L.box_rows,
+                                         lead(B_FULL + s));
+                    } else {
+                        mbar_expect_tx(bar(B_FULL + s), bytes);
+                        bulk_g2s(smem_base + kStageOff + s * kStageBytes, src, bytes, bar(B_FULL + s));
+                        src += bytes;
+                    }
                 }
             }
         }
@@ -84,23 +109,30 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         const bool tr = (P.debug & 4) && blockIdx.x == 0 && leader;
         int ti = 0;
         if (tr) P.trace[ti++] = clock64();
+        if (rank != 0) {
+            // peer block of a pair: nothing to issue, only its own tile's recurrent state to move
+            if (P.recurrent_layer >= 0) {
+                mbar_wait(bar(B_HGO), 0, P.error_flag, 251);
+                if (leader) {
+                    bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
+                    bulk_commit();
+                    bulk_wait_all();
+                }
+            }
+        } else
         for (int l = 0; l < P.n_layers; ++l) {
             const LayerDesc& L = P.L[l];
-            mbar_wait(bar(B_ACT), l & 1, P.error_flag, 200 + l);       // operand of layer l is complete
+            mbar_wait<kPair>(bar(B_ACT), l & 1, P.error_flag, 200 + l);   // operand of layer l is complete (in both blocks of a pair)
             if (tr) P.trace[ti++] = clock64();
             if (P.recurrent_layer >= 0 && leader) {
-                if (l == P.recurrent_layer - 1) {                      // X's h region is idle from here on
-                    mbar_expect_tx(bar(B_HFULL), kHTileBytes);
-                    bulk_g2s(smem_base + kHOff, P.h_state + tile * (int64_t)kHTileBytes, kHTileBytes, bar(B_HFULL));
-                }
                 if (l == P.recurrent_layer + 1) {                      // Y holds h' as a finished operand tile
                     bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
                     bulk_commit();
                 }
             }
             tc_fence_after();
-            const uint32_t idesc = instr_desc_bf16(L.N_c);
-            const uint32_t lbo_b = (uint32_t)L.N_c * 16u;
+            const uint32_t idesc = instr_desc_bf16(L.N_c, kTile * CTA);
+            const uint32_t lbo_b = (uint32_t)(L.N_c / CTA) * 16u;
             const int stages_per_chunk = L.K / L.K_s, mma_per_stage = L.K_s / 16;
             // descriptors advance in their low word only (addresses stay below 2^18): +2 K slabs per MMA
             const uint64_t a_desc0 = smem_desc(smem_base + L.in_off, kKChunkBytes, 128);
@@ -109,7 +141,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             for (int c = 0; c < L.n_chunks; ++c, ++chunk_it) {
                 const uint32_t a = chunk_it & 1, use = chunk_it >> 1;
                 if (use > 0) {
-                    mbar_wait(bar(B_ACC_EMPTY + a), (use - 1) & 1, P.error_flag, 300 + l);
+                    mbar_wait<kPair>(bar(B_ACC_EMPTY + a), (use - 1) & 1, P.error_flag, 300 + l);
                     tc_fence_after();
                 }
                 if (tr) P.trace[ti++] = clock64();
@@ -117,31 +149,31 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 uint64_t a_desc = a_desc0;
                 uint32_t accumulate = 0;
                 for (int ks = 0; ks < stages_per_chunk; ++ks) {
-                    mbar_wait(bar(B_FULL + slot), slot_phase, P.error_flag, 400 + l);
+                    mbar_wait<kPair>(bar(B_FULL + slot), slot_phase, P.error_flag, 400 + l);
                     tc_fence_after();
                     if (leader) {
                         uint64_t b_desc = b_desc0 + (uint64_t)(slot * (kStageBytes >> 4));
                         if (mma_per_stage == 2) {
 #pragma unroll
-                            for (int k = 0; k < 2; ++k) { umma_bf16(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
+                            for (int k = 0; k < 2; ++k) { umma_bf16<CTA>(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
                         } else if (mma_per_stage == 4) {
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) { umma_bf16(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
+                            for (int k = 0; k < 4; ++k) { umma_bf16<CTA>(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
                         } else {
-                            for (int k = 0; k < mma_per_stage; ++k) { umma_bf16(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
+                            for (int k = 0; k < mma_per_stage; ++k) { umma_bf16<CTA>(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
                         }
-                        umma_commit(bar(B_EMPTY + slot));            // stage free once these MMAs have read it
+                        umma_commit<CTA>(bar(B_EMPTY + slot));            // stage free once these MMAs have read it
                     }
                     __syncwarp();
                     a_desc += (uint64_t)(mma_per_stage * a_step);
                     accumulate = 1;
                     if (++slot == kStages) { slot = 0; slot_phase ^= 1; }
                 }
-                if (leader) umma_commit(bar(B_ACC_FULL + a));        // accumulator chunk complete
+                if (leader) umma_commit<CTA>(bar(B_ACC_FULL + a));        // accumulator chunk complete
                 if (tr) P.trace[ti++] = clock64();
             }
         }
-        if (P.recurrent_layer >= 0 && leader) bulk_wait_all();
+        if (rank == 0 && P.recurrent_layer >= 0 && leader) bulk_wait_all();
     } else {
         // ================= epilogue: 8 warps; warp w reads tensor-memory lanes 32*(w%4).., i.e. aircraft row
         // 32*(w%4)+lane, and takes half (w/4) of every chunk's columns =================
@@ -185,7 +217,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         }
         fence_async_smem();
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar(B_ACT));
+        if (lane == 0) signal_operand(0);
         mbar_wait(bar(B_BIAS), 0, P.error_flag, 700);
 
         uint32_t chunk_it = 0;
@@ -223,6 +255,12 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
                     tc_fence_after();
+                    if (l == P.recurrent_layer - 2 && c == L.n_chunks - 1 && threadIdx.x == 0) {
+                        // every MMA of this layer has completed: nothing reads X's h region until the actor LSTM, so
+                        // h_prev can travel now, two layers ahead of its use (finish_policy checks the layer table)
+                        mbar_expect_tx(bar(B_HFULL), kHTileBytes);
+                        bulk_g2s(smem_base + kHOff, P.h_state + tile * (int64_t)kHTileBytes, kHTileBytes, bar(B_HFULL));
+                    }
                     for (int j = j0; j < j0 + w; j += 16) {
                         uint32_t vi[16], vg[16], vo[16]; float bi[16], bg[16], bo[16], h[16];
                         tmem_ld16_issue(t0 + j, vi);
@@ -288,7 +326,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar(B_ACC_EMPTY + a));
+                if (lane == 0) { if (kPair) mbar_arrive_cluster_relaxed(lead(B_ACC_EMPTY + a)); else mbar_arrive(bar(B_ACC_EMPTY + a)); }
                 if (tr) P.trace[ti++] = clock64();
             }
             if (l == P.recurrent_layer - 1) {
@@ -302,16 +340,17 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             }
             fence_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar(B_ACT));
+            if (lane == 0) signal_operand(l + 1);
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    if (kPair) cluster_sync();          // nobody leaves while the other block may still touch its barriers or tensor memory
     if (warp == kEpiWarps + 1) {
         __syncwarp();
         tc_fence_after();
-        tmem_dealloc(tmem_base, kTmemCols);
+        tmem_dealloc<CTA>(tmem_base, kTmemCols);
     }
 }
 
@@ -348,6 +387,7 @@ struct acb200_policy {
     size_t weight_bytes = 0;
     double flops_per_aircraft = 0.0;   // algorithmic: 2 * out * in over the layers, h0 = 0 products excluded
     int device = 0;
+    int cta = 1;                       // thread blocks per MMA: 1 = single block (default), 2 = SM pair (cta_group::2)
 };
 
 namespace {
@@ -449,6 +489,9 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
 int build_policy(acb200_ctx* ctx, int kind, std::vector<HostLayer>& layers, acb200_policy** out) {
     acb200_policy* p = new acb200_policy();
     p->kind = kind;
+    // ACB200_POLICY_CTA=2 selects the SM-pair kernel (cta_group::2 MMAs, tensor-map weight loads, half the weight traffic
+    // per SM).  Both pass the same tests; they measure the same on C4, so the simpler one is the default.
+    if (const char* v = getenv("ACB200_POLICY_CTA")) p->cta = atoi(v) == 2 ? 2 : 1;
     const int rc = finish_policy(ctx, p, layers, out);
     if (rc != ACB200_OK) acb200_policy_destroy(p);
     return rc;
@@ -457,27 +500,45 @@ int build_policy(acb200_ctx* ctx, int kind, std::vector<HostLayer>& layers, acb2
 int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& layers, acb200_policy** out) {
     std::vector<uint16_t> packed;
     std::vector<float> bias;
+    std::vector<size_t> layer_offset;
     p->params.n_layers = (int)layers.size();
     p->params.recurrent_layer = -1;
     for (size_t l = 0; l < layers.size(); ++l) {
         HostLayer& h = layers[l];
         LayerDesc& d = h.d;
+        // stage depth: as many K slabs as one ring slot holds of this block's share of the columns (at most 8 MMAs)
+        d.K_s = 16;
+        for (int ks = 16; ks <= d.K && ks <= 128; ks += 16)
+            if (d.K % ks == 0 && (uint32_t)(d.N_c / p->cta) * ks * 2u <= kStageBytes) d.K_s = ks;
+        d.box_rows = (d.N_c / p->cta) * d.K_s * 2 / 128;
+        layer_offset.push_back(packed.size() * 2);
         if (d.K % 16 || d.K % d.K_s || d.K_s % 16 || d.N_c % 16 || d.N_c > 256 ||
-            (uint32_t)d.N_c * d.K_s * 2u > kStageBytes)
+            (uint32_t)(d.N_c / p->cta) * d.K_s * 2u > kStageBytes || (d.N_c / p->cta) % 8 ||
+            ((d.N_c / p->cta) * d.K_s * 2) % 128 || d.box_rows > 256)
             return pfail(ctx, ACB200_EVALUE, "policy: bad layer geometry");
         d.bias_off = (int)bias.size();
         bias.insert(bias.end(), h.b.begin(), h.b.end());
         if (d.epi == EPI_LSTM) p->params.recurrent_layer = (int)l;
         if ((d.epi == EPI_LSTM && d.N_c != 256) || (d.epi == EPI_LSTM0 && d.N_c % 96) || (d.epi == EPI_RELU && d.N_c % 32))
             return pfail(ctx, ACB200_EVALUE, "policy: chunk width does not split over the two epilogue halves");
+        const int n_half = d.N_c / p->cta;      // a CTA pair splits every stage's columns in two halves, leader first
         for (int c = 0; c < d.n_chunks; ++c)
             for (int ks = 0; ks < d.K / d.K_s; ++ks)
-                for (int kk = 0; kk < d.K_s / 8; ++kk)
-                    for (int n = 0; n < d.N_c; ++n)
-                        for (int j = 0; j < 8; ++j)
-                            packed.push_back(bf16_bits(h.w[(size_t)(c * d.N_c + n) * d.K + ks * d.K_s + kk * 8 + j]));
+                for (int r = 0; r < p->cta; ++r)
+                    for (int kk = 0; kk < d.K_s / 8; ++kk)
+                        for (int n = r * n_half; n < (r + 1) * n_half; ++n)
+                            for (int j = 0; j < 8; ++j)
+                                packed.push_back(bf16_bits(h.w[(size_t)(c * d.N_c + n) * d.K + ks * d.K_s + kk * 8 + j]));
         p->params.L[l] = d;
         p->flops_per_aircraft += h.real_flops;
+    }
+    if (p->params.recurrent_layer >= 0) {
+        // the kernel loads h_prev behind the features (X + kHOff) while layer rec-2's last epilogue and layer rec-1 run
+        const int r = p->params.recurrent_layer;
+        if (r < 2 || layers[r - 2].d.epi != EPI_LSTM0 || layers[r - 1].d.in_off < kXBytes ||
+            layers[r - 1].d.out_off + (uint32_t)layers[r - 1].d.N_c * layers[r - 1].d.n_chunks * 256u > kHOff ||
+            layers[r].d.in_off != 0 || layers[r].d.out_off != kXBytes)
+            return pfail(ctx, ACB200_EVALUE, "policy: layer table does not leave X's h region free ahead of the recurrent layer");
     }
     while (bias.size() % 4) bias.push_back(0.f);   // bulk copies move multiples of 16 bytes
     if (bias.size() > (size_t)kMaxBias) return pfail(ctx, ACB200_EVALUE, "policy: too many bias values");
@@ -491,8 +552,30 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         (e = alloc_error_flag(&p->d_error, &p->h_error)) != cudaSuccess ||
         (e = cudaMemcpy(p->d_weights, packed.data(), p->weight_bytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMemcpy(p->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess) {
+        (e = cudaFuncSetAttribute(policy_forward_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(policy_forward_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess) {
         return pfail(ctx, ACB200_ECUDA, std::string("policy upload: ") + cudaGetErrorString(e));
+    }
+    if (p->cta == 2) {
+        // one tiled tensor map per layer: its packed weights seen as rows of 128 bytes, box = one block's half stage
+        typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                        const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if ((e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q)) != cudaSuccess || !fn)
+            return pfail(ctx, ACB200_ECUDA, "policy: cuTensorMapEncodeTiled is not available");
+        for (size_t l = 0; l < layers.size(); ++l) {
+            const size_t end = l + 1 < layers.size() ? layer_offset[l + 1] : p->weight_bytes;
+            const cuuint64_t dims[2] = {64, (end - layer_offset[l]) / 128};
+            const cuuint64_t strides[1] = {128};
+            const cuuint32_t box[2] = {64, (cuuint32_t)p->params.L[l].box_rows};
+            const cuuint32_t estr[2] = {1, 1};
+            const CUresult r = ((EncodeTiled)fn)(&p->params.wmap[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p->d_weights + layer_offset[l],
+                                                 dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return pfail(ctx, ACB200_ECUDA, "policy: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+        }
     }
     p->params.weights = p->d_weights;
     p->params.bias = p->d_bias;
@@ -549,7 +632,7 @@ void acb200_policy_destroy(acb200_policy* p) {
 int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes, size_t* c_bytes) {
     if (!p) return ACB200_ENULL;
     if (n < 0) return ACB200_EVALUE;
-    const size_t tiles = (size_t)((n + kTile - 1) / kTile);
+    const size_t tiles = (size_t)(((n + kTile - 1) / kTile + 1) & ~(int64_t)1);   // whole SM pairs
     const bool rec = p->params.recurrent_layer >= 0;
     if (h_bytes) *h_bytes = rec ? tiles * kHTileBytes : 0;
     if (c_bytes) *c_bytes = rec ? tiles * (size_t)kHidden * kTile * sizeof(float) : 0;
@@ -576,9 +659,23 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
     if ((debug & 4) && !trace) { cudaMalloc(&trace, 2048 * sizeof(long long)); cudaMemset(trace, 0, 2048 * sizeof(long long)); }
     P.trace = trace;
     const int64_t tiles = (n + kTile - 1) / kTile;
-    policy_forward_kernel<<<(unsigned)tiles, kThreads, kSmemBytes, ctx->stream>>>(P);
+    cudaError_t e;
+    if (p->cta == 2) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)((tiles + 1) & ~(int64_t)1));   // an odd last tile gets an all-padding partner
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = kSmemBytes;
+        cfg.stream = ctx->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, policy_forward_kernel<2>, P);
+    } else {
+        policy_forward_kernel<1><<<(unsigned)tiles, kThreads, kSmemBytes, ctx->stream>>>(P);
+        e = cudaGetLastError();
+    }
     ctx->launches += 1;
-    const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return pfail(ctx, ACB200_ECUDA, std::string("policy_forward_kernel: ") + cudaGetErrorString(e));
     if ((debug & 4) && getenv("ACB200_POLICY_TRACE")) {   // development aid: dump block 0's time line
         static int dumped = 0;

@@ -9,6 +9,7 @@
 // threads (one thread per aircraft row, one 16-byte store per 8 outputs), weights are packed into it on the host
 // once, so a weight stage is ONE contiguous cp.async.bulk from L2.
 #pragma once
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -45,9 +46,11 @@ struct LayerDesc {
     int n_chunks;
     uint32_t in_off, out_off;   // byte offsets of the A operand / of output column 0 inside the activation area
     int bias_off;   // float offset into the bias array (permuted like the packed rows)
+    int box_rows;   // CTA-pair mode: 128-byte rows of one block's half of a stage (the tensor map's box height)
 };
 
 struct PolicyParams {
+    CUtensorMap wmap[kMaxLayers];   // CTA-pair mode: layer l's packed weights as rows of 128 bytes, box = one block's half stage
     int n_layers;
     int recurrent_layer;      // index of the EPI_LSTM layer, -1 if none
     LayerDesc L[kMaxLayers];
@@ -90,11 +93,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     return ok != 0;
 }
 // Bounded wait: a protocol bug must end as a trapped kernel with a code in *err, not as a hung GPU.
+// CLUSTER: the barrier collects arrivals from both CTAs of a pair (acquire at cluster scope).
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity);
+template <bool CLUSTER = false>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* err, int code) {
-    if (mbar_try_wait(bar, parity)) return;
+    auto ready = [&]() { return CLUSTER ? mbar_try_wait_cluster(bar, parity) : mbar_try_wait(bar, parity); };
+    if (ready()) return;
     long long t0 = 0;
     uint32_t spins = 0;
-    while (!mbar_try_wait(bar, parity)) {
+    while (!ready()) {
         if ((++spins & 0xFFFu) != 0) continue;
         if (t0 == 0) t0 = clock64();
         else if (clock64() - t0 > 4000000000LL) {   // about two seconds
@@ -103,6 +110,52 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int* er
             __trap();
         }
     }
+}
+
+// ---- thread-block cluster (CTA pair) ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on a barrier that may live in the other CTA of the pair (address from mapa)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+// same without ordering of this thread's earlier memory operations: enough where the arrival only says "my tensor-memory
+// reads are done" (tcgen05.wait::ld + tcgen05.fence cover those); a cluster-scope release costs hundreds of cycles
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_bar) {
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {   // own barrier, arrivals from the pair
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Tiled (tensor-map) load of one box into THIS block's shared memory, completing on a barrier that may be the pair
+// leader's: only the tensor form of the bulk copy takes .cta_group::2, which is what lets both halves of a weight
+// stage report to the one barrier the MMA warp waits on.
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t cluster_bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(cluster_bar)
+        : "memory");
 }
 
 // ---- bulk asynchronous copies (TMA engine, 1-D) ---------------------------------------------------------------------
@@ -120,12 +173,20 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---- tensor memory + tcgen05 ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {   // whole warp
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+template <int CTA>
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {   // whole warp (the same warp in both CTAs of a pair)
+    if (CTA == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
 }
+template <int CTA>
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {    // whole warp, the allocating one
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+    if (CTA == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -135,21 +196,41 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
     return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
            ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46);
 }
-// instruction descriptor: D = f32, A = B = bf16, both K-major, M = 128
-__device__ __forceinline__ uint32_t instr_desc_bf16(int n_cols) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((uint32_t)(kTile >> 4) << 24);
+// instruction descriptor: D = f32, A = B = bf16, both K-major, M = 128 per CTA (256 over a CTA pair)
+__device__ __forceinline__ uint32_t instr_desc_bf16(int n_cols, int m_rows) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n_cols >> 3) << 17) | ((uint32_t)(m_rows >> 4) << 24);
 }
+// CTA == 2: one instruction drives both SMs of the pair -- A rows 0..127 from the leader's shared memory, 128..255 from
+// the peer's (same offsets), B columns split in halves between the two, D rows into each CTA's own tensor memory.
+template <int CTA>
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
+    if (CTA == 2)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+            : "memory");
 }
-// mbarrier arrive once every tcgen05 operation this thread issued so far has completed
+// mbarrier arrive once every tcgen05 operation this thread issued so far has completed; for a CTA pair the arrive is
+// multicast to the barrier at the same offset in both CTAs
+template <int CTA>
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    if (CTA == 2) {
+        const uint16_t mask = 3;
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                     "h"(mask)
+                     : "memory");
+    } else {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    }
 }
 
 // 16 consecutive fp32 accumulator columns of this thread's lane (32x32b: lane = 32 * (warp % 4) + laneid)

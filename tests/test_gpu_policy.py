@@ -68,6 +68,28 @@ def test_lstm_policy_sequence_vs_oracle(n, scale):
         assert worst_ref < F32_TOL, worst_ref
 
 
+def test_sm_pair_kernel_matches_single_block_kernel(monkeypatch):
+    """The cta_group::2 variant (ACB200_POLICY_CTA=2: one MMA stream for an SM pair, weight halves loaded through tensor
+    maps onto the leader's barrier) computes the same sums in the same order: actions and state bit for bit."""
+    import acb200
+    n = 900                                            # 8 tiles: the last pair is half padding
+    net = po.make_policy("lstm", seed=1)
+    out = {}
+    for cta in ("1", "2"):
+        monkeypatch.setenv("ACB200_POLICY_CTA", cta)
+        pol = acb200.LearnedPolicyB200(net.state_dict(), kind="lstm", n=n)
+        acts = []
+        for t in range(4):
+            obs = po.synthetic_obs(n, seed=50 + t).cuda()
+            es = torch.full((n,), t == 0, dtype=torch.bool, device="cuda")
+            acts.append(pol(obs, es).clone())
+        out[cta] = (torch.stack(acts), *pol.get_lstm_states())
+    assert torch.equal(out["1"][0], out["2"][0])
+    assert np.array_equal(out["1"][1], out["2"][1]) and np.array_equal(out["1"][2], out["2"][2])
+    emu, _ = po.forward_bf16_emulated(net, po.synthetic_obs(n, seed=50), net.initial_state(n), torch.ones(n, dtype=torch.bool))
+    assert (out["2"][0][0].cpu() - emu).abs().max().item() < EMU_TOL
+
+
 def test_state_import_export_roundtrip():
     n = 300
     net, pol = _policy("lstm", n)
