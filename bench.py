@@ -118,20 +118,20 @@ def make_inputs(n, id_offset, seed=42):
     return difficulty, att, phase
 
 
-def oracle_env(n, nthreads, id_offset=0):
+def oracle_env(n, nthreads, id_offset=0, dt=0.02):
     import numpy as np
     from oracle import oracle as orc
     difficulty, att, phase = make_inputs(n, id_offset)
     env = orc.Env(n, controller=orc.CTRL_ATTITUDE_PID, seed=42, id_offset=id_offset, difficulty=difficulty,
-                  command_type=orc.CMD_STEP, nthreads=nthreads)
+                  command_type=orc.CMD_STEP, nthreads=nthreads, dt=dt)
     env.att_cmd[:] = att
     env.reset()
     env.step_count[:] = phase
     return env
 
 
-def time_oracle(n, nthreads, warmup, steps=None, budget_s=None):
-    env = oracle_env(n, nthreads)
+def time_oracle(n, nthreads, warmup, steps=None, budget_s=None, dt=0.02):
+    env = oracle_env(n, nthreads, dt=dt)
     for _ in range(warmup):
         env.step()
     t0 = time.perf_counter()
@@ -153,13 +153,15 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     n = args.ref_envs
-    value, done, el = time_oracle(n, cores, args.warmup, steps=args.steps)
+    k1 = args.workload == "k1"
+    value, done, el = time_oracle(n, cores, args.warmup, steps=args.steps, dt=0.001 if k1 else 0.02)
     sample = f"{n} aircraft x {done} env steps of the same C3 workload (bounded sample), OpenMP over aircraft"
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": METRIC.replace("20 RK4 substeps", "1 RK4 substep") if k1 else METRIC, "value": value,
+        "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * el / done, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(1 << 20), "sample_envs": n},
+        "config": {"workload": workload_name(1 << 20) + (" [at K=1: dt=0.001]" if k1 else ""), "sample_envs": n},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -183,8 +185,10 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
     n = args.envs
     precision = args.precision
+    k_sub = 1 if args.workload == "k1" else K_SUB          # k1: control step == physics step, the HBM-bound end of the path
+    flop_per_env_step = 1014 * k_sub + 320
     env = acb200.BatchedRateControlEnv(n, controller="attitude_pid", precision=precision, device=local, seed=42,
-                                       id_offset=rank * n, command_type="step")
+                                       id_offset=rank * n, command_type="step", dt=0.001 * k_sub)
     difficulty, att, phase = make_inputs(n, rank * n)
     env.set_curriculum(torch.as_tensor(difficulty), "step")
     env.att_cmd.copy_(torch.as_tensor(att).to(env.dtype))
@@ -267,27 +271,31 @@ def run_gpu(args):
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get(f"env_step_f{precision}_{n}")
+            traffic = json.load(f).get(f"env_step{'_k1' if k_sub == 1 else ''}_f{precision}_{n}")
     except Exception:
         pass
-    achieved_tflops = per_gpu * FLOP_PER_ENV_STEP / 1e12
+    achieved_tflops = per_gpu * flop_per_env_step / 1e12
     achieved_gbs = per_gpu * bytes_step / 1e9
+    roof_fp = {"bound": "fp32", "note": "non-tensor FP32 issue-bound; the path is neither HBM- nor tensor-bound (DESIGN.md 4); HBM view in roofline_hbm",
+               "achieved": achieved_tflops, "peak": fp_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fp_peak,
+               "peak_source": "measured here: FMA-chain kernel, all SMs (derived nominal: %.1f)" % FP32_PEAK_DERIVED_TFLOPS,
+               "flop_per_env_step": flop_per_env_step, "kernel": "env_step_kernel", "kernel_ms": ms / args.steps,
+               "traffic": traffic}
+    roof_hbm = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+                "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
+                "bytes_per_env_step": bytes_step, "algorithmic_bytes_per_launch": bytes_step * n, "kernel": "env_step_kernel",
+                "kernel_ms": ms / args.steps, "traffic": traffic}
+    k1 = args.workload == "k1"
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": METRIC.replace("20 RK4 substeps", "1 RK4 substep") if k1 else METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if precision == 32 else "f64", "data": "synthetic",
-        "config": {"workload": workload_name(n), "envs_per_gpu": n, "controller": "attitude_pid", "substeps": K_SUB,
+        "config": {"workload": workload_name(n).replace("C3:", "C3 at K=1 (HBM-bound end of the path):").replace("dt=0.02 K=20 RK4 substeps", "dt=0.001 K=1 RK4 substep") if k1 else workload_name(n),
+                   "envs_per_gpu": n, "controller": "attitude_pid", "substeps": k_sub,
                    "l2": f"working set {n * bytes_step / 2 / 1e6:.0f} MB per step > 126 MB L2 (inputs larger than L2)",
                    "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
-        "roofline": {"bound": "fp32", "note": "non-tensor FP32 issue-bound; the path is neither HBM- nor tensor-bound (DESIGN.md 4); HBM view in roofline_hbm",
-                     "achieved": achieved_tflops, "peak": fp_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fp_peak,
-                     "peak_source": "measured here: FMA-chain kernel, all SMs (derived nominal: %.1f)" % FP32_PEAK_DERIVED_TFLOPS,
-                     "flop_per_env_step": FLOP_PER_ENV_STEP, "kernel": "env_step_kernel", "kernel_ms": ms / args.steps,
-                     "traffic": traffic},
-        "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
-                         "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
-                         "bytes_per_env_step": bytes_step, "algorithmic_bytes_per_launch": bytes_step * n,
-                         "traffic": traffic},
+        "roofline": roof_hbm if k1 else roof_fp,
+        ("roofline_fp32" if k1 else "roofline_hbm"): roof_fp if k1 else roof_hbm,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": e2e_ms / e2e_steps},
         "gpu_launches": int(launches),
@@ -296,7 +304,7 @@ def run_gpu(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        v, done, el = time_oracle(args.ref_envs, cores, 1, budget_s=args.cpu_seconds)
+        v, done, el = time_oracle(args.ref_envs, cores, 1, budget_s=args.cpu_seconds, dt=0.001 * k_sub)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"{args.ref_envs} aircraft x {done} env steps ({el:.1f} s) of the same workload, C oracle with OpenMP"}
     print(json.dumps(out))
@@ -322,8 +330,9 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=50)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c3", choices=["c3", "c4"],
-                    help="c3 (default, BASELINE metric): 2^20 aircraft, cascaded PID; c4: 262144 aircraft, learned LSTM policy")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "k1"],
+                    help="c3 (default, BASELINE metric): 2^20 aircraft, cascaded PID, K=20; c4: 262144 aircraft, learned LSTM policy; "
+                         "k1: c3 with one RK4 substep per env step (the HBM-bound K=1 path)")
     ap.add_argument("--ref-envs-c4", type=int, default=4096, help="aircraft in the bounded CPU sample of --workload c4")
     args = ap.parse_args()
     if args.workload == "c4":
