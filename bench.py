@@ -230,6 +230,7 @@ def run_gpu(args):
     value = n * world * args.steps / (ms * 1e-3)
 
     # ---- end-to-end arm: host buffers, H2D of the step's commands + D2H of obs/reward/done every step
+    numa_cores = acb200.sharding.bind_host_to_gpu(local) if world > 1 else []   # staging buffers on the GPU's own NUMA node
     pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
     att_host = pin((4, n), env.dtype); att_host.copy_(torch.as_tensor(att).to(env.dtype))
     obs_h, rew_h = pin((n, 18), torch.float32), pin((n,), torch.float32)
@@ -297,7 +298,7 @@ def run_gpu(args):
         "roofline": roof_hbm if k1 else roof_fp,
         ("roofline_fp32" if k1 else "roofline_hbm"): roof_fp if k1 else roof_hbm,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "ms_per_step": e2e_ms / e2e_steps},
+                "ms_per_step": e2e_ms / e2e_steps, "host_cores_bound": len(numa_cores)},
         "gpu_launches": int(launches),
         "clocks": clk,
         "episode_stats": dict(zip(acb200.envs.STATS_NAMES, stats.cpu().tolist())),
@@ -330,11 +331,17 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=50)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "k1"],
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5", "k1"],
                     help="c3 (default, BASELINE metric): 2^20 aircraft, cascaded PID, K=20; c4: 262144 aircraft, learned LSTM policy; "
-                         "k1: c3 with one RK4 substep per env step (the HBM-bound K=1 path)")
+                         "k1: c3 with one RK4 substep per env step (the HBM-bound K=1 path); c5: 2^20 aircraft, waypoint mission, 5-level cascade, K=1")
     ap.add_argument("--ref-envs-c4", type=int, default=4096, help="aircraft in the bounded CPU sample of --workload c4")
     args = ap.parse_args()
+    if args.workload == "c5":
+        from tools import bench_c5
+        args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+        if args.steps == 1000 and args.impl == "reference":
+            args.steps = 20
+        return bench_c5.run_reference(args) if args.impl == "reference" else bench_c5.run_gpu(args, ROOT, ClockSampler)
     if args.workload == "c4":
         from tools import bench_c4
         if args.envs == 1 << 20:

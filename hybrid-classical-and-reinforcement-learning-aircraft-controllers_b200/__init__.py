@@ -10,7 +10,9 @@ from . import sharding, vecenv
 from .vecenv import B200VecEnv
 from . import policy
 from .policy import LearnedPolicyB200
+from . import rollout
+from .rollout import RolloutBufferB200
 
-__all__ = ["policy", "LearnedPolicyB200", "_cabi", "adapters", "pid_bindings", "SimulationAircraftBackendB200", "vecenv", "sharding", "B200VecEnv", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
+__all__ = ["policy", "LearnedPolicyB200", "rollout", "RolloutBufferB200", "_cabi", "adapters", "pid_bindings", "SimulationAircraftBackendB200", "vecenv", "sharding", "B200VecEnv", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
            "default_controller_params", "kernel_info"]
 __version__ = "0.1.0"

@@ -102,6 +102,7 @@ SYMBOLS = [
     "acb200_launch_count", "acb200_measure_fp32_peak",
     "acb200_policy_create_lstm", "acb200_policy_create_mlp", "acb200_policy_destroy", "acb200_policy_state_bytes",
     "acb200_policy_forward", "acb200_policy_state_export", "acb200_policy_state_import", "acb200_policy_info",
+    "acb200_gae",
 ]
 
 _lib = None
@@ -151,6 +152,7 @@ def load() -> C.CDLL:
     L.acb200_policy_state_export.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     L.acb200_policy_state_import.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     L.acb200_policy_info.argtypes = [vp, P(dbl), P(C.c_size_t), P(i32)]
+    L.acb200_gae.argtypes = [vp, C.c_int32, i64, vp, vp, vp, vp, vp, dbl, dbl, vp, vp]
     _lib = L
     return L
 

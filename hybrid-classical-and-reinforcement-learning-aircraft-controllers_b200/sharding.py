@@ -33,3 +33,24 @@ def make_sharded_env(n_total: int, rank: int, world: int, device=None, **kw):
     from .envs import BatchedRateControlEnv
     first, count = shard_range(n_total, rank, world)
     return BatchedRateControlEnv(count, id_offset=first, device=rank if device is None else device, **kw)
+
+
+def bind_host_to_gpu(device_index: int) -> list:
+    """Pin this process to the CPU cores NVML reports as local to the GPU, so that pinned host buffers allocated
+    afterwards are first-touched on the GPU's own NUMA node (the host-buffer step is PCIe-bound, and on an 8-GPU box
+    remote-node staging memory is what the ranks end up fighting over).  Returns the core list ([] = left unchanged:
+    NVML not importable, or no affinity information)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(int(device_index))
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cores = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        allowed = sorted(set(cores) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return []

@@ -282,6 +282,15 @@ int acb200_policy_state_import(acb200_ctx* ctx, const acb200_policy* p, int64_t 
 /* algorithmic FLOPs (2*M*N*K over the layers as executed) and packed weight bytes per 128-aircraft tile */
 int acb200_policy_info(const acb200_policy* p, double* flops_per_aircraft, size_t* weight_bytes, int* smem_bytes);
 
+/* ---- rollout post-processing on the device ------------------------------------------------
+ * Replaces stable-baselines3 RolloutBuffer.compute_returns_and_advantage (third party; run by the PPO / RecurrentPPO the
+ * reference builds at learned_controllers/utils/training_utils.py:112-160, train_overnight.py:151-167) on device-resident
+ * rollouts: rewards, values, advantages, returns f32 [T][n] row-major; episode_starts u8 [T][n] (1 where step t began an
+ * episode); last_values f32 [n], dones u8 [n] for the step after the last one.  float32 arithmetic in numpy's order:
+ * bit-identical to the host implementation. */
+int acb200_gae(acb200_ctx* ctx, int32_t T, int64_t n, const float* rewards, const float* values, const uint8_t* episode_starts,
+               const float* last_values, const uint8_t* dones, double gamma, double gae_lambda, float* advantages, float* returns);
+
 /* ---- host-side PID core (the same fp32 arithmetic as the kernels; mirrors PIDController::compute/reset) ---- */
 float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt);
 void acb200_pid_reset(acb200_pid_state* st);

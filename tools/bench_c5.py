@@ -1,0 +1,200 @@
+"""bench.py --workload c5: BASELINE.json configs[4] -- 2^20 aircraft per GPU flying a looping square mission
+(300 m side at 100 m altitude, 15 m/s, pure-pursuit guidance) through the full 5-level cascade
+(waypoint -> HSA/TECS -> attitude -> rate -> surface), dt = dt_physics = 0.01 (K = 1: ONE RK4 substep per control step),
+initial states jittered +-20 m / +-10 deg heading by global id.  One step = one launch of step_guided_kernel<float, 1>."""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+METRIC = "aircraft control-steps/sec (waypoint->HSA->attitude->rate->surface cascade, 1 RK4 substep per step)"
+UNIT = "env-steps/s"
+DT = 0.01
+SQUARE = [[300.0, 0.0, -100.0, 15.0], [300.0, 300.0, -100.0, 15.0], [0.0, 300.0, -100.0, 15.0], [0.0, 0.0, -100.0, 15.0]]
+# step_guided_kernel<T,1>: loads state 13 + pid 18 + pid_outer 9 + wp_index 1, stores state 13 + controls 4 + derived 4 +
+# pid 18 + pid_outer 9 + wp_index 1 (4-byte words, fp32 build)
+BYTES_PER_STEP = (13 + 18 + 9 + 1 + 13 + 4 + 4 + 18 + 9 + 1) * 4
+
+
+def workload_name(n):
+    return (f"C5: {n} aircraft/GPU, looping square mission 300 m @ 100 m / 15 m/s, pure-pursuit guidance + HSA (TECS) + "
+            f"attitude->rate->surface PID cascade, dt=0.01 K=1 RK4 substep")
+
+
+def initial_states(n, id_offset, seed=7):
+    import numpy as np
+    ids = np.arange(id_offset, id_offset + n, dtype=np.uint64)
+
+    def u(stream):
+        with np.errstate(over="ignore"):
+            x = ids + np.uint64(seed * 0x9E3779B97F4A7C15 & 0xFFFFFFFFFFFFFFFF) + np.uint64(stream) * np.uint64(0xBF58476D1CE4E5B9)
+            x ^= x >> np.uint64(30); x *= np.uint64(0xBF58476D1CE4E5B9)
+            x ^= x >> np.uint64(27); x *= np.uint64(0x94D049BB133111EB)
+            x ^= x >> np.uint64(31)
+        return (x >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+
+    s = np.zeros((13, n), np.float64)
+    s[0] = -20.0 + 40.0 * u(1); s[1] = -20.0 + 40.0 * u(2); s[2] = -100.0
+    s[3] = 15.0
+    s[8] = np.radians(-10.0 + 20.0 * u(3))
+    return s
+
+
+def run_gpu(args, ROOT, ClockSampler):
+    import torch
+    import acb200
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.envs
+    fleet = acb200.AircraftFleet(n, precision=32, device=local, config={"dt_physics": DT})
+    fleet.reset(torch.as_tensor(initial_states(n, rank * n)))
+    fleet.set_mission(SQUARE, acceptance_radius=40.0, guidance="PP", loop=True)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if dist is None:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        fleet.step_waypoint(DT)
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    l0 = fleet.ctx.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        fleet.step_waypoint(DT)
+    ev1.record()
+    barrier()
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = fleet.ctx.launch_count - l0
+    value = n * world * args.steps / (ms * 1e-3)
+
+    # end to end: the caller reads every aircraft's state back each step (AircraftInterface.step returns the state);
+    # the mission is autonomous, so nothing travels host -> device per step
+    state_h = torch.empty((13, n), dtype=torch.float32, pin_memory=True)
+    derived_h = torch.empty((4, n), dtype=torch.float32, pin_memory=True)
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+
+    def step_host():
+        fleet.step_waypoint(DT)
+        state_h.copy_(fleet.state, non_blocking=True); derived_h.copy_(fleet.derived, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(2):
+        step_host()
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        step_host()
+    ev1.record()
+    barrier()
+    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
+    clk = clocks.stop() if rank == 0 else None
+    wp = fleet.wp_index.cpu()
+    alt = fleet.derived[1].float().cpu()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    achieved = value / world * BYTES_PER_STEP / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f).get(f"step_waypoint_f32_{n}")
+    except Exception:
+        pass
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": workload_name(n), "envs_per_gpu": n, "substeps": 1,
+                   "l2": f"working set {n * BYTES_PER_STEP / 2 / 1e6:.0f} MB per step > 126 MB L2 (inputs larger than L2)",
+                   "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
+        "roofline": {"bound": "hbm", "kernel": "step_guided_kernel<float,1>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "kernel_ms": ms / args.steps, "bytes_per_env_step": BYTES_PER_STEP,
+                     "algorithmic_bytes_per_launch": BYTES_PER_STEP * n,
+                     "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback", "traffic": traffic},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": (13 + 4) * 4 * n,
+                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                "note": "autonomous mission: no per-step host input; state + derived outputs read back every step"},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "mission": {"mean_waypoint_index": float(wp.float().mean()), "altitude_mean": float(alt.mean()), "altitude_min": float(alt.min()),
+                    "sim_seconds": (args.warmup + args.steps + e2e_steps + 2) * DT},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        v, done, el, cores, sample = time_cpu(args.ref_envs, budget_s=args.cpu_seconds)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+    print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def time_cpu(n, budget_s=None, steps=None, warmup=1):
+    import numpy as np
+    from oracle import oracle as orc
+    cores = os.cpu_count() or 1
+    P, CP = orc.default_aircraft_params(), orc.default_controller_params()
+    state = initial_states(n, 0)
+    wp = np.asarray(SQUARE, np.float64)
+    idx = np.zeros(n, np.int32); pid = np.zeros((18, n), np.float32); pid_outer = np.zeros((9, n), np.float32)
+
+    def step():
+        orc.step_waypoint(P, CP, state, wp, idx, pid, pid_outer, DT, guidance=orc.GUIDANCE_PP, acceptance_radius=40.0, loop=True,
+                          dt_physics=DT, nthreads=cores)
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter(); done = 0
+    while True:
+        step(); done += 1
+        if steps is not None and done >= steps:
+            break
+        if budget_s is not None and done >= 3 and time.perf_counter() - t0 >= budget_s:
+            break
+    el = time.perf_counter() - t0
+    return n * done / el, done, el, cores, f"{n} aircraft x {done} steps ({el:.1f} s) of the same mission, C oracle with OpenMP"
+
+
+def run_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    v, done, el, cores, sample = time_cpu(args.ref_envs, steps=args.steps, warmup=args.warmup)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * el / done, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(1 << 20), "sample_envs": args.ref_envs},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
