@@ -34,6 +34,21 @@ __device__ __forceinline__ void store_pid(float* pid, int64_t n, int64_t i, int 
 }
 
 // ---- Simplified6DOF.reset for a masked subset (simplified_6dof.py:189-212) ------------------------
+// Resident blocks per SM the register allocation of the fp32 build aims at (measured on B200, r01d; the fp64 parity
+// build keeps the compiler's own choice).  env_step: 6 blocks = 80 registers, 8 bytes of spill: +3.5 % at K=1, +0.3 % at
+// K=20 over 96 registers (8 blocks = 64 registers spills 156 bytes and loses 2 %).  step_guided (K=1 missions, the most
+// memory-bound kernel): 8 blocks = 64 registers: +14 % over 126 registers (6 blocks: -11 %, it spills 224 bytes there).
+#ifndef ACB_GUIDED_MIN_BLOCKS
+#define ACB_GUIDED_MIN_BLOCKS 8
+#endif
+#ifndef ACB_ENV_MIN_BLOCKS
+#define ACB_ENV_MIN_BLOCKS 6
+#endif
+template <typename T> struct MinBlocks {
+    static constexpr int env = sizeof(T) == 4 ? ACB_ENV_MIN_BLOCKS : 1;
+    static constexpr int guided = sizeof(T) == 4 ? ACB_GUIDED_MIN_BLOCKS : 1;
+};
+
 template <typename T>
 __global__ void __launch_bounds__(kBlock) fleet_reset_kernel(FleetPtrs<T> f, const uint8_t* __restrict__ mask,
                                                              const T* __restrict__ init_state) {
@@ -162,7 +177,7 @@ template <typename T> struct MissionPtrs {
 };
 
 template <typename T, int LEVEL>
-__global__ void __launch_bounds__(kBlock) step_guided_kernel(const __grid_constant__ DynParams<T> P,
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kernel(const __grid_constant__ DynParams<T> P,
                                                              const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
                                                              float* __restrict__ pid_outer, const T* __restrict__ cmd,
                                                              MissionPtrs<T> M, float dt_ctrl, int K, T h,
@@ -324,7 +339,7 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvPtrs<T> B, const _
 // -> controller -> PID memory stored back; (B) K RK4 substeps on 12 states + held controls; (C) the
 // env's bookkeeping words are loaded only now -> reward / termination / (cold) Philox reset -> scatter.
 template <typename T>
-__global__ void __launch_bounds__(kBlock) env_step_kernel(const __grid_constant__ DynParams<T> P,
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::env) env_step_kernel(const __grid_constant__ DynParams<T> P,
                                                           const __grid_constant__ CtrlParams<T> C,
                                                           const __grid_constant__ EnvConst<T> E, EnvPtrs<T> B,
                                                           const float* __restrict__ action, int64_t first, int64_t count) {
