@@ -47,9 +47,14 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
     const int64_t tile = blockIdx.x;
     constexpr bool kPair = CTA == 2;
     const uint32_t rank = kPair ? cluster_ctarank() : 0u;      // 0: leader of the pair
-    // barriers the leader's MMA warp waits on collect arrivals from both blocks: address them in the leader
+    // Barriers the leader's MMA warp waits on collect arrivals from both blocks.  The leader's own warps arrive locally;
+    // the peer's arrive remotely and RELAXED: what the arrival announces is either "my tensor-memory reads are done"
+    // (tcgen05.wait::ld + tcgen05.fence) or "my rows of the next operand are written" -- rows that only the peer's own
+    // tensor core will read, from the peer's own shared memory, and that every lane has already pushed through
+    // fence.proxy.async before the warp's __syncwarp.  Nothing the leader's threads read depends on it, so the
+    // cluster-scope release (a ~1000-cycle fence per layer hand-off, measured) buys nothing here.
     auto lead = [&](int i) { return kPair ? mapa(bar(i), 0) : bar(i); };
-    auto arrive_lead = [&](int i) { if (kPair) mbar_arrive_cluster(lead(i)); else mbar_arrive(bar(i)); };
+    auto arrive_lead = [&](int i) { if (kPair && rank != 0) mbar_arrive_cluster_relaxed(lead(i)); else mbar_arrive(bar(i)); };
     // "the operand of layer k is complete" (one lane per epilogue warp).  The peer block's MMA warp is not in the issue
     // chain, so it gets a single-use barrier for the one moment it cares about (h' ready to store; no phase it could miss).
     auto signal_operand = [&](int k) {
@@ -271,7 +276,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {
                             const float cc = sigmoid_half(__uint_as_float(vi[q]), bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]);
-                            h[q] = sigmoid_half(__uint_as_float(vo[q]), bo[q]) * tanh_fast(cc);
+                            h[q] = sigmoid_half(__uint_as_float(vo[q]), bo[q]) * tanh_unit(cc);     // |cc| < 1
                         }
                         store_row16(act, L.out_off, c * U + j, row, h);
                     }
@@ -326,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) { if (kPair) mbar_arrive_cluster_relaxed(lead(B_ACC_EMPTY + a)); else mbar_arrive(bar(B_ACC_EMPTY + a)); }
+                if (lane == 0) arrive_lead(B_ACC_EMPTY + a);
                 if (tr) P.trace[ti++] = clock64();
             }
             if (l == P.recurrent_layer - 1) {
@@ -387,7 +392,7 @@ struct acb200_policy {
     size_t weight_bytes = 0;
     double flops_per_aircraft = 0.0;   // algorithmic: 2 * out * in over the layers, h0 = 0 products excluded
     int device = 0;
-    int cta = 1;                       // thread blocks per MMA: 1 = single block (default), 2 = SM pair (cta_group::2)
+    int cta = 2;                       // thread blocks per MMA: 2 = SM pair (cta_group::2, default), 1 = single block
 };
 
 namespace {
@@ -489,9 +494,10 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
 int build_policy(acb200_ctx* ctx, int kind, std::vector<HostLayer>& layers, acb200_policy** out) {
     acb200_policy* p = new acb200_policy();
     p->kind = kind;
-    // ACB200_POLICY_CTA=2 selects the SM-pair kernel (cta_group::2 MMAs, tensor-map weight loads, half the weight traffic
-    // per SM).  Both pass the same tests; they measure the same on C4, so the simpler one is the default.
-    if (const char* v = getenv("ACB200_POLICY_CTA")) p->cta = atoi(v) == 2 ? 2 : 1;
+    // Default: the SM-pair kernel (cta_group::2 MMAs, tensor-map weight loads onto the leader's barrier, half the weight
+    // traffic per SM): 0.513 ms against 0.561 ms per 262 144-aircraft forward.  ACB200_POLICY_CTA=1 selects
+    // the single-block kernel (same arithmetic, bit-identical results; tests/test_gpu_policy.py compares the two).
+    if (const char* v = getenv("ACB200_POLICY_CTA")) p->cta = atoi(v) == 1 ? 1 : 2;
     const int rc = finish_policy(ctx, p, layers, out);
     if (rc != ACB200_OK) acb200_policy_destroy(p);
     return rc;

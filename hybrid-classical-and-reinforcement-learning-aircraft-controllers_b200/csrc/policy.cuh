@@ -257,6 +257,16 @@ __device__ __forceinline__ float tanh_fast(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// tanh on [-1, 1] on the FMA pipe: x * P(x^2), P of degree 3, max abs error 3.3e-5 (tanh.approx itself: ~5e-4).  Used where
+// the argument is a product of a sigmoid and a tanh, so that one of the four transcendentals per stateless LSTM unit
+// leaves the MUFU pipe, which is what bounds the epilogue (tools/fit_tanh_unit.py refits the coefficients).
+__device__ __forceinline__ float tanh_unit(float x) {
+    const float t = x * x;
+    float p = fmaf(t, -0.024656429886817932f, 0.11541730910539627f);
+    p = fmaf(t, p, -0.3288934528827667f);
+    p = fmaf(t, p, 0.9996939301490784f);
+    return x * p;
+}
 // sigmoid(z) with z = 2 * (0.5 * acc + 0.5 * b): the bias array holds 0.5 * b for these gates, so one FFMA feeds the MUFU
 __device__ __forceinline__ float sigmoid_half(float acc, float half_b) { return fmaf(0.5f, tanh_fast(fmaf(acc, 0.5f, half_b)), 0.5f); }
 
