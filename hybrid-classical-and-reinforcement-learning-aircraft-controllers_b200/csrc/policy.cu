@@ -27,7 +27,8 @@ using namespace acbp;
 namespace {
 
 // barrier slots inside the 128-byte barrier block
-enum { B_FULL = 0, B_EMPTY = 4, B_ACC_FULL = 8, B_ACC_EMPTY = 10, B_ACT = 12, B_HFULL = 13, B_BIAS = 14, B_HGO = 15, B_COUNT = 16 };   // B_HGO: h' may be stored (peer block of a pair)
+enum { B_FULL = 0, B_EMPTY = 4, B_ACC_FULL = 8, B_ACC_EMPTY = 10, B_ACT = 12, B_HFULL = 13, B_BIAS = 14, B_HGO = 15, B_YFREE = 16, B_COUNT = 17 };
+// B_HGO: h' may be stored (peer block of a pair); B_YFREE: the bulk store of h' has finished reading buffer Y
 
 // CTA == 1: one thread block per 128-aircraft tile.  CTA == 2: a cluster of two blocks (an SM pair) works as one
 // 256-row tile: the leader's MMA warp issues cta_group::2 instructions for both, each block stages only HALF of every
@@ -44,9 +45,14 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kBarOff + 8 * B_COUNT);
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler
-    const int64_t tile = blockIdx.x;
     constexpr bool kPair = CTA == 2;
     const uint32_t rank = kPair ? cluster_ctarank() : 0u;      // 0: leader of the pair
+    // Persistent: block (pair) b walks the tile groups b, b + G, b + 2G, ...; barriers, tensor memory and the biases are
+    // set up once, the weight ring and the accumulator ring keep turning across tiles (the producer is already loading
+    // the next tile's first stages while this tile's last layers drain).  Every role below runs the same sequence.
+    const int64_t n_groups = ((P.n + kTile - 1) / kTile + CTA - 1) / CTA;     // tiles (single) or tile pairs
+    const int64_t group0 = blockIdx.x / CTA, group_stride = gridDim.x / CTA;
+    auto tile_of = [&](int64_t g) { return g * CTA + (int64_t)rank; };
     // Barriers the leader's MMA warp waits on collect arrivals from both blocks.  The leader's own warps arrive locally;
     // the peer's arrive remotely and RELAXED: what the arrival announces is either "my tensor-memory reads are done"
     // (tcgen05.wait::ld + tcgen05.fence) or "my rows of the next operand are written" -- rows that only the peer's own
@@ -67,6 +73,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         for (int a = 0; a < 2; ++a) { mbar_init(bar(B_ACC_FULL + a), 1); mbar_init(bar(B_ACC_EMPTY + a), kEpiWarps * CTA); }   // one arrival per epilogue warp
         mbar_init(bar(B_ACT), kEpiWarps * CTA);
         mbar_init(bar(B_HGO), kEpiWarps);
+        mbar_init(bar(B_YFREE), 1);
         mbar_init(bar(B_HFULL), 1);
         mbar_init(bar(B_BIAS), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -83,8 +90,9 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         if (lane == 0) {
             mbar_expect_tx(bar(B_BIAS), (uint32_t)P.n_bias * 4u);
             bulk_g2s(smem_base + kBiasOff, P.bias, (uint32_t)P.n_bias * 4u, bar(B_BIAS));
-            const uint8_t* src = P.weights;
             uint32_t it = 0;
+            for (int64_t g = group0; g < n_groups; g += group_stride) {
+            const uint8_t* src = P.weights;
             for (int l = 0; l < P.n_layers; ++l) {
                 const LayerDesc& L = P.L[l];
                 const uint32_t bytes = (uint32_t)(L.N_c / CTA) * (uint32_t)L.K_s * 2u;   // this block's share of a stage
@@ -105,6 +113,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     }
                 }
             }
+            }
         }
     } else if (warp == kEpiWarps + 1) {
         // ================= MMA issuer: the whole warp walks the chain (so that addresses and descriptors stay in
@@ -114,27 +123,39 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         const bool tr = (P.debug & 4) && blockIdx.x == 0 && leader;
         int ti = 0;
         if (tr) P.trace[ti++] = clock64();
+        // h' -> HBM: one bulk store out of buffer Y; once its reads of Y are done the next tile's first layer may
+        // overwrite Y (B_YFREE), the write itself only has to land before the kernel ends
+        auto store_h = [&](int64_t tile) {
+            if (leader) {
+                bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
+                bulk_commit();
+            }
+        };
+        auto release_y = [&]() {       // not in the issue path: called once the tile's last MMAs are on their way
+            if (leader) {
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                mbar_arrive(bar(B_YFREE));
+            }
+            __syncwarp();
+        };
+        uint32_t tile_it = 0;
+        for (int64_t g = group0; g < n_groups; g += group_stride, ++tile_it) {
+        const int64_t tile = tile_of(g);
         if (rank != 0) {
             // peer block of a pair: nothing to issue, only its own tile's recurrent state to move
             if (P.recurrent_layer >= 0) {
-                mbar_wait(bar(B_HGO), 0, P.error_flag, 251);
-                if (leader) {
-                    bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
-                    bulk_commit();
-                    bulk_wait_all();
-                }
+                mbar_wait(bar(B_HGO), tile_it & 1, P.error_flag, 251);
+                store_h(tile);
+                release_y();
             }
-        } else
+            continue;
+        }
+        const uint32_t act_base = tile_it * (uint32_t)(P.n_layers + 1);     // B_ACT completes n_layers + 1 phases per tile
         for (int l = 0; l < P.n_layers; ++l) {
             const LayerDesc& L = P.L[l];
-            mbar_wait<kPair>(bar(B_ACT), l & 1, P.error_flag, 200 + l);   // operand of layer l is complete (in both blocks of a pair)
-            if (tr) P.trace[ti++] = clock64();
-            if (P.recurrent_layer >= 0 && leader) {
-                if (l == P.recurrent_layer + 1) {                      // Y holds h' as a finished operand tile
-                    bulk_s2g(P.h_state + tile * (int64_t)kHTileBytes, smem_base + kXBytes, kHTileBytes);
-                    bulk_commit();
-                }
-            }
+            mbar_wait<kPair>(bar(B_ACT), (act_base + l) & 1, P.error_flag, 200 + l);   // operand of layer l is complete (in both blocks of a pair)
+            if (tr && tile_it == (uint32_t)(P.debug >> 4)) P.trace[ti++] = clock64();
+            if (P.recurrent_layer >= 0 && l == P.recurrent_layer + 1) store_h(tile);   // Y holds h' as a finished operand tile
             tc_fence_after();
             const uint32_t idesc = instr_desc_bf16(L.N_c, kTile * CTA);
             const uint32_t lbo_b = (uint32_t)(L.N_c / CTA) * 16u;
@@ -149,7 +170,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     mbar_wait<kPair>(bar(B_ACC_EMPTY + a), (use - 1) & 1, P.error_flag, 300 + l);
                     tc_fence_after();
                 }
-                if (tr) P.trace[ti++] = clock64();
+                if (tr && tile_it == (uint32_t)(P.debug >> 4)) P.trace[ti++] = clock64();
                 const uint32_t d_tmem = tmem_base + a * 256u;
                 uint64_t a_desc = a_desc0;
                 uint32_t accumulate = 0;
@@ -175,20 +196,31 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     if (++slot == kStages) { slot = 0; slot_phase ^= 1; }
                 }
                 if (leader) umma_commit<CTA>(bar(B_ACC_FULL + a));        // accumulator chunk complete
-                if (tr) P.trace[ti++] = clock64();
+                if (tr && tile_it == (uint32_t)(P.debug >> 4)) P.trace[ti++] = clock64();
             }
         }
-        if (rank == 0 && P.recurrent_layer >= 0 && leader) bulk_wait_all();
+        // the last phase of B_ACT of this tile ("last layer's epilogue done") has no MMA behind it: step over it, so that
+        // the wait for the next tile's first operand cannot be satisfied by it
+        if (P.recurrent_layer >= 0) release_y();
+        mbar_wait<kPair>(bar(B_ACT), (act_base + P.n_layers) & 1, P.error_flag, 299);
+        }
+        if (P.recurrent_layer >= 0 && leader) bulk_wait_all();
     } else {
         // ================= epilogue: 8 warps; warp w reads tensor-memory lanes 32*(w%4).., i.e. aircraft row
         // 32*(w%4)+lane, and takes half (w/4) of every chunk's columns =================
         const int half = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
+        const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
+        uint32_t chunk_it = 0, tile_it = 0;
+        const bool tr0 = (P.debug & 4) && blockIdx.x == 0 && threadIdx.x == 0;
+        int ti = 1024;
+        for (int64_t g = group0; g < n_groups; g += group_stride, ++tile_it) {
+        const int64_t tile = tile_of(g);
+        const bool tr = tr0 && tile_it == (uint32_t)(P.debug >> 4);
         const int64_t e = tile * kTile + row;
         const bool valid = e < P.n;
         const bool fresh = valid && ((P.episode_start != nullptr && P.episode_start[e] != 0) ||
                                      (P.episode_start_b != nullptr && P.episode_start_b[e] != 0));
-        const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
 
         if (half == 0) {
             // observation -> X as [hi | lo | hi | 0] bf16 columns (64 wide) against [W_hi | W_hi | W_lo | 0]:
@@ -223,11 +255,10 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         fence_async_smem();
         __syncwarp();
         if (lane == 0) signal_operand(0);
-        mbar_wait(bar(B_BIAS), 0, P.error_flag, 700);
+        if (tile_it == 0) mbar_wait(bar(B_BIAS), 0, P.error_flag, 700);
+        // the first layer writes buffer Y: the previous tile's h' must have left it
+        if (tile_it > 0 && P.recurrent_layer >= 0) mbar_wait(bar(B_YFREE), (tile_it - 1) & 1, P.error_flag, 701);
 
-        uint32_t chunk_it = 0;
-        const bool tr = (P.debug & 4) && blockIdx.x == 0 && threadIdx.x == 0;
-        int ti = 1024;
         if (tr) P.trace[ti++] = clock64();
         for (int l = 0; l < P.n_layers; ++l) {
             const LayerDesc& L = P.L[l];
@@ -336,7 +367,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             }
             if (l == P.recurrent_layer - 1) {
                 // h_prev has landed behind the features; a fresh episode starts from zeros ((1 - episode_start) * h)
-                mbar_wait(bar(B_HFULL), 0, P.error_flag, 600);
+                mbar_wait(bar(B_HFULL), tile_it & 1, P.error_flag, 600);
                 if (fresh || !valid) {
                     const uint4 z = make_uint4(0, 0, 0, 0);
                     for (int kc = half * (kHidden / 16); kc < (half + 1) * (kHidden / 16); ++kc)
@@ -346,6 +377,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             fence_async_smem();
             __syncwarp();
             if (lane == 0) signal_operand(l + 1);
+        }
         }
     }
 
@@ -392,6 +424,7 @@ struct acb200_policy {
     size_t weight_bytes = 0;
     double flops_per_aircraft = 0.0;   // algorithmic: 2 * out * in over the layers, h0 = 0 products excluded
     int device = 0;
+    int resident = 0;                  // blocks (single) / clusters (pair) that fit on the device at once: the persistent grid
     int cta = 2;                       // thread blocks per MMA: 2 = SM pair (cta_group::2, default), 1 = single block
 };
 
@@ -665,10 +698,30 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
     if ((debug & 4) && !trace) { cudaMalloc(&trace, 2048 * sizeof(long long)); cudaMemset(trace, 0, 2048 * sizeof(long long)); }
     P.trace = trace;
     const int64_t tiles = (n + kTile - 1) / kTile;
+    const int64_t groups = (tiles + p->cta - 1) / p->cta;            // an odd last tile gets an all-padding partner
     cudaError_t e;
+    if (p->resident == 0) {          // persistent grid: as many blocks / clusters as the device holds at once
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        p->resident = sms > 0 ? sms / p->cta : 1;
+        if (p->cta == 2) {
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(2 * (unsigned)p->resident); q.blockDim = dim3(kThreads); q.dynamicSmemBytes = kSmemBytes;
+            cudaLaunchAttribute a[1];
+            a[0].id = cudaLaunchAttributeClusterDimension;
+            a[0].val.clusterDim.x = 2; a[0].val.clusterDim.y = 1; a[0].val.clusterDim.z = 1;
+            q.attrs = a; q.numAttrs = 1;
+            int clusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&clusters, policy_forward_kernel<2>, &q) == cudaSuccess && clusters > 0)
+                p->resident = clusters;
+            else
+                cudaGetLastError();
+        }
+    }
+    const unsigned n_blocks = (unsigned)(groups < p->resident ? groups : p->resident);
     if (p->cta == 2) {
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)((tiles + 1) & ~(int64_t)1));   // an odd last tile gets an all-padding partner
+        cfg.gridDim = dim3(2 * n_blocks);
         cfg.blockDim = dim3(kThreads);
         cfg.dynamicSmemBytes = kSmemBytes;
         cfg.stream = ctx->stream;
@@ -678,7 +731,7 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
         cfg.attrs = attr; cfg.numAttrs = 1;
         e = cudaLaunchKernelEx(&cfg, policy_forward_kernel<2>, P);
     } else {
-        policy_forward_kernel<1><<<(unsigned)tiles, kThreads, kSmemBytes, ctx->stream>>>(P);
+        policy_forward_kernel<1><<<n_blocks, kThreads, kSmemBytes, ctx->stream>>>(P);
         e = cudaGetLastError();
     }
     ctx->launches += 1;
