@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                         load_bias16(bias + j, b);
                         tmem_ld_wait(v);
 #pragma unroll
-                        for (int q = 0; q < 16; ++q) h[q] = fmaxf(__uint_as_float(v[q]) + b[q], 0.f);
+                        for (int q = 0; q < 16; ++q) h[q] = max_nan(__uint_as_float(v[q]) + b[q], 0.f);
                         store_row16(act, L.out_off, c * L.N_c + j, row, h);
                     }
                 } else if (L.epi == EPI_LSTM0) {
@@ -352,10 +352,10 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                         tmem_ld_wait(v);
                         if (valid) {
                             float4 o;
-                            o.x = fminf(fmaxf(__uint_as_float(v[0]) + bias[0], -1.f), 1.f);
-                            o.y = fminf(fmaxf(__uint_as_float(v[1]) + bias[1], -1.f), 1.f);
-                            o.z = fminf(fmaxf(__uint_as_float(v[2]) + bias[2], -1.f), 1.f);
-                            o.w = fminf(fmaxf(__uint_as_float(v[3]) + bias[3], 0.f), 1.f);
+                            o.x = min_nan(max_nan(__uint_as_float(v[0]) + bias[0], -1.f), 1.f);
+                            o.y = min_nan(max_nan(__uint_as_float(v[1]) + bias[1], -1.f), 1.f);
+                            o.z = min_nan(max_nan(__uint_as_float(v[2]) + bias[2], -1.f), 1.f);
+                            o.w = min_nan(max_nan(__uint_as_float(v[3]) + bias[3], 0.f), 1.f);
                             reinterpret_cast<float4*>(P.action)[e] = o;
                         }
                     }

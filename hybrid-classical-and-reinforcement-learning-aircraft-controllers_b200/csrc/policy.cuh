@@ -270,6 +270,17 @@ __device__ __forceinline__ float tanh_unit(float x) {
 // sigmoid(z) with z = 2 * (0.5 * acc + 0.5 * b): the bias array holds 0.5 * b for these gates, so one FFMA feeds the MUFU
 __device__ __forceinline__ float sigmoid_half(float acc, float half_b) { return fmaf(0.5f, tanh_fast(fmaf(acc, 0.5f, half_b)), 0.5f); }
 
+// NaN-propagating max / min: torch.relu and np.clip hand a NaN through, fmaxf / fminf would swallow it
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float y;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(y) : "f"(a), "f"(b));
+    return y;
+}
+__device__ __forceinline__ float min_nan(float a, float b) {
+    float y;
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(y) : "f"(a), "f"(b));
+    return y;
+}
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&t);

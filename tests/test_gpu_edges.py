@@ -1,0 +1,70 @@
+"""Edge cases of the C-ABI path: empty and ragged fleets, single aircraft, bad arguments, non-finite inputs."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("precision", [32, 64])
+def test_ragged_sizes_match_a_larger_run(precision):
+    """n = 1, 127, 129, 1000: every aircraft's result equals the same aircraft's result inside a 4096-aircraft run
+    (block tails, warp tails, the obs staging through shared memory)."""
+    import acb200
+    big = acb200.BatchedRateControlEnv(4096, controller="attitude_pid", precision=precision, seed=9)
+    big.reset()
+    for _ in range(3):
+        big.step()
+    for n in (1, 127, 129, 1000):
+        env = acb200.BatchedRateControlEnv(n, controller="attitude_pid", precision=precision, seed=9)
+        env.reset()
+        for _ in range(3):
+            env.step()
+        assert torch.equal(env.state, big.state[:, :n])
+        assert torch.equal(env.obs, big.obs[:n])
+        assert torch.equal(env.reward, big.reward[:n])
+
+
+def test_empty_fleet_is_a_no_op():
+    import acb200
+    import ctypes as C
+    ctx = acb200.Context(0)
+    before = ctx.launch_count
+    # GAE over nothing, policy over nothing: OK without a launch
+    assert ctx.lib.acb200_gae(ctx.handle, 0, 0, 1, 1, 1, 1, 1, 0.99, 0.95, 1, 1) == 0
+    pol = acb200.LearnedPolicyB200(acb200.policy.random_policy_state_dict("mlp", 0), kind="mlp", n=1, ctx=ctx)
+    obs = torch.zeros((1, 18), device="cuda"); act = torch.zeros((1, 4), device="cuda")
+    assert ctx.lib.acb200_policy_forward(ctx.handle, pol.handle, 0, obs.data_ptr(), None, None, None, None, act.data_ptr()) == 0
+    assert ctx.launch_count == before
+
+
+def test_bad_arguments_raise_like_the_reference():
+    import acb200
+    fleet = acb200.AircraftFleet(8, precision=64)
+    ctrl = torch.zeros((4, 8), dtype=torch.float64, device="cuda")
+    coarse = acb200.AircraftFleet(8, precision=64, config={"dt_physics": 2.0})
+    with pytest.raises(ValueError):                      # simplified_6dof.py:241-245: substep above max_timestep
+        coarse.step_surface(ctrl, 2.0)
+    with pytest.raises(ValueError):
+        fleet.step_surface(ctrl, float("nan"))
+    with pytest.raises(ValueError):
+        fleet.step_surface(ctrl, -0.01)
+    with pytest.raises(RuntimeError):                    # mission not set
+        fleet.step_waypoint(0.01)
+    ctx = acb200.Context(0)
+    assert ctx.lib.acb200_gae(ctx.handle, 4, 4, None, None, None, None, None, 0.99, 0.95, None, None) == -3   # ACB200_ENULL
+
+
+def test_non_finite_observation_stays_in_its_row():
+    """A NaN observation poisons that aircraft's action only (rows are independent through every layer)."""
+    import acb200
+    n = 256
+    pol = acb200.LearnedPolicyB200(acb200.policy.random_policy_state_dict("lstm", 0), kind="lstm", n=n)
+    obs = torch.randn(n, 18, device="cuda")
+    clean = pol(obs).clone()
+    pol.reset_state()
+    obs2 = obs.clone(); obs2[5, 3] = float("nan"); obs2[200, 0] = float("inf")
+    dirty = pol(obs2).clone()
+    keep = torch.ones(n, dtype=torch.bool, device="cuda"); keep[5] = False; keep[200] = False
+    assert torch.equal(dirty[keep], clean[keep])
+    assert not torch.isfinite(dirty[5]).all()
