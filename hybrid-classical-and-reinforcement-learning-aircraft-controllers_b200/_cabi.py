@@ -54,6 +54,16 @@ class ControllerParamsC(C.Structure):
                 ("max_speed_reduction", C.c_double), ("min_speed", C.c_double)]
 
 
+SENSOR_STDDEV_KEYS = ("imu_gyro_stddev", "imu_accel_stddev", "gps_position_stddev", "gps_velocity_stddev", "airspeed_stddev",
+                      "altitude_stddev", "attitude_stddev")
+
+
+class SensorConfigC(C.Structure):
+    _fields_ = [("enabled", C.c_int32), ("_pad", C.c_int32)] + [(k, C.c_double) for k in SENSOR_STDDEV_KEYS] + [
+        ("gyro_bias_walk_stddev", C.c_double), ("accel_bias_walk_stddev", C.c_double), ("seed", C.c_uint64),
+        ("id_offset", C.c_int64)]
+
+
 class MissionC(C.Structure):
     _fields_ = [("waypoints", C.c_void_p), ("n_waypoints", C.c_int32), ("guidance", C.c_int32), ("wp_index", C.c_void_p),
                 ("loop", C.c_int32), ("_pad", C.c_int32), ("acceptance_radius", C.c_double)]
@@ -103,6 +113,7 @@ SYMBOLS = [
     "acb200_policy_create_lstm", "acb200_policy_create_mlp", "acb200_policy_destroy", "acb200_policy_state_bytes",
     "acb200_policy_forward", "acb200_policy_state_export", "acb200_policy_state_import", "acb200_policy_info",
     "acb200_gae",
+    "acb200_default_sensor_config", "acb200_sensor_update", "acb200_sensor_reset",
 ]
 
 _lib = None
@@ -153,6 +164,10 @@ def load() -> C.CDLL:
     L.acb200_policy_state_import.argtypes = [vp, vp, i64, vp, vp, vp, vp]
     L.acb200_policy_info.argtypes = [vp, P(dbl), P(C.c_size_t), P(i32)]
     L.acb200_gae.argtypes = [vp, C.c_int32, i64, vp, vp, vp, vp, vp, dbl, dbl, vp, vp]
+    L.acb200_default_sensor_config.argtypes = [P(SensorConfigC)]
+    L.acb200_default_sensor_config.restype = None
+    L.acb200_sensor_update.argtypes = [vp, P(FleetC), P(SensorConfigC), vp, C.c_uint32, vp, vp]
+    L.acb200_sensor_reset.argtypes = [vp, i64, i32, vp, vp]
     _lib = L
     return L
 

@@ -232,6 +232,37 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_
 /* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 64k aircraft per chunk) */
 int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 
+/* ---- sensor model ------------------------------------------------------------------------
+ * NoisySensorInterface, interfaces/sensor.py:137-263: Gaussian noise on position, velocity, attitude, angular rate (plus a
+ * slowly drifting gyro bias), airspeed and altitude; gyro / accelerometer biases take one random-walk step per update.
+ * The reference draws from numpy's PCG64 Generator (sensor.py:189-190), which a counter-based generator cannot replay:
+ * parity is exact in the arithmetic given the normals (oracle: orc_sensor_update) and distributional against the reference. */
+typedef struct {
+    int32_t enabled;                 /* 0: measured = truth, biases untouched   sensor.py:204-206 */
+    int32_t _pad;
+    double imu_gyro_stddev;          /* rad/s  0.01   sensor.py:176-182 */
+    double imu_accel_stddev;         /* m/s^2  0.1    (configured and reported; AircraftState carries no acceleration) */
+    double gps_position_stddev;      /* m      1.0  */
+    double gps_velocity_stddev;      /* m/s    0.1  */
+    double airspeed_stddev;          /* m/s    0.5  */
+    double altitude_stddev;          /* m      0.5  */
+    double attitude_stddev;          /* rad    0.01 */
+    double gyro_bias_walk_stddev;    /* 1e-4 per update   sensor.py:230 */
+    double accel_bias_walk_stddev;   /* 1e-3 per update   sensor.py:231 */
+    uint64_t seed;                   /* Philox key */
+    int64_t id_offset;               /* global id of local aircraft 0 */
+} acb200_sensor_config;
+
+void acb200_default_sensor_config(acb200_sensor_config* c);
+/* sensor.update(true_state) for every aircraft: reads f->state / f->derived, writes measured_state real[13][n] (time copied)
+ * and measured_derived real[4][n] (airspeed, altitude noisy; ground_speed, heading copied).  bias real[6][n] = gyro_bias[3],
+ * accel_bias[3], read and advanced.  tick: the update counter (Philox counter word) -- the caller passes 0,1,2,...; the same
+ * (seed, global id, tick) always yields the same noise.  Negative or non-finite stddev -> ACB200_EVALUE. */
+int acb200_sensor_update(acb200_ctx* ctx, const acb200_fleet* f, const acb200_sensor_config* cfg, void* bias, uint32_t tick,
+                         void* measured_state, void* measured_derived);
+/* sensor.reset(): zero the biases of aircraft with mask[i] != 0 (NULL = all)   sensor.py:245-251 */
+int acb200_sensor_reset(acb200_ctx* ctx, int64_t n, int32_t precision, void* bias, const uint8_t* mask);
+
 /* ---- learned rate policy, actor forward (row a20) -------------------------------------------------------------
  * Replaces: model.predict(obs, state=lstm_state, deterministic=True) at controllers/learned_rate_agent.py:220-227
  * with the network of learned_controllers/networks/lstm_policy.py:13-164 (LSTMFeaturesExtractor + sb3-contrib's

@@ -690,6 +690,86 @@ static inline void rng_block(rng_t* g, uint32_t block, uint32_t out[4]) {
 }
 
 /* ------------------------------------------------------------------------------------------
+ * NoisySensorInterface.update for a fleet -- interfaces/sensor.py:200-243.
+ *   measured position/velocity/attitude = truth + sigma * z           (:209-217)
+ *   measured angular_rate = truth + sigma_gyro * z + gyro_bias        (:218-222, the bias BEFORE this update's walk)
+ *   measured airspeed / altitude = truth + sigma * z                  (:223-228)
+ *   gyro_bias += 1e-4 * z;  accel_bias += 1e-3 * z                    (:230-231)
+ * in that draw order (20 normals per update).  The reference's z come from numpy's PCG64 ziggurat (sensor.py:189-190),
+ * which cannot be replayed by a counter-based generator; here z = Box-Muller on Philox4x32-10 words keyed
+ * (seed; global id, tick, 'SEN'+block), the stream csrc/sensor.cu uses, so kernel-vs-oracle parity is tight and
+ * parity with the reference is distributional (tests/test_sensor.py against tests/golden/sensor_stats.json).
+ * ---------------------------------------------------------------------------------------- */
+#define ORC_SENSOR_STREAM 0x53454E00u
+
+static void normal_pair(uint32_t w0, uint32_t w1, double* z0, double* z1) {
+    const double two_pi = 6.283185307179586476925286766559;
+    const double u1 = ((double)w0 + 0.5) * (1.0 / 4294967296.0);
+    const double u2 = ((double)w1 + 0.5) * (1.0 / 4294967296.0);
+    const double r = sqrt(-2.0 * log(u1));
+    *z0 = r * cos(two_pi * u2);
+    *z1 = r * sin(two_pi * u2);
+}
+
+void orc_sensor_normals(uint64_t seed, int64_t global_id, uint32_t tick, double z[20]) {
+    rng_t g;
+    rng_init(&g, seed, global_id, tick);
+    for (uint32_t k = 0; k < 5; ++k) {
+        uint32_t w[4];
+        rng_block(&g, ORC_SENSOR_STREAM + k, w);
+        normal_pair(w[0], w[1], &z[4 * k + 0], &z[4 * k + 1]);
+        normal_pair(w[2], w[3], &z[4 * k + 2], &z[4 * k + 3]);
+    }
+}
+
+static int sensor_sigma_ok(const orc_sensor_config* S) {
+    const double sd[9] = {S->imu_gyro_stddev, S->imu_accel_stddev, S->gps_position_stddev, S->gps_velocity_stddev,
+                          S->airspeed_stddev, S->altitude_stddev, S->attitude_stddev, S->gyro_bias_walk_stddev,
+                          S->accel_bias_walk_stddev};
+    for (int k = 0; k < 9; ++k) if (!(sd[k] >= 0.0) || isinf(sd[k])) return 0;   /* Generator.normal: "scale < 0" */
+    return 1;
+}
+
+/* one aircraft, given its 20 standard normals in the reference's draw order */
+static void sensor_apply_one(const orc_sensor_config* S, double s[13], double d[4], double b[6], const double z[20]) {
+    for (int a = 0; a < 3; ++a) {
+        s[a] = s[a] + S->gps_position_stddev * z[a];
+        s[3 + a] = s[3 + a] + S->gps_velocity_stddev * z[3 + a];
+        s[6 + a] = s[6 + a] + S->attitude_stddev * z[6 + a];
+        s[9 + a] = (s[9 + a] + S->imu_gyro_stddev * z[9 + a]) + b[a];
+    }
+    d[0] = d[0] + S->airspeed_stddev * z[12];
+    d[1] = d[1] + S->altitude_stddev * z[13];
+    for (int a = 0; a < 3; ++a) {
+        b[a] = b[a] + S->gyro_bias_walk_stddev * z[14 + a];
+        b[3 + a] = b[3 + a] + S->accel_bias_walk_stddev * z[17 + a];
+    }
+}
+
+/* z_ext NULL: z = the Philox/Box-Muller stream of (seed, id_offset + i, tick).  z_ext [20][n]: caller-supplied standard
+ * normals (the tests pass numpy's PCG64 draws to compare with the reference bit for bit). */
+int orc_sensor_update(const orc_sensor_config* S, int64_t n, const double* state, const double* derived, double* bias,
+                      uint32_t tick, const double* z_ext, double* m_state, double* m_derived) {
+    if (!sensor_sigma_ok(S)) return -1;
+    for (int64_t i = 0; i < n; ++i) {
+        double s[13], d[4];
+        for (int f = 0; f < 13; ++f) s[f] = state[(int64_t)f * n + i];
+        for (int f = 0; f < 4; ++f) d[f] = derived[(int64_t)f * n + i];
+        if (S->enabled) {
+            double z[20], b[6];
+            if (z_ext) for (int k = 0; k < 20; ++k) z[k] = z_ext[(int64_t)k * n + i];
+            else orc_sensor_normals(S->seed, S->id_offset + i, tick, z);
+            for (int f = 0; f < 6; ++f) b[f] = bias[(int64_t)f * n + i];
+            sensor_apply_one(S, s, d, b, z);
+            for (int f = 0; f < 6; ++f) bias[(int64_t)f * n + i] = b[f];
+        }
+        for (int f = 0; f < 13; ++f) m_state[(int64_t)f * n + i] = s[f];
+        for (int f = 0; f < 4; ++f) m_derived[(int64_t)f * n + i] = d[f];
+    }
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------
  * environment
  * ---------------------------------------------------------------------------------------- */
 #define OBS 18

@@ -175,6 +175,20 @@ int orc_env_step(const orc_aircraft_params* P, const orc_controller_params* C, c
 /* Philox4x32-10 block, exposed for the known-answer test. */
 void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 
+/* NoisySensorInterface (interfaces/sensor.py:137-263); same field order as acb200_sensor_config */
+typedef struct {
+    int32_t enabled, _pad;
+    double imu_gyro_stddev, imu_accel_stddev, gps_position_stddev, gps_velocity_stddev, airspeed_stddev, altitude_stddev,
+        attitude_stddev, gyro_bias_walk_stddev, accel_bias_walk_stddev;
+    uint64_t seed;
+    int64_t id_offset;
+} orc_sensor_config;
+void orc_sensor_normals(uint64_t seed, int64_t global_id, uint32_t tick, double z[20]);
+/* state [13][n], derived [4][n], bias [6][n] (in/out), z_ext [20][n] or NULL (Philox stream), m_state [13][n],
+ * m_derived [4][n]; -1 for a bad stddev */
+int orc_sensor_update(const orc_sensor_config* S, int64_t n, const double* state, const double* derived, double* bias,
+                      uint32_t tick, const double* z_ext, double* m_state, double* m_derived);
+
 #ifdef __cplusplus
 }
 #endif

@@ -81,6 +81,17 @@ class EnvConfig(C.Structure):
     ]
 
 
+SENSOR_STDDEV_KEYS = ("imu_gyro_stddev", "imu_accel_stddev", "gps_position_stddev", "gps_velocity_stddev", "airspeed_stddev",
+                      "altitude_stddev", "attitude_stddev")
+SENSOR_DEFAULTS = dict(zip(SENSOR_STDDEV_KEYS, (0.01, 0.1, 1.0, 0.1, 0.5, 0.5, 0.01)))     # interfaces/sensor.py:176-182
+
+
+class SensorConfig(C.Structure):
+    _fields_ = [("enabled", C.c_int32), ("_pad", C.c_int32)] + [(k, C.c_double) for k in SENSOR_STDDEV_KEYS] + [
+        ("gyro_bias_walk_stddev", C.c_double), ("accel_bias_walk_stddev", C.c_double), ("seed", C.c_uint64),
+        ("id_offset", C.c_int64)]
+
+
 def build(force: bool = False) -> str:
     """Compile the restatement (and nothing else) if the .so is missing or stale."""
     src = os.path.join(_HERE, "acb_oracle.c")
@@ -124,6 +135,9 @@ def lib() -> C.CDLL:
         L.orc_env_step.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.POINTER(EnvConfig),
                                    C.POINTER(EnvBuffers), C.c_void_p, C.c_int]
         L.orc_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_sensor_normals.argtypes = [C.c_uint64, C.c_int64, C.c_uint32, C.c_void_p]
+        L.orc_sensor_update.argtypes = [C.POINTER(SensorConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
+                                        C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -287,3 +301,34 @@ def philox(ctr, key):
     c = np.asarray(ctr, np.uint32); k = np.asarray(key, np.uint32); out = np.zeros(4, np.uint32)
     lib().orc_philox4x32_10(c.ctypes.data, k.ctypes.data, out.ctypes.data)
     return out
+
+
+# ---- NoisySensorInterface (interfaces/sensor.py:137-263) ---------------------------------------------------------------
+def sensor_config(noise_config: dict | None = None, id_offset: int = 0) -> SensorConfig:
+    """The reference's noise_config dict (sensor.py:146-182) -> POD.  ``seed`` None is not reproducible there; 0 here."""
+    nc = dict(noise_config or {})
+    c = SensorConfig(enabled=int(bool(nc.get("enabled", True))), gyro_bias_walk_stddev=0.0001, accel_bias_walk_stddev=0.001,
+                     seed=int(nc.get("seed") or 0), id_offset=id_offset)
+    for k in SENSOR_STDDEV_KEYS:
+        setattr(c, k, float(nc.get(k, SENSOR_DEFAULTS[k])))
+    return c
+
+
+def sensor_normals(seed: int, global_id: int, tick: int) -> np.ndarray:
+    z = np.zeros(20)
+    lib().orc_sensor_normals(seed, global_id, tick, z.ctypes.data)
+    return z
+
+
+def sensor_update(cfg: SensorConfig, state, derived_in, bias, tick: int, z=None):
+    """state [13][n], derived [4][n] float64 (truth); bias [6][n] float64 advanced in place -> (m_state, m_derived).
+    z [20][n]: caller-supplied standard normals in the reference's draw order instead of the Philox stream."""
+    n = state.shape[1]
+    _chk(state, np.float64, (13, n)); _chk(derived_in, np.float64, (4, n)); _chk(bias, np.float64, (6, n))
+    if z is not None:
+        _chk(z, np.float64, (20, n))
+    ms, md = np.empty_like(state), np.empty_like(derived_in)
+    if lib().orc_sensor_update(C.byref(cfg), n, _ptr(state), _ptr(derived_in), _ptr(bias), tick, _ptr(z), _ptr(ms),
+                               _ptr(md)) != 0:
+        raise ValueError("scale < 0")
+    return ms, md

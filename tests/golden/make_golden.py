@@ -382,8 +382,66 @@ def gen_guidance(pool):
         print("waypoint", guidance, "final waypoint index per aircraft", res[0][2][-1], [int(r[2][-1]) for r in res])
 
 
+# ------------------------------------------------------------------------------------------------
+def gen_sensor():
+    """NoisySensorInterface (interfaces/sensor.py:137-263): per case, T updates on a moving truth.  The fixture keeps the
+    truth, the reference's measured states and bias history, and the 20 standard normals per update the reference's PCG64
+    Generator consumed (replayed here from the same seed: Generator.normal(0, s, k) = s * standard_normal(k), in
+    order), so the test can push the SAME normals through the restatement and compare bit for bit."""
+    from interfaces.sensor import NoisySensorInterface
+    cases = {
+        "default_seed42": {"enabled": True, "seed": 42},
+        "custom_seed123": {"enabled": True, "imu_gyro_stddev": 0.1, "gps_position_stddev": 5.0, "attitude_stddev": 0.05,
+                           "airspeed_stddev": 1.0, "seed": 123},              # tests/test_interfaces.py:361-369
+        "gps_seed999": {"enabled": True, "gps_position_stddev": 1.0, "seed": 999},   # tests/test_interfaces.py:406-411
+        "disabled": {"enabled": False, "imu_gyro_stddev": 100.0, "seed": 5},         # tests/test_interfaces.py:391-395
+    }
+    T = 120
+    out = {}
+    for name, nc in cases.items():
+        rng = np.random.default_rng(1000 + len(name))
+        truth = sample_initial_states(rng, T)                 # [13][T]: a different truth per update
+        truth[0:2] = rng.uniform(-500, 500, (2, T)); truth[4:6] = rng.uniform(-2, 2, (2, T)); truth[12] = 0.01 * np.arange(T)
+        der = np.stack([rng.uniform(12, 30, T), -truth[2], rng.uniform(10, 30, T), rng.uniform(0, 2 * np.pi, T)])
+        sensor = NoisySensorInterface(dict(nc))
+        meas = np.zeros((T, 17)); bias = np.zeros((T, 6))
+        for t in range(T):
+            st = AircraftState(time=float(truth[12, t]), position=truth[0:3, t].copy(), velocity=truth[3:6, t].copy(),
+                               attitude=truth[6:9, t].copy(), angular_rate=truth[9:12, t].copy(), airspeed=float(der[0, t]),
+                               altitude=float(der[1, t]), ground_speed=float(der[2, t]), heading=float(der[3, t]))
+            sensor.update(st)
+            m = sensor.get_state()
+            meas[t] = np.concatenate([m.position, m.velocity, m.attitude, m.angular_rate, [m.time, m.airspeed, m.altitude,
+                                                                                           m.ground_speed, m.heading]])
+            bias[t] = np.concatenate([sensor._gyro_bias, sensor._accel_bias])
+        z = np.random.default_rng(nc["seed"]).standard_normal((T, 20)) if nc["enabled"] else np.zeros((T, 20))
+        out[name + "/truth"] = np.concatenate([truth, der]).T.copy()      # [T][17]
+        out[name + "/measured"] = meas
+        out[name + "/bias"] = bias
+        out[name + "/z"] = z
+        out[name + "/params"] = np.array([float(nc["enabled"])] + [sensor.get_noise_parameters()[k] for k in (
+            "imu_gyro_stddev", "imu_accel_stddev", "gps_position_stddev", "gps_velocity_stddev", "airspeed_stddev",
+            "altitude_stddev", "attitude_stddev")] + [float(nc["seed"])])
+    # distribution summary of the reference's own noise: 4000 sensors x 64 updates at the default config
+    R, U = 4000, 64
+    noise = np.zeros((R, 14)); walk = np.zeros((R, 6))
+    zero = AircraftState()
+    for r in range(R):
+        sensor = NoisySensorInterface({"enabled": True, "seed": 10_000 + r})
+        for _ in range(U):
+            sensor.update(zero)
+        m = sensor.get_state()
+        noise[r] = np.concatenate([m.position, m.velocity, m.attitude, m.angular_rate - 0.0, [m.airspeed, m.altitude]])
+        walk[r] = np.concatenate([sensor._gyro_bias, sensor._accel_bias])
+    out["stats/updates"] = np.array([U]); out["stats/sensors"] = np.array([R])
+    out["stats/noise_std"] = noise.std(axis=0); out["stats/noise_mean"] = noise.mean(axis=0)
+    out["stats/walk_std"] = walk.std(axis=0); out["stats/walk_mean"] = walk.mean(axis=0)
+    np.savez_compressed(os.path.join(HERE, "sensor.npz"), **out)
+    print("sensor.npz", {k: v.shape for k, v in out.items() if k.startswith("default")}, out["stats/noise_std"], out["stats/walk_std"])
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "guidance"]
+    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "guidance", "sensor"]
     with mp.Pool(8) as pool:
         if "pid" in which: gen_pid_kat()
         if "dyn" in which: gen_dynamics_kat()
@@ -391,3 +449,4 @@ if __name__ == "__main__":
         if "cascade" in which: gen_cascade(pool)
         if "env" in which: gen_env(pool)
         if "guidance" in which: gen_guidance(pool)
+        if "sensor" in which: gen_sensor()
