@@ -99,6 +99,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 const int n_stage = L.n_chunks * (L.K / L.K_s);
                 for (int i = 0; i < n_stage; ++i, ++it) {
                     const uint32_t s = it % kStages, use = it / kStages;
+                    if (P.debug & 8) continue;          // experiment: no ring at all (the MMA warp does not wait either)
                     if (use > 0) mbar_wait(bar(B_EMPTY + s), (use - 1) & 1, P.error_flag, 100 + l);
                     if (P.debug & 1) { if (rank == 0) mbar_arrive(bar(B_FULL + s)); continue; }
                     if (kPair) {
@@ -175,7 +176,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 uint64_t a_desc = a_desc0;
                 uint32_t accumulate = 0;
                 for (int ks = 0; ks < stages_per_chunk; ++ks) {
-                    mbar_wait<kPair>(bar(B_FULL + slot), slot_phase, P.error_flag, 400 + l);
+                    if (!(P.debug & 8)) mbar_wait<kPair>(bar(B_FULL + slot), slot_phase, P.error_flag, 400 + l);
                     tc_fence_after();
                     if (leader) {
                         uint64_t b_desc = b_desc0 + (uint64_t)(slot * (kStageBytes >> 4));
@@ -188,7 +189,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                         } else {
                             for (int k = 0; k < mma_per_stage; ++k) { umma_bf16<CTA>(d_tmem, a_desc + k * a_step, b_desc + k * b_step, idesc, accumulate | k); }
                         }
-                        umma_commit<CTA>(bar(B_EMPTY + slot));            // stage free once these MMAs have read it
+                        if (!(P.debug & 8)) umma_commit<CTA>(bar(B_EMPTY + slot));   // stage free once these MMAs have read it
                     }
                     __syncwarp();
                     a_desc += (uint64_t)(mma_per_stage * a_step);
@@ -206,9 +207,9 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         }
         if (P.recurrent_layer >= 0 && leader) bulk_wait_all();
     } else {
-        // ================= epilogue: 8 warps; warp w reads tensor-memory lanes 32*(w%4).., i.e. aircraft row
-        // 32*(w%4)+lane, and takes half (w/4) of every chunk's columns =================
-        const int half = warp >> 2;
+        // ================= epilogue: warp w reads tensor-memory lanes 32*(w%4).., i.e. aircraft row
+        // 32*(w%4)+lane, and takes part w/4 (of kParts) of every chunk's columns =================
+        const int part = warp >> 2;
         const int row = (warp & 3) * 32 + lane;
         const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
         uint32_t chunk_it = 0, tile_it = 0;
@@ -222,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
         const bool fresh = valid && ((P.episode_start != nullptr && P.episode_start[e] != 0) ||
                                      (P.episode_start_b != nullptr && P.episode_start_b[e] != 0));
 
-        if (half == 0) {
+        {
             // observation -> X as [hi | lo | hi | 0] bf16 columns (64 wide) against [W_hi | W_hi | W_lo | 0]:
             // x*W ~ (hi+lo)*W_hi + hi*W_lo keeps 16 mantissa bits of both (altitude ~100 m enters unnormalised)
             float o[ACB200_POLICY_OBS];
@@ -246,6 +247,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
             for (int q = 3 * ACB200_POLICY_OBS; q < 64; ++q) col[q] = 0.f;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
+                if (g % kParts != part) continue;          // the four 16-column groups are shared out over the row's warps
                 float t[16];
 #pragma unroll
                 for (int q = 0; q < 16; ++q) t[q] = col[16 * g + q];
@@ -272,7 +274,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     __syncwarp();
                     tc_fence_after();
                 } else if (L.epi == EPI_RELU) {
-                    const int w = L.N_c >> 1, j0 = half * w;
+                    const int w = L.N_c / kParts, j0 = part * w;      // w < 16 (the head's layer before it): part 0 takes all
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
                     tc_fence_after();
@@ -287,7 +289,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     }
                 } else if (L.epi == EPI_LSTM0) {
                     // h0 = c0 = 0 on every call (lstm_policy.py:86): c = sig(i) tanh(g), h = sig(o) tanh(c); f unused
-                    const int U = L.N_c / 3, w = U >> 1, j0 = half * w;
+                    const int U = L.N_c / 3, w = U / kParts, j0 = part * w;
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
                     tc_fence_after();
@@ -302,8 +304,8 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                         tmem_ld16_issue(t0 + j, vi);
                         tmem_ld16_issue(t0 + U + j, vg);
                         tmem_ld16_issue(t0 + 2 * U + j, vo);
-                        load_bias16(bias + j, bi); load_bias16(bias + U + j, bg); load_bias16(bias + 2 * U + j, bo);
                         tmem_ld_wait(vi); tmem_ld_wait(vg); tmem_ld_wait(vo);
+                        load_bias16(bias + j, bi); load_bias16(bias + U + j, bg); load_bias16(bias + 2 * U + j, bo);
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {
                             const float cc = sigmoid_half(__uint_as_float(vi[q]), bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]);
@@ -312,27 +314,27 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                         store_row16(act, L.out_off, c * U + j, row, h);
                     }
                 } else if (L.epi == EPI_LSTM) {
-                    const int U = L.N_c / 4, w = U >> 1, j0 = half * w;   // w == 32 here: two groups of 16 units
+                    constexpr int kW = 64 / kParts;                  // U == 64 (finish_policy checks): kW / 16 groups of 16 units
+                    const int U = L.N_c / 4, j0 = part * kW;
                     float* cst = P.c_state + (tile * kHidden + (int64_t)c * U + j0) * kTile + row;
-                    float cp[32];
+                    float cp[kW];
                     const bool carry = valid && !fresh;
 #pragma unroll
-                    for (int q = 0; q < 32; ++q) cp[q] = (carry && q < w) ? cst[(int64_t)q * kTile] : 0.f;   // before the wait
+                    for (int q = 0; q < kW; ++q) cp[q] = carry ? cst[(int64_t)q * kTile] : 0.f;   // before the wait
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
                     tc_fence_after();
 #pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        if (g * 16 >= w) break;
+                    for (int g = 0; g < kW / 16; ++g) {
                         const int j = j0 + g * 16;
                         uint32_t vi[16], vf[16], vg[16], vo[16]; float bi[16], bf[16], bg[16], bo[16], h[16];
                         tmem_ld16_issue(t0 + j, vi);
                         tmem_ld16_issue(t0 + U + j, vf);
                         tmem_ld16_issue(t0 + 2 * U + j, vg);
                         tmem_ld16_issue(t0 + 3 * U + j, vo);
+                        tmem_ld_wait(vi); tmem_ld_wait(vf); tmem_ld_wait(vg); tmem_ld_wait(vo);
                         load_bias16(bias + j, bi); load_bias16(bias + U + j, bf);
                         load_bias16(bias + 2 * U + j, bg); load_bias16(bias + 3 * U + j, bo);
-                        tmem_ld_wait(vi); tmem_ld_wait(vf); tmem_ld_wait(vg); tmem_ld_wait(vo);
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {
                             const float cn = fmaf(sigmoid_half(__uint_as_float(vf[q]), bf[q]), cp[g * 16 + q],
@@ -346,7 +348,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
                     tc_fence_after();
-                    if (half == 0) {
+                    if (part == 0) {
                         uint32_t v[16];
                         tmem_ld16_issue(t0, v);
                         tmem_ld_wait(v);
@@ -370,7 +372,7 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
                 mbar_wait(bar(B_HFULL), tile_it & 1, P.error_flag, 600);
                 if (fresh || !valid) {
                     const uint4 z = make_uint4(0, 0, 0, 0);
-                    for (int kc = half * (kHidden / 16); kc < (half + 1) * (kHidden / 16); ++kc)
+                    for (int kc = part * (kHidden / 8 / kParts); kc < (part + 1) * (kHidden / 8 / kParts); ++kc)
                         *reinterpret_cast<uint4*>(act + kHOff + (uint32_t)kc * kKChunkBytes + (uint32_t)row * 16) = z;
                 }
             }
@@ -558,8 +560,9 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         d.bias_off = (int)bias.size();
         bias.insert(bias.end(), h.b.begin(), h.b.end());
         if (d.epi == EPI_LSTM) p->params.recurrent_layer = (int)l;
-        if ((d.epi == EPI_LSTM && d.N_c != 256) || (d.epi == EPI_LSTM0 && d.N_c % 96) || (d.epi == EPI_RELU && d.N_c % 32))
-            return pfail(ctx, ACB200_EVALUE, "policy: chunk width does not split over the two epilogue halves");
+        if ((d.epi == EPI_LSTM && d.N_c != 256) || (d.epi == EPI_LSTM0 && d.N_c % (48 * kParts)) ||
+            (d.epi == EPI_RELU && d.N_c % (16 * kParts)))
+            return pfail(ctx, ACB200_EVALUE, "policy: chunk width does not split into 16-column groups over the epilogue warps");
         const int n_half = d.N_c / p->cta;      // a CTA pair splits every stage's columns in two halves, leader first
         for (int c = 0; c < d.n_chunks; ++c)
             for (int ks = 0; ks < d.K / d.K_s; ++ks)
@@ -718,7 +721,10 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
                 cudaGetLastError();
         }
     }
-    const unsigned n_blocks = (unsigned)(groups < p->resident ? groups : p->resident);
+    unsigned n_blocks = (unsigned)(groups < p->resident ? groups : p->resident);
+    static const int grid_cap = getenv("ACB200_POLICY_GRID") ? atoi(getenv("ACB200_POLICY_GRID")) : 0;   // development aid: fewer
+    if (grid_cap > 0 && (unsigned)grid_cap < n_blocks) n_blocks = (unsigned)grid_cap;                   // blocks, same per-tile time?
+
     if (p->cta == 2) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(2 * n_blocks);

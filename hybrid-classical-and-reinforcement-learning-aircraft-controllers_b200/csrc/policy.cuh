@@ -31,9 +31,14 @@ constexpr uint32_t kKChunkBytes = kTile * 16;   // one 8-wide K slab of an activ
 constexpr int kHidden = 256;
 constexpr uint32_t kHTileBytes = kHidden * kTile * 2;   // one tile of h, bf16, already in operand layout
 constexpr uint32_t kHOff = 16 * kKChunkBytes;           // h sits behind the 128 feature columns in X
-constexpr int kEpiWarps = 8;             // two warps per tensor-memory lane quarter: each takes half of a chunk's columns
+#ifndef ACB_EPI_WARPS
+#define ACB_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = ACB_EPI_WARPS;  // kParts warps per tensor-memory lane quarter: each takes 1/kParts of a chunk's columns
+constexpr int kParts = kEpiWarps / 4;
+static_assert(kEpiWarps == 8 || kEpiWarps == 16, "epilogue warps: 8 or 16");
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kThreads = kEpiThreads + 64;   // + warp 8: weight producer, warp 9: MMA issuer
+constexpr int kThreads = kEpiThreads + 64;   // + weight producer warp, MMA issuer warp
 constexpr uint32_t kTmemCols = 512;      // two accumulator buffers of 256 fp32 columns
 
 enum Epilogue : int { EPI_RELU = 0, EPI_LSTM0 = 1, EPI_LSTM = 2, EPI_HEAD = 3 };
@@ -66,7 +71,7 @@ struct PolicyParams {
     int64_t n;
     int* error_flag;
     long long* trace;         // debug & 4: clock64 stamps of block 0 ([0..1023] MMA thread, [1024..2047] epilogue thread 0)
-    int debug;                // timing experiments only (ACB200_POLICY_DEBUG): 1 = no weight traffic, 2 = no gate math
+    int debug;                // timing experiments only (ACB200_POLICY_DEBUG): 1 = no weight traffic, 2 = no gate math, 8 = no weight ring at all
 };
 
 // ---- shared-memory addresses, mbarriers -------------------------------------------------------------------------
@@ -235,6 +240,11 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 
 // 16 consecutive fp32 accumulator columns of this thread's lane (32x32b: lane = 32 * (warp % 4) + laneid)
 __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&v)[16]) {
+#ifdef ACB_DBG_NO_LDTM        // timing experiment only: no tensor-memory read, values the compiler cannot fold
+#pragma unroll
+    for (int q = 0; q < 16; ++q) asm volatile("mov.b32 %0, %1;" : "=r"(v[q]) : "r"(taddr + q));
+    return;
+#endif
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
@@ -253,9 +263,13 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
 
 // ---- gate arithmetic (fp32; one MUFU per transcendental) ---------------------------------------------------------------
 __device__ __forceinline__ float tanh_fast(float x) {
+#ifdef ACB_DBG_NO_MUFU        // timing experiment only: the transcendental replaced by one FMA
+    return fmaf(x, 0.25f, 0.125f);
+#else
     float y;
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+#endif
 }
 // tanh on [-1, 1] on the FMA pipe: x * P(x^2), P of degree 3, max abs error 3.3e-5 (tanh.approx itself: ~5e-4).  Used where
 // the argument is a product of a sigmoid and a tanh, so that one of the four transcendentals per stateless LSTM unit
