@@ -113,6 +113,7 @@ SYMBOLS = [
     "acb200_policy_create_lstm", "acb200_policy_create_mlp", "acb200_policy_destroy", "acb200_policy_state_bytes",
     "acb200_policy_forward", "acb200_policy_state_export", "acb200_policy_state_import", "acb200_policy_info",
     "acb200_gae",
+    "acb200_env_step_range",
     "acb200_default_sensor_config", "acb200_sensor_update", "acb200_sensor_reset",
 ]
 
@@ -148,6 +149,7 @@ def load() -> C.CDLL:
     L.acb200_step_waypoint.argtypes = [vp, P(FleetC), vp, P(MissionC), dbl, dbl, dbl, vp, vp]
     L.acb200_env_reset.argtypes = [vp, P(EnvC), P(EnvConfigC), vp]
     L.acb200_env_step.argtypes = [vp, P(EnvC), P(EnvConfigC), vp]
+    L.acb200_env_step_range.argtypes = [vp, P(EnvC), P(EnvConfigC), vp, i64, i64]
     L.acb200_env_step_host.argtypes = [vp, P(EnvC), P(EnvConfigC), vp, vp, vp, vp, vp, vp, vp]
     L.acb200_set_host_chunks.argtypes = [vp, i32]
     L.acb200_pid_compute_f32.argtypes = [P(PidConfigC), P(PidStateC), flt, flt, flt]; L.acb200_pid_compute_f32.restype = flt

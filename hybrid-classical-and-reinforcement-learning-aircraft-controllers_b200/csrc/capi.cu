@@ -328,6 +328,18 @@ int acb200_env_step(acb200_ctx* ctx, const acb200_env* env, const acb200_env_con
     return env_step_impl(ctx, env, cfg, action, nullptr);
 }
 
+// Aircraft [first, first + count) only, with the context's CURRENT parameters: the building block of per-group
+// parameter randomisation (set_aircraft_params, step_range, next group...).  Parameters stay in the constant bank, so a
+// group costs one launch and nothing per aircraft.
+int acb200_env_step_range(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action,
+                          int64_t first, int64_t count) {
+    if (!ctx || !env) return ACB200_ENULL;
+    if (first < 0 || count < 0 || first + count > env->fleet.n) return fail(ctx, ACB200_EVALUE, "env_step_range: range outside the fleet");
+    if (first % 128) return fail(ctx, ACB200_EVALUE, "env_step_range: first must be a multiple of 128 (whole blocks, aligned obs rows)");
+    if (count == 0) return ACB200_OK;
+    return env_step_impl(ctx, env, cfg, action, nullptr, first, count);
+}
+
 // Host-buffer step.  The fleet is cut into chunks and each chunk runs  H2D(action / attitude command) -> kernel ->
 // D2H(obs, reward, done flags)  on one of three worker streams, so that chunk c's D2H, chunk c+1's kernel and chunk
 // c+2's H2D overlap: the call is bound by the slower PCIe direction, not by the sum of the three phases.

@@ -21,6 +21,26 @@ STATS_NAMES = ("episodes", "return_sum", "return_sq_sum", "length_sum", "crashes
     "sum_" + c for c in COMPONENT_NAMES) + ("nonfinite_repairs", "aircraft_steps")
 
 
+RANDOMIZED_FIELDS = ("mass", "inertia_xx", "inertia_yy", "inertia_zz", "cl_alpha", "cd_0", "cl_elevator", "cm_elevator",
+                     "cn_rudder", "cl_aileron", "cm_alpha", "cn_beta", "cl_beta", "damping_roll", "damping_pitch", "damping_yaw",
+                     "max_thrust")
+
+
+def randomize_aircraft_params(base, n_groups: int, spread: float = 0.2, seed: int = 0, fields=RANDOMIZED_FIELDS):
+    """``n_groups`` copies of ``base`` with each listed field scaled by U(1 - spread, 1 + spread) (numpy PCG64, host side:
+    a few hundred numbers).  Group 0 is ``base`` itself."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    out = []
+    for g in range(n_groups):
+        p = _cabi.AircraftParamsC.from_buffer_copy(bytes(base))
+        if g:
+            for f in fields:
+                setattr(p, f, getattr(base, f) * float(rng.uniform(1.0 - spread, 1.0 + spread)))
+        out.append(p)
+    return out
+
+
 class BatchedRateControlEnv:
     """obs float32 [n,18]; action float32 [n,4] = aileron, elevator, rudder, throttle (rate_env.py:228-233)."""
 
@@ -86,11 +106,42 @@ class BatchedRateControlEnv:
         self.ctx.check(self.ctx.lib.acb200_env_reset(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(mask)))
         return self.obs
 
+    # -- domain randomisation: parameter GROUPS ----------------------------
+    def set_param_groups(self, groups, bounds=None):
+        """Give contiguous groups of aircraft their own ``AircraftParams`` (the reference has one per env instance,
+        simulation_backend.py:55-80).  ``groups``: list of ``_cabi.AircraftParamsC``; ``bounds``: len(groups)+1 offsets,
+        multiples of 128 except the last (default: an even split).  Each group is one launch with its parameters in the
+        constant bank; ``None`` / [] returns to one parameter set for the whole fleet."""
+        if not groups:
+            if getattr(self, "_groups", None):          # back to the default parameter set (simulation_backend.py:74-76)
+                base = _cabi.default_aircraft_params()
+                self.ctx.check(self.ctx.lib.acb200_set_aircraft_params(self.ctx.handle, C.byref(base)))
+            self._groups = None
+            return
+        g = len(groups)
+        if bounds is None:
+            per = ((self.n + g - 1) // g + 127) // 128 * 128
+            bounds = [min(k * per, self.n) for k in range(g)] + [self.n]
+        bounds = [int(b) for b in bounds]
+        if len(bounds) != g + 1 or bounds[0] != 0 or bounds[-1] != self.n or any(b % 128 for b in bounds[:-1]) or \
+                any(b1 < b0 for b0, b1 in zip(bounds, bounds[1:])):
+            raise ValueError("bounds must rise from 0 to n in multiples of 128")
+        for pr in groups:                      # validate now (ValueError like AircraftParams.__post_init__), restore after
+            self.ctx.check(self.ctx.lib.acb200_set_aircraft_params(self.ctx.handle, C.byref(pr)))
+        self._groups = (list(groups), bounds)
+
     def step(self, action: Optional[torch.Tensor] = None):
         """One control step for every aircraft; tensors returned are views of the env's own buffers."""
         self._bind_stream()
         if action is not None:
             assert action.dtype == torch.float32 and action.shape == (self.n, 4) and action.is_contiguous()
+        if getattr(self, "_groups", None):
+            groups, bounds = self._groups
+            lib, h = self.ctx.lib, self.ctx.handle
+            for pr, lo, hi in zip(groups, bounds, bounds[1:]):
+                self.ctx.check(lib.acb200_set_aircraft_params(h, C.byref(pr)))
+                self.ctx.check(lib.acb200_env_step_range(h, C.byref(self.c), C.byref(self.cfg), _ptr(action), lo, hi - lo))
+            return self.obs, self.reward, self.terminated, self.truncated
         self.ctx.check(self.ctx.lib.acb200_env_step(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action)))
         return self.obs, self.reward, self.terminated, self.truncated
 

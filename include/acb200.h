@@ -220,6 +220,12 @@ int acb200_step_waypoint(acb200_ctx* ctx, const acb200_fleet* f, float* pid_oute
 int acb200_env_reset(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const uint8_t* mask);
 /* action float[n][4] (aileron, elevator, rudder, throttle); may be NULL unless controller is EXTERNAL/RESIDUAL */
 int acb200_env_step(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const float* action);
+/* The same step for aircraft [first, first + count) only (first a multiple of 128), with the parameters the context holds
+ * NOW: per-group parameter randomisation is  for each group: acb200_set_aircraft_params(...); acb200_env_step_range(...).
+ * The reference has one global AircraftParams per env instance (simulation_backend.py:55-80); a group here is what N
+ * env instances constructed with the same params are there.  action indexes the whole fleet (float[n][4]). */
+int acb200_env_step_range(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const float* action,
+                          int64_t first, int64_t count);
 /* Same step with HOST buffers (pinned for speed), what SubprocVecEnv.step_wait hands to the trainer
  * (learned_controllers/utils/training_utils.py:60-69): copies action_host (float[n][4], nullable) and att_cmd_host
  * (real[4][n], nullable: the per-step attitude command of ACB200_CTRL_ATTITUDE_PID) in, obs / reward / terminated /
