@@ -113,7 +113,7 @@ SYMBOLS = [
     "acb200_policy_create_lstm", "acb200_policy_create_mlp", "acb200_policy_destroy", "acb200_policy_state_bytes",
     "acb200_policy_forward", "acb200_policy_state_export", "acb200_policy_state_import", "acb200_policy_info",
     "acb200_gae",
-    "acb200_env_step_range",
+    "acb200_env_step_range", "acb200_telemetry_record",
     "acb200_default_sensor_config", "acb200_sensor_update", "acb200_sensor_reset",
 ]
 
@@ -170,6 +170,7 @@ def load() -> C.CDLL:
     L.acb200_default_sensor_config.restype = None
     L.acb200_sensor_update.argtypes = [vp, P(FleetC), P(SensorConfigC), vp, C.c_uint32, vp, vp]
     L.acb200_sensor_reset.argtypes = [vp, i64, i32, vp, vp]
+    L.acb200_telemetry_record.argtypes = [vp, P(FleetC), vp, i64, vp]
     _lib = L
     return L
 

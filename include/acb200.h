@@ -269,6 +269,14 @@ int acb200_sensor_update(acb200_ctx* ctx, const acb200_fleet* f, const acb200_se
 /* sensor.reset(): zero the biases of aircraft with mask[i] != 0 (NULL = all)   sensor.py:245-251 */
 int acb200_sensor_reset(acb200_ctx* ctx, int64_t n, int32_t precision, void* bias, const uint8_t* mask);
 
+/* ---- telemetry sampling ----------------------------------------------------------------------
+ * What TelemetryLogger.log_state / log_surfaces keep per logged aircraft (visualization/logger.py:72-120), for k sampled
+ * aircraft at once: out real[21][k] = state rows 0..12 | derived rows 0..3 | held controls rows 0..3 of aircraft
+ * ids[j] (device int64[k]; an id outside [0, n) logs NaN).  The caller advances `out` through its own device ring and
+ * writes the file (host mirror: telemetry.TelemetryRecorderB200, the reference's JSON / HDF5 layouts). */
+#define ACB200_TELEMETRY_FIELDS 21
+int acb200_telemetry_record(acb200_ctx* ctx, const acb200_fleet* f, const int64_t* ids, int64_t k, void* out);
+
 /* ---- learned rate policy, actor forward (row a20) -------------------------------------------------------------
  * Replaces: model.predict(obs, state=lstm_state, deterministic=True) at controllers/learned_rate_agent.py:220-227
  * with the network of learned_controllers/networks/lstm_policy.py:13-164 (LSTMFeaturesExtractor + sb3-contrib's

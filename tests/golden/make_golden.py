@@ -440,8 +440,48 @@ def gen_sensor():
     print("sensor.npz", {k: v.shape for k, v in out.items() if k.startswith("default")}, out["stats/noise_std"], out["stats/walk_std"])
 
 
+# ------------------------------------------------------------------------------------------------
+def gen_telemetry():
+    """TelemetryLogger's JSON layout (visualization/logger.py:72-147) for 3 aircraft x 6 steps: the fixture keeps the
+    records the states were built from ([T][21][k]: state 13 | derived 4 | controls 4 in ControlSurfaces.to_array order)
+    and the file the unmodified logger wrote, byte for byte."""
+    import tempfile
+    import importlib.util          # visualization/__init__.py pulls in matplotlib (absent here): load logger.py by path
+    ref = os.environ.get("REFERENCE", "/root/reference")
+    spec = importlib.util.spec_from_file_location("ref_telemetry_logger", os.path.join(ref, "visualization", "logger.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    TelemetryLogger = mod.TelemetryLogger
+    rng = np.random.default_rng(77)
+    T, k = 6, 3
+    rec = rng.normal(size=(T, 21, k))
+    rec[:, 12, :] = (0.01 * np.arange(1, T + 1))[:, None]
+    ids = ["lead", "wing_left", "wing_right"]
+    meta = {"lead": {"type": "rc_plane", "formation_index": 0}, "wing_left": {"type": "rc_plane", "formation_index": 1},
+            "wing_right": {}}
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "log.json")
+        lg = TelemetryLogger(path)
+        for a in ids:
+            lg.register_aircraft(a, metadata=meta[a] or None)
+        for t in range(T):
+            for j, a in enumerate(ids):
+                r = rec[t, :, j]
+                st = AircraftState(time=float(r[12]), position=r[0:3].copy(), velocity=r[3:6].copy(), attitude=r[6:9].copy(),
+                                   angular_rate=r[9:12].copy(), airspeed=float(r[13]), altitude=float(r[14]),
+                                   ground_speed=float(r[15]), heading=float(r[16]))
+                lg.log_state(a, st)
+                lg.log_command(a, ControlCommand(mode=ControlMode.WAYPOINT), float(r[12]))
+                lg.log_surfaces(a, ControlSurfaces(elevator=float(r[17]), aileron=float(r[18]), rudder=float(r[19]),
+                                                   throttle=float(r[20])), float(r[12]))
+        lg.close()
+        text = open(path).read()
+    open(os.path.join(HERE, "telemetry.json"), "w").write(text)
+    np.save(os.path.join(HERE, "telemetry_records.npy"), rec)
+    print("telemetry.json", len(text), "bytes")
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "guidance", "sensor"]
+    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "guidance", "sensor", "telemetry"]
     with mp.Pool(8) as pool:
         if "pid" in which: gen_pid_kat()
         if "dyn" in which: gen_dynamics_kat()
@@ -450,3 +490,4 @@ if __name__ == "__main__":
         if "env" in which: gen_env(pool)
         if "guidance" in which: gen_guidance(pool)
         if "sensor" in which: gen_sensor()
+        if "telemetry" in which: gen_telemetry()
