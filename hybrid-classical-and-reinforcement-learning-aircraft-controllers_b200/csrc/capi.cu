@@ -365,8 +365,8 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming);
         if (e != cudaSuccess) return cuda_fail(ctx, e, "env_step_host: stream setup");
     }
-    // chunks of a multiple of 128 aircraft (whole blocks, 16-byte aligned obs rows), about 64k aircraft each
-    int chunks = ctx->host_chunks > 0 ? ctx->host_chunks : (int)((n + 65535) / 65536);
+    // chunks of a multiple of 128 aircraft (whole blocks, 16-byte aligned obs rows), about 128k aircraft each
+    int chunks = ctx->host_chunks > 0 ? ctx->host_chunks : (int)((n + 131071) / 131072);
     if (chunks > 64) chunks = 64;
     if (chunks < 1) chunks = 1;
     int64_t per = ((n + chunks - 1) / chunks + 127) / 128 * 128;
@@ -377,8 +377,13 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
     for (int s = 0; s < acb200_ctx::kPipe && e == cudaSuccess; ++s) e = cudaStreamWaitEvent(ctx->pipe[s], ctx->fork, 0);
     if (e != cudaSuccess) return cuda_fail(ctx, e, "env_step_host: fork");
     int used = 0;
-    for (int64_t first = 0, c = 0; first < n; first += per, ++c) {
-        const int64_t count = (n - first < per) ? (n - first) : per;
+    // the first chunks are short (per/8, per/4, per/2): the D2H engine, which bounds the call, starts after one small H2D and
+    // one small kernel instead of a full-sized pair
+    int64_t count = 0;
+    for (int64_t first = 0, c = 0; first < n; first += count, ++c) {
+        int64_t want = per;
+        if (ctx->host_chunks == 0 && chunks >= 4 && c < 3) want = ((per >> (3 - c)) + 127) / 128 * 128;
+        count = (n - first < want) ? (n - first) : want;
         const cudaStream_t st = ctx->pipe[c % acb200_ctx::kPipe];
         used = (int)((c + 1 < acb200_ctx::kPipe) ? c + 1 : acb200_ctx::kPipe);
         if (action_host) {
@@ -395,16 +400,18 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
         if (rc) return rc;
         e = cudaMemcpyAsync(obs_host + first * ACB200_OBS_DIM, env->obs + first * ACB200_OBS_DIM,
                             (size_t)count * ACB200_OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host + first, reward_dev + first, (size_t)count * sizeof(float), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(terminated_host + first, env->terminated + first, (size_t)count, cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(truncated_host + first, env->truncated + first, (size_t)count, cudaMemcpyDeviceToHost, st);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "D2H results");
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "D2H obs");
     }
-    // join: the context's stream continues after every worker, then the host waits for it
+    // join: the context's stream continues after every worker.  Reward and the two flag arrays (6 of the 78 bytes per
+    // aircraft) leave in three whole-fleet copies behind the last chunk instead of three small ones per chunk: a copy
+    // costs ~4 us of PCIe time whatever its size (tools/pcie_probe.py: 48.7 GB/s in per-chunk pieces, 54.6 GB/s for obs alone)
     for (int s = 0; s < used && e == cudaSuccess; ++s) {
         e = cudaEventRecord(ctx->pipe_done[s], ctx->pipe[s]);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->pipe_done[s], 0);
     }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, reward_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(terminated_host, env->terminated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(truncated_host, env->truncated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step_host");
 }

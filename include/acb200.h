@@ -235,7 +235,7 @@ int acb200_env_step_range(acb200_ctx* ctx, const acb200_env* e, const acb200_env
 int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg,
                          const float* action_host, const void* att_cmd_host, float* action_dev, float* obs_host,
                          float* reward_host, uint8_t* terminated_host, uint8_t* truncated_host);
-/* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 64k aircraft per chunk) */
+/* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 128k aircraft per chunk) */
 int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 
 /* ---- sensor model ------------------------------------------------------------------------

@@ -9,7 +9,7 @@ pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
 att_host = pin((4, n), torch.float32); att_host.copy_(torch.as_tensor(att).float())
 obs_h, rew_h = pin((n, 18), torch.float32), pin((n,), torch.float32)
 term_h, trunc_h = pin((n,), torch.uint8), pin((n,), torch.uint8)
-for chunks in (0, 2, 4, 6, 8, 12, 16, 32):
+for chunks in (0, 8, 0, 8, 0, 8):
     env.ctx.check(env.ctx.lib.acb200_set_host_chunks(env.ctx.handle, chunks))
     for _ in range(3):
         env.step_host(None, obs_h, rew_h, term_h, trunc_h, att_cmd_host=att_host)
