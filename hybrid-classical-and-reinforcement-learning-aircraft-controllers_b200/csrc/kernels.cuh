@@ -2,6 +2,7 @@
 // control-step boundary through coalesced structure-of-arrays loads and stores; everything between
 // (K RK4 substeps x 4 derivative evaluations, PID, reward, termination, reset) runs out of registers.
 #pragma once
+#include <stdlib.h>
 #include <string.h>
 
 #include "env.cuh"
@@ -484,6 +485,12 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::env) env_step_kernel(con
     }
 }
 
+}  // namespace acb
+#ifdef ACB_PAIR_KERNEL
+#include "kernels_pair_f32.cuh"   // throughput build: two aircraft per thread on packed FP32 instructions
+#endif
+namespace acb {
+
 // ---- launchers -------------------------------------------------------------------------------------
 static inline unsigned grid_for(int64_t n) { return (unsigned)((n + kBlock - 1) / kBlock); }
 
@@ -567,6 +574,23 @@ cudaError_t Launch<T>::env_step(const acb200_aircraft_params& ap, const acb200_c
                                 const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
                                 cudaStream_t st) {
     if (count <= 0) return cudaSuccess;
+#ifdef ACB_PAIR_KERNEL
+    if constexpr (sizeof(T) == 4) {
+        // Default path of the throughput build: aircraft pairs on packed FP32 instructions; a last odd aircraft (and any
+        // layout without 8-byte field alignment) goes through the one-aircraft-per-thread kernel, which computes the
+        // same bits.  ACB200_ENV_PAIR=0 forces the scalar kernel (A/B measurements, the bit-identity test).
+        const char* pair_env = getenv("ACB200_ENV_PAIR");      // read per launch: the bit-identity test flips it in-process
+        const bool pair_enabled = !(pair_env && pair_env[0] == '0');
+        if (pair_enabled && count >= 2 && pair_layout_ok(e, first)) {
+            const int64_t pairs = count / 2;
+            cudaError_t err = launch_env_step_pair(make_dyn_params<float>(ap), make_ctrl_params<float>(cp),
+                                                   make_env_const<float>(cfg, K, h), e, action, first, pairs, st);
+            if (err != cudaSuccess || !(count & 1)) return err;
+            first += 2 * pairs;
+            count = 1;
+        }
+    }
+#endif
     env_step_kernel<T><<<grid_for(count), kBlock, 0, st>>>(make_dyn_params<T>(ap), make_ctrl_params<T>(cp),
                                                            make_env_const<T>(cfg, K, h), e, action, first, count);
     return cudaGetLastError();
@@ -578,6 +602,9 @@ template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, Kerne
     else if (!strcmp(name, "step_cascade_rate")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_RATE>;
     else if (!strcmp(name, "step_cascade_attitude")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE>;
     else if (!strcmp(name, "env_step")) fn = (const void*)env_step_kernel<T>;
+#ifdef ACB_PAIR_KERNEL
+    else if (!strcmp(name, "env_step_pair") && sizeof(T) == 4) fn = env_step_pair_entry();
+#endif
     else if (!strcmp(name, "step_hsa")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_HSA>;
     else if (!strcmp(name, "step_waypoint")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_WAYPOINT>;
     else if (!strcmp(name, "env_reset")) fn = (const void*)env_reset_kernel<T>;

@@ -32,6 +32,7 @@ template <typename T> struct DynParams {
     T damp_p, damp_q, damp_r;                    // damping * (b or c) / 2
     T inv_vt0, inv_min_airspeed;
     T tan_max_alpha, sin_max_pitch, cos_max_pitch;
+    T euler_rate_gain;                           // bound of |d(Euler angle)/dt| / max|body rate|: 1 + 2 / cos(max_pitch), +1 %
     T inv_ixx, inv_iyy, inv_izz;
     T b_ixx, c_iyy, b_izz;                       // span / Ixx, chord / Iyy, span / Izz
     T gyro_x, gyro_y, gyro_z;                    // (Izz-Iyy)/Ixx, (Ixx-Izz)/Iyy, (Iyy-Ixx)/Izz
@@ -89,6 +90,7 @@ template <typename T> static inline DynParams<T> make_dyn_params(const acb200_ai
     d.tan_max_alpha = (T)tan(host_radians(a.max_alpha));
     d.sin_max_pitch = (T)sin(host_radians(a.max_pitch_angle));
     d.cos_max_pitch = (T)cos(host_radians(a.max_pitch_angle));
+    d.euler_rate_gain = (T)(1.01 * (1.0 + 2.0 / fabs(cos(host_radians(a.max_pitch_angle)))));
     d.inv_ixx = (T)(1.0 / a.inertia_xx); d.inv_iyy = (T)(1.0 / a.inertia_yy); d.inv_izz = (T)(1.0 / a.inertia_zz);
     d.b_ixx = (T)(a.wing_span / a.inertia_xx); d.c_iyy = (T)(a.chord / a.inertia_yy); d.b_izz = (T)(a.wing_span / a.inertia_zz);
     d.gyro_x = (T)((a.inertia_zz - a.inertia_yy) / a.inertia_xx);

@@ -1,0 +1,125 @@
+"""The throughput build's default env step owns TWO aircraft per thread and runs the substeps on Blackwell's packed FP32
+instructions (csrc/kernels_pair_f32.cuh, physics_f32x2.cuh).  Every lane operation is the IEEE operation of the
+one-aircraft-per-thread kernel in the same order, so the two kernels must agree BIT FOR BIT on every buffer -- which also
+puts the pair kernel under every fp32 tolerance the scalar kernel is tested against (tests/test_gpu_parity_f32.py)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+BUFFERS = ("state", "controls", "derived", "pid", "rate_cmd", "prev_action", "rew_mem", "sched", "env_time", "step_count",
+           "is_settled", "episode_idx", "ep_return", "obs", "reward", "terminated", "truncated", "terminal_obs", "components")
+
+
+def _make(acb200, n, controller, seed, command_mix):
+    env = acb200.BatchedRateControlEnv(n, controller=controller, precision=32, seed=seed, episode_length=1.0,
+                                       track_components=True)
+    g = torch.Generator().manual_seed(seed)
+    if command_mix:
+        env.set_curriculum(torch.tensor([0.3, 0.5, 0.7])[torch.randint(0, 3, (n,), generator=g)],
+                           torch.randint(0, 4, (n,), generator=g).to(torch.uint8))
+    att = torch.zeros(4, n)
+    att[0].uniform_(-0.5, 0.5, generator=g); att[1].uniform_(-0.1, 0.15, generator=g)
+    att[2] = float("inf"); att[3].uniform_(0.3, 0.9, generator=g)
+    env.att_cmd.copy_(att)
+    return env
+
+
+def _run(acb200, pair, n, controller, steps, seed, command_mix, ranges=None):
+    os.environ["ACB200_ENV_PAIR"] = "1" if pair else "0"
+    try:
+        env = _make(acb200, n, controller, seed, command_mix)
+        env.reset()
+        g = torch.Generator().manual_seed(seed + 1)
+        rewards = []
+        for t in range(steps):
+            action = None
+            if controller in ("external", "residual"):
+                action = (torch.rand(n, 4, generator=g) * 2 - 1).mul_(0.6 if controller == "external" else 1.0).cuda()
+                if controller == "external":
+                    action[:, 3] = action[:, 3].abs()
+            if ranges is None:
+                env.step(action)
+            else:
+                env._bind_stream()
+                for lo, cnt in ranges:
+                    env.ctx.check(env.ctx.lib.acb200_env_step_range(env.ctx.handle, C.byref(env.c), C.byref(env.cfg),
+                                                                    None if action is None else C.c_void_p(action.data_ptr()),
+                                                                    lo, cnt))
+            rewards.append(env.reward.clone())
+        torch.cuda.synchronize()
+        out = {k: getattr(env, k).cpu().numpy().copy() for k in BUFFERS}
+        out["rewards"] = torch.stack(rewards).cpu().numpy()
+        out["stats"] = env.stats.cpu().numpy().copy()
+        return out
+    finally:
+        os.environ.pop("ACB200_ENV_PAIR", None)
+
+
+def _same_bits(a, b, what):
+    for k in a:
+        if k == "stats":
+            continue
+        x, y = np.ascontiguousarray(a[k]), np.ascontiguousarray(b[k])
+        assert x.shape == y.shape and x.dtype == y.dtype
+        assert np.array_equal(x.view(np.uint8), y.view(np.uint8)), f"{what}: {k} differs in {(x != y).sum()} places"
+    # episode statistics are float partial sums in a different association; the counters are exact
+    sa, sb = a["stats"], b["stats"]
+    assert np.array_equal(sa[[0, 3, 4, 5, 14, 15]], sb[[0, 3, 4, 5, 14, 15]])
+    assert np.allclose(sa, sb, rtol=2e-5, atol=1e-3)
+
+
+@pytest.mark.parametrize("controller", ["attitude_pid", "rate_pid", "external", "residual"])
+def test_pair_kernel_is_bit_identical_to_the_one_aircraft_kernel(controller):
+    import acb200
+    n, steps = 2048 + 2 * 37, 130          # a ragged last block; 130 steps of a 50-step episode: every aircraft resets twice
+    a = _run(acb200, False, n, controller, steps, seed=5, command_mix=True)
+    b = _run(acb200, True, n, controller, steps, seed=5, command_mix=True)
+    assert a["stats"][0] >= 2 * n                                  # the in-kernel auto-reset ran on both sides
+    _same_bits(a, b, controller)
+
+
+def test_pair_kernel_ranges_odd_counts():
+    """env_step_range (first a multiple of 128) with odd counts (the pair kernel plus one scalar aircraft), a one- and a
+    two-aircraft range, against the scalar kernel on the same ranges; whole-block ranges against one whole-fleet launch."""
+    import acb200
+    n = 1024
+    ranges = [(0, 127), (128, 1), (256, 2), (384, 255), (640, 383)]
+    a = _run(acb200, False, n, "attitude_pid", 60, seed=9, command_mix=False, ranges=ranges)
+    b = _run(acb200, True, n, "attitude_pid", 60, seed=9, command_mix=False, ranges=ranges)
+    _same_bits(a, b, "ranges")
+    ranges = [(0, 128), (128, 384), (512, 512)]
+    b = _run(acb200, True, n, "attitude_pid", 60, seed=9, command_mix=False, ranges=ranges)
+    c = _run(acb200, True, n, "attitude_pid", 60, seed=9, command_mix=False)
+    _same_bits(b, c, "ranges vs whole fleet")
+
+
+def test_odd_fleet_size_falls_back_to_the_one_aircraft_kernel():
+    import acb200
+    a = _run(acb200, False, 777, "rate_pid", 40, seed=2, command_mix=True)
+    b = _run(acb200, True, 777, "rate_pid", 40, seed=2, command_mix=True)
+    _same_bits(a, b, "odd n")
+
+
+def test_pair_kernel_repairs_nonfinite_state_like_the_one_aircraft_kernel():
+    import acb200
+    outs = []
+    for pair in (False, True):
+        os.environ["ACB200_ENV_PAIR"] = "1" if pair else "0"
+        try:
+            env = acb200.BatchedRateControlEnv(512, controller="rate_pid", precision=32, seed=1, auto_reset=False)
+            env.reset()
+            env.state[0, 3] = float("nan"); env.state[4, 10] = float("inf"); env.state[7, 11] = float("-inf")
+            env.state[2, 200] = float("inf"); env.state[9, 201] = float("nan")
+            for _ in range(3):
+                env.step()
+            torch.cuda.synchronize()
+            outs.append((env.state.cpu().numpy().copy(), env.stats.cpu().numpy().copy()))
+        finally:
+            os.environ.pop("ACB200_ENV_PAIR", None)
+    assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
+    assert np.isfinite(outs[1][0]).all() and outs[0][1][14] == outs[1][1][14] > 0

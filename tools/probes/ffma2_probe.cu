@@ -1,0 +1,82 @@
+// ffma2_probe.cu -- issue/pipe throughput of Blackwell's packed FP32 instructions (FFMA2) against scalar FFMA, and
+// of the mixes the fused substep is made of (FMA-pipe + ALU-pipe FMNMX + MUFU).  Build:
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/probes/ffma2_probe tools/probes/ffma2_probe.cu
+// Prints one JSON object.  Measurement tool only (not on the product path).
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+
+#define ITERS 4096
+template <int MODE> __global__ void __launch_bounds__(256) probe(float* out, float a, float b) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    float2 x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = make_float2(tid * 1e-9f + i, tid * 2e-9f - i);
+    const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (MODE == 0) {          // 16 scalar FFMA
+                x[i].x = fmaf(x[i].x, a, b);
+                x[i].y = fmaf(x[i].y, a, b);
+            } else if (MODE == 1) {   // 8 FFMA2 (same flops)
+                x[i] = __ffma2_rn(x[i], a2, b2);
+            } else if (MODE == 2) {   // 8 FFMA2 + 16 FMNMX
+                x[i] = __ffma2_rn(x[i], a2, b2);
+                x[i].x = fminf(x[i].x, 3.0e38f);
+                x[i].y = fminf(x[i].y, 3.0e38f);
+            } else if (MODE == 3) {   // 16 FFMA + 16 FMNMX
+                x[i].x = fminf(fmaf(x[i].x, a, b), 3.0e38f);
+                x[i].y = fminf(fmaf(x[i].y, a, b), 3.0e38f);
+            } else if (MODE == 4) {   // 8 FFMA2 + 4 MUFU
+                x[i] = __ffma2_rn(x[i], a2, b2);
+                if (i % 2 == 0) asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(x[i].x));
+            } else if (MODE == 5) {   // 16 FFMA + 4 MUFU
+                x[i].x = fmaf(x[i].x, a, b);
+                x[i].y = fmaf(x[i].y, a, b);
+                if (i % 2 == 0) asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(x[i].x));
+            } else if (MODE == 6) {   // 8 FFMA2 + 8 FMNMX + 2 MUFU  (close to the substep's mix per 16 flop-pairs)
+                x[i] = __ffma2_rn(x[i], a2, b2);
+                x[i].x = fminf(x[i].x, 3.0e38f);
+                if (i % 4 == 0) asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(x[i].y));
+            } else if (MODE == 7) {   // the same mix, scalar
+                x[i].x = fminf(fmaf(x[i].x, a, b), 3.0e38f);
+                x[i].y = fmaf(x[i].y, a, b);
+                if (i % 4 == 0) asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(x[i].y));
+            }
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += x[i].x + x[i].y;
+    if (s == 12345.678f) out[tid] = s;
+}
+
+template <int MODE> static double run(int sms, float* d) {
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int blocks = sms * 8;
+    probe<MODE><<<blocks, 256>>>(d, 0.999f, 1e-3f);
+    cudaDeviceSynchronize();
+    cudaEventRecord(e0);
+    for (int r = 0; r < 5; ++r) probe<MODE><<<blocks, 256>>>(d, 0.999f, 1e-3f);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    // fma lanes-ops per second (one FFMA lane-op = 2 flop)
+    return 5.0 * blocks * 256.0 * ITERS * 16.0 / (ms * 1e-3);
+}
+
+int main() {
+    cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
+    float* d; cudaMalloc(&d, 1 << 26);
+    const int sms = p.multiProcessorCount;
+    double r[8];
+    r[0] = run<0>(sms, d); r[1] = run<1>(sms, d); r[2] = run<2>(sms, d); r[3] = run<3>(sms, d);
+    r[4] = run<4>(sms, d); r[5] = run<5>(sms, d); r[6] = run<6>(sms, d); r[7] = run<7>(sms, d);
+    printf("{\"sms\": %d, \"fma_lane_ops_per_s\": {\"ffma\": %.4g, \"ffma2\": %.4g, \"ffma2+fmnmx\": %.4g, \"ffma+fmnmx\": %.4g, "
+           "\"ffma2+mufu\": %.4g, \"ffma+mufu\": %.4g, \"mix_ffma2\": %.4g, \"mix_ffma\": %.4g}, "
+           "\"tflops_ffma\": %.2f, \"tflops_ffma2\": %.2f}\n",
+           sms, r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], 2 * r[0] / 1e12, 2 * r[1] / 1e12);
+    return 0;
+}
