@@ -4,7 +4,8 @@
 Workload (BASELINE.json configs[2], "C3"): 2^20 aircraft per GPU, each a RateControlEnv (dt 0.02 =
 20 RK4 substeps of 1 ms) flown by the full cascaded attitude -> rate -> surface PID, "step" rate
 commands, per-aircraft difficulty drawn from {easy, medium, hard}, in-kernel Philox curriculum
-resets.  One "step" = one control step of every aircraft = ONE launch of env_step_kernel<float>.
+resets.  One "step" = one control step of every aircraft = ONE launch of env_step_pair_kernel (fp32: two aircraft per thread on packed FP32
+instructions; env_step_kernel<T>, one aircraft per thread, for the fp64 parity build and ACB200_ENV_PAIR=0).
 
     python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
     python bench.py --impl reference [...]                          # the CPU arm (oracle port, all cores)
@@ -270,9 +271,13 @@ def run_gpu(args):
     fp32_measured = env.ctx.measure_fp32_peak()
     fp_peak = fp32_measured if precision == 32 else fp32_measured / 2
     traffic = None
+    # fp32 fleets of even size run the two-aircraft-per-thread kernel on packed FP32 (csrc/kernels_pair_f32.cuh)
+    pair = (precision == 32 and n % 2 == 0 and os.environ.get("ACB200_ENV_PAIR", "1")[:1] != "0"
+            and (k_sub >= 4 or "ACB200_PAIR_VARIANT" in os.environ))
+    kernel_name = "env_step_pair_kernel" if pair else "env_step_kernel"
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get(f"env_step{'_k1' if k_sub == 1 else ''}_f{precision}_{n}")
+            traffic = json.load(f).get(f"env_step{'_pair' if pair else ''}{'_k1' if k_sub == 1 else ''}_f{precision}_{n}")
     except Exception:
         pass
     achieved_tflops = per_gpu * flop_per_env_step / 1e12
@@ -280,11 +285,11 @@ def run_gpu(args):
     roof_fp = {"bound": "fp32", "note": "non-tensor FP32 issue-bound; the path is neither HBM- nor tensor-bound (DESIGN.md 4); HBM view in roofline_hbm",
                "achieved": achieved_tflops, "peak": fp_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fp_peak,
                "peak_source": "measured here: FMA-chain kernel, all SMs (derived nominal: %.1f)" % FP32_PEAK_DERIVED_TFLOPS,
-               "flop_per_env_step": flop_per_env_step, "kernel": "env_step_kernel", "kernel_ms": ms / args.steps,
+               "flop_per_env_step": flop_per_env_step, "kernel": kernel_name, "kernel_ms": ms / args.steps,
                "traffic": traffic}
     roof_hbm = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
                 "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
-                "bytes_per_env_step": bytes_step, "algorithmic_bytes_per_launch": bytes_step * n, "kernel": "env_step_kernel",
+                "bytes_per_env_step": bytes_step, "algorithmic_bytes_per_launch": bytes_step * n, "kernel": kernel_name,
                 "kernel_ms": ms / args.steps, "traffic": traffic}
     k1 = args.workload == "k1"
     out = {

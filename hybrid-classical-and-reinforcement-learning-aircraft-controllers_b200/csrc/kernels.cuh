@@ -581,7 +581,7 @@ cudaError_t Launch<T>::env_step(const acb200_aircraft_params& ap, const acb200_c
         // same bits.  ACB200_ENV_PAIR=0 forces the scalar kernel (A/B measurements, the bit-identity test).
         const char* pair_env = getenv("ACB200_ENV_PAIR");      // read per launch: the bit-identity test flips it in-process
         const bool pair_enabled = !(pair_env && pair_env[0] == '0');
-        if (pair_enabled && count >= 2 && pair_layout_ok(e, first)) {
+        if (pair_enabled && count >= 2 && pair_variant(K) >= 0 && pair_layout_ok(e, first)) {
             const int64_t pairs = count / 2;
             cudaError_t err = launch_env_step_pair(make_dyn_params<float>(ap), make_ctrl_params<float>(cp),
                                                    make_env_const<float>(cfg, K, h), e, action, first, pairs, st);

@@ -250,18 +250,19 @@ env_step_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_co
 
 // Block shape of the pair kernel: threads per block x resident blocks per SM the register allocation aims at.
 // ACB200_PAIR_VARIANT picks one of the compiled shapes (measurements); the default is the fastest measured on B200.
+// Measured on B200 (2^20 aircraft, profiles/r01g_pair_variants.md): at K = 20 substeps the 168-register shape without
+// spills (12 warps per SM) is fastest; the 128-register shapes spill ~250 bytes and lose what the extra warps gain.  Below
+// K = 4 the step is a memory-bound gather / scatter where the one-aircraft kernel (24 warps per SM) is as fast or
+// faster, so the launcher keeps it there (pair_variant() < 0) unless ACB200_PAIR_VARIANT names a shape.
 #define ACB_PAIR_VARIANTS(X) X(0, 128, 3) X(1, 128, 4) X(2, 64, 7) X(3, 64, 8) X(4, 64, 6)
-#ifndef ACB_PAIR_DEFAULT_VARIANT
-#define ACB_PAIR_DEFAULT_VARIANT 0
-#endif
-static inline int pair_variant() {
+static inline int pair_variant(int K) {
     const char* v = getenv("ACB200_PAIR_VARIANT");
-    return (v && v[0] >= '0' && v[0] <= '4') ? v[0] - '0' : ACB_PAIR_DEFAULT_VARIANT;
+    return (v && v[0] >= '0' && v[0] <= '4') ? v[0] - '0' : (K < 4 ? -1 : 0);
 }
 static inline cudaError_t launch_env_step_pair(const DynParams<float>& P, const CtrlParams<float>& C, const EnvConst<float>& E,
                                                const EnvPtrs<float>& e, const float* action, int64_t first, int64_t pairs,
                                                cudaStream_t st) {
-    switch (pair_variant()) {
+    switch (pair_variant(E.K)) {
 #define ACB_PAIR_CASE(id, block, minb)                                                                                        \
     case id:                                                                                                                  \
         env_step_pair_kernel<block, minb><<<(unsigned)((pairs + block - 1) / block), block, 0, st>>>(P, C, E, e, action, first, \
@@ -273,7 +274,7 @@ static inline cudaError_t launch_env_step_pair(const DynParams<float>& P, const 
     return cudaGetLastError();
 }
 static inline const void* env_step_pair_entry() {
-    switch (pair_variant()) {
+    switch (pair_variant(20)) {
 #define ACB_PAIR_CASE(id, block, minb) case id: return (const void*)env_step_pair_kernel<block, minb>;
         ACB_PAIR_VARIANTS(ACB_PAIR_CASE)
 #undef ACB_PAIR_CASE

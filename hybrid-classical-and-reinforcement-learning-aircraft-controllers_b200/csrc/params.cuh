@@ -32,6 +32,7 @@ template <typename T> struct DynParams {
     T damp_p, damp_q, damp_r;                    // damping * (b or c) / 2
     T inv_vt0, inv_min_airspeed;
     T tan_max_alpha, sin_max_pitch, cos_max_pitch;
+    T rk_two, rk_one;                            // RK4 weights 2 and 1 as run-time values (physics_f32x2.cuh)
     T euler_rate_gain;                           // bound of |d(Euler angle)/dt| / max|body rate|: 1 + 2 / cos(max_pitch), +1 %
     T inv_ixx, inv_iyy, inv_izz;
     T b_ixx, c_iyy, b_izz;                       // span / Ixx, chord / Iyy, span / Izz
@@ -90,6 +91,7 @@ template <typename T> static inline DynParams<T> make_dyn_params(const acb200_ai
     d.tan_max_alpha = (T)tan(host_radians(a.max_alpha));
     d.sin_max_pitch = (T)sin(host_radians(a.max_pitch_angle));
     d.cos_max_pitch = (T)cos(host_radians(a.max_pitch_angle));
+    d.rk_two = T(2); d.rk_one = T(1);
     d.euler_rate_gain = (T)(1.01 * (1.0 + 2.0 / fabs(cos(host_radians(a.max_pitch_angle)))));
     d.inv_ixx = (T)(1.0 / a.inertia_xx); d.inv_iyy = (T)(1.0 / a.inertia_yy); d.inv_izz = (T)(1.0 / a.inertia_zz);
     d.b_ixx = (T)(a.wing_span / a.inertia_xx); d.c_iyy = (T)(a.chord / a.inertia_yy); d.b_izz = (T)(a.wing_span / a.inertia_zz);

@@ -18,7 +18,7 @@
 #error "physics_f32x2.cuh implements the SFU trigonometry variant only"
 #endif
 #ifndef ACB_F32X2_UNROLL_STAGES
-#define ACB_F32X2_UNROLL_STAGES 0
+#define ACB_F32X2_UNROLL_STAGES 1
 #endif
 
 namespace acb {
@@ -222,7 +222,11 @@ __device__ __forceinline__ int rk4_step_f32x2(const DynParams<float>& P, const H
 #endif
     for (int stage = 1; stage < 4; ++stage) {
         const float a = (stage == 3) ? dt : half_dt;
-        const float wgt = (stage == 3) ? 1.0f : 2.0f;
+        // With the stages unrolled the compiler would know the weight, turn fma(1, k, acc) into k + acc and contract that
+        // add with the multiply that produced k[8] (= yaw_num * rc) -- one rounding less than the one-aircraft kernel's
+        // fma(wgt, k, acc) with its run-time wgt.  The weights come from the parameter block (constant bank), which
+        // neither nvvm nor ptxas can fold, so the accumulation stays an FMA.
+        const float wgt = (stage == 3) ? P.rk_one : P.rk_two;
 #pragma unroll
         for (int i = 0; i < 12; ++i) t[i] = X::fma(X::bc(a), k[i], s[i]);
         X::attitude_trig(t[6], t[7], t[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
