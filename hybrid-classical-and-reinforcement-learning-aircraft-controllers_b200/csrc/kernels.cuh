@@ -48,6 +48,7 @@ __device__ __forceinline__ void store_pid(float* pid, int64_t n, int64_t i, int 
 template <typename T> struct MinBlocks {
     static constexpr int env = sizeof(T) == 4 ? ACB_ENV_MIN_BLOCKS : 1;
     static constexpr int guided = sizeof(T) == 4 ? ACB_GUIDED_MIN_BLOCKS : 1;
+    static constexpr int cascade = sizeof(T) == 4 ? 4 : 1;      // step_surface / step_cascade: 128 registers
 };
 
 template <typename T>
@@ -85,7 +86,7 @@ __global__ void __launch_bounds__(kBlock) fleet_reset_kernel(FleetPtrs<T> f, con
 
 // ---- K-A: backend.set_controls + backend.step ------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(kBlock) step_surface_kernel(const __grid_constant__ DynParams<T> P, FleetPtrs<T> f,
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::cascade) step_surface_kernel(const __grid_constant__ DynParams<T> P, FleetPtrs<T> f,
                                                               const T* __restrict__ ctrl_in, int K, T h) {
     const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (i >= f.n) return;
@@ -113,7 +114,7 @@ __global__ void __launch_bounds__(kBlock) step_surface_kernel(const __grid_const
 
 // ---- K-B: agent.compute_action + backend.set_controls + backend.step ------------------------------
 template <typename T, int LEVEL>
-__global__ void __launch_bounds__(kBlock) step_cascade_kernel(const __grid_constant__ DynParams<T> P,
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::cascade) step_cascade_kernel(const __grid_constant__ DynParams<T> P,
                                                               const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
                                                               const T* __restrict__ cmd, float dt_ctrl, int K, T h,
                                                               T* __restrict__ surfaces_out) {

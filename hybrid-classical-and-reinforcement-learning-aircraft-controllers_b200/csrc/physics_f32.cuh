@@ -87,10 +87,12 @@ struct FastF32 {
     static __device__ __forceinline__ void sincos_yaw(float x, float* s, float* c) { sincos_mufu(x, s, c); }
     // roll, pitch, yaw of one (stage) state.  The guards only fire for states the physics itself never produces
     // (a caller-injected attitude far outside the wrapped/clamped ranges, or a substep so long that a stage overshoots).
+    // GUARDED = false: the caller has bounded the angles of all four stages for this substep (substep_angles_in_sfu_range).
+    template <bool GUARDED = true>
     static __device__ __forceinline__ void attitude_trig(float phi, float theta, float psi, float* sphi, float* cphi, float* sth,
                                                          float* cth, float* spsi, float* cpsi) {
 #if ACB_F32_MUFU_TRIG
-        if (fmaxf(fmaxf(fabsf(phi), fabsf(theta)), fabsf(psi)) > 12.0f) {
+        if (GUARDED && fmaxf(fmaxf(fabsf(phi), fabsf(theta)), fabsf(psi)) > 12.0f) {
             F32::sincos(phi, sphi, cphi);
             F32::sincos(theta, sth, cth);
             F32::sincos(psi, spsi, cpsi);
@@ -229,14 +231,26 @@ static __device__ __noinline__ int repair_state_f32(float* s) {
     return repaired;
 }
 
+// One test per substep instead of one per stage: a stage angle is angle + a k with a <= dt, |k[6..8]| <= (1 + 2 /
+// cos(max_pitch)) max|rate| (:463-471 with the pitch clipped for tan / cos), and a stage rate is at most max|rate| + dt
+// max_angular_acceleration (:485-487).  Within the bound no stage leaves the SFU's accurate range (|x| <= 12), so the
+// per-stage test of attitude_trig -- a branch in front of every stage's MUFU block, which also fences the instruction
+// scheduler -- can go; beyond it the substep runs the guarded code.  Both give the same bits.
+__device__ __forceinline__ bool substep_angles_in_sfu_range(const DynParams<float>& P, const float (&s)[12], float dt) {
+    const float ang = fmaxf(fmaxf(fabsf(s[6]), fabsf(s[7])), fabsf(s[8]));
+    const float rate = fmaxf(fmaxf(fabsf(s[9]), fabsf(s[10])), fabsf(s[11]));
+    return fmaf(dt * P.euler_rate_gain, rate + dt * P.max_angular_acceleration, ang) <= 11.5f;
+}
+
 // One RK4 substep (:248-254) and the post-step clamps (:258-291).
-__device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const HeldControlsF32& H, float (&s)[12], float& time,
-                                            float dt) {
+template <bool GUARDED>
+__device__ __forceinline__ int rk4_step_f32_impl(const DynParams<float>& P, const HeldControlsF32& H, float (&s)[12], float& time,
+                                                 float dt) {
     float k[12], acc[12], t[12];
     const float half_dt = 0.5f * dt;
     float sphi, cphi, sth, cth, spsi, cpsi;
     // stage 1 at the state itself
-    FastF32::attitude_trig(s[6], s[7], s[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
+    FastF32::attitude_trig<GUARDED>(s[6], s[7], s[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
     dynamics_f32(P, H, s, sphi, cphi, sth, cth, spsi, cpsi, k);
 #pragma unroll
     for (int i = 0; i < 12; ++i) acc[i] = k[i];
@@ -252,7 +266,7 @@ __device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const Hel
         const float wgt = (stage == 3) ? 1.0f : 2.0f;
 #pragma unroll
         for (int i = 0; i < 12; ++i) t[i] = fmaf(a, k[i], s[i]);
-        FastF32::attitude_trig(t[6], t[7], t[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
+        FastF32::attitude_trig<GUARDED>(t[6], t[7], t[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
         dynamics_f32(P, H, t, sphi, cphi, sth, cth, spsi, cpsi, k);
 #pragma unroll
         for (int i = 0; i < 12; ++i) acc[i] = fmaf(wgt, k[i], acc[i]);
@@ -293,13 +307,43 @@ __device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const Hel
     return repaired;
 }
 
+// The substep with a test of every stage's angles (any state, any substep length).
+__device__ __forceinline__ int rk4_step_f32(const DynParams<float>& P, const HeldControlsF32& H, float (&s)[12], float& time,
+                                            float dt) {
+    return rk4_step_f32_impl<true>(P, H, s, time, dt);
+}
+// Cold, out of line: the hot loop carries only the unguarded copy of the substep.
+static __device__ __noinline__ int rk4_step_f32_guarded(const DynParams<float>& P, const HeldControlsF32& H, float* s, float* time,
+                                                        float dt) {
+    float x[12], t = *time;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) x[i] = s[i];
+    const int repaired = rk4_step_f32_impl<true>(P, H, x, t, dt);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) s[i] = x[i];
+    *time = t;
+    return repaired;
+}
+
 // SimulationAircraftBackend.step for the throughput build: K substeps of h under zero-order hold.
 __device__ __forceinline__ int backend_step(const DynParams<float>& P, float (&s)[12], float& time, const float (&c)[4], int K,
                                             float h) {
     const HeldControlsF32 H = hold_controls(P, c);
     int repaired = 0;
 #pragma unroll 1
-    for (int k = 0; k < K; ++k) repaired += rk4_step_f32(P, H, s, time, h);
+    for (int k = 0; k < K; ++k) {
+        if (substep_angles_in_sfu_range(P, s, h)) {
+            repaired += rk4_step_f32_impl<false>(P, H, s, time, h);
+        } else {
+            float tmp[12], tt = time;          // only this copy lives in local memory, not the loop-carried state
+#pragma unroll
+            for (int i = 0; i < 12; ++i) tmp[i] = s[i];
+            repaired += rk4_step_f32_guarded(P, H, tmp, &tt, h);
+#pragma unroll
+            for (int i = 0; i < 12; ++i) s[i] = tmp[i];
+            time = tt;
+        }
+    }
     return repaired;
 }
 
