@@ -42,11 +42,10 @@ __device__ __forceinline__ void store_pid2(float* pid, int64_t n, int64_t i, int
     }
 }
 
-template <int BLOCK, int MIN_BLOCKS>
-__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS)
-env_step_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C,
-                     const __grid_constant__ EnvConst<float> E, EnvPtrs<float> B, const float* __restrict__ action, int64_t first,
-                     int64_t pairs) {
+template <int BLOCK>
+__device__ __forceinline__ void env_step_pair_body(const DynParams<float>& P, const CtrlParams<float>& C, const EnvConst<float>& E,
+                                                   const EnvPtrs<float>& B, const float* __restrict__ action, int64_t first,
+                                                   int64_t pairs) {
     // aircraft [first, first + 2 pairs) of the fleet; first and the field stride n are even (checked by the launcher)
     __shared__ __align__(16) float stage[2 * BLOCK * ACB200_OBS_DIM];
     __shared__ double block_stats[ACB200_STATS_FIELDS];
@@ -248,16 +247,23 @@ env_step_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_co
     }
 }
 
+template <int BLOCK, int MIN_BLOCKS>
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS)
+env_step_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C,
+                     const __grid_constant__ EnvConst<float> E, EnvPtrs<float> B, const float* __restrict__ action, int64_t first,
+                     int64_t pairs) {
+    env_step_pair_body<BLOCK>(P, C, E, B, action, first, pairs);
+}
 // Block shape of the pair kernel: threads per block x resident blocks per SM the register allocation aims at.
 // ACB200_PAIR_VARIANT picks one of the compiled shapes (measurements); the default is the fastest measured on B200.
 // Measured on B200 (2^20 aircraft, profiles/r01g_pair_variants.md): at K = 20 substeps the 168-register shape without
 // spills (12 warps per SM) is fastest; the 128-register shapes spill ~250 bytes and lose what the extra warps gain.  Below
 // K = 4 the step is a memory-bound gather / scatter where the one-aircraft kernel (24 warps per SM) is as fast or
 // faster, so the launcher keeps it there (pair_variant() < 0) unless ACB200_PAIR_VARIANT names a shape.
-#define ACB_PAIR_VARIANTS(X) X(0, 128, 3) X(1, 128, 4) X(2, 64, 7) X(3, 64, 8) X(4, 64, 6)
+#define ACB_PAIR_VARIANTS(X) X(0, 128, 3) X(1, 128, 4) X(2, 64, 7)
 static inline int pair_variant(int K) {
     const char* v = getenv("ACB200_PAIR_VARIANT");
-    return (v && v[0] >= '0' && v[0] <= '4') ? v[0] - '0' : (K < 4 ? -1 : 0);
+    return (v && v[0] >= '0' && v[0] <= '2') ? v[0] - '0' : (K < 4 ? -1 : 0);
 }
 static inline cudaError_t launch_env_step_pair(const DynParams<float>& P, const CtrlParams<float>& C, const EnvConst<float>& E,
                                                const EnvPtrs<float>& e, const float* action, int64_t first, int64_t pairs,
