@@ -32,6 +32,11 @@ template <typename T> struct DynParams {
     T damp_p, damp_q, damp_r;                    // damping * (b or c) / 2
     T inv_vt0, inv_min_airspeed;
     T tan_max_alpha, sin_max_pitch, cos_max_pitch;
+    // moments / inertia with 0.5 rho S (b or c) / I folded into every coefficient: L/Ixx = V^2 (ql_beta beta + ql_damp p / V + ql_ail aileron)
+    T half_rho_S_m;                              // 0.5 rho S / m
+    T ql_beta, ql_damp, ql_ail;                  // 0.5 rho S b / Ixx * {cl_beta, damping_roll b / 2, cl_aileron max_aileron}
+    T qm_alpha, qm_damp, qm_elev;                // 0.5 rho S c / Iyy * {cm_alpha, damping_pitch c / 2, cm_elevator max_elevator}
+    T qn_beta, qn_damp, qn_rud;                  // 0.5 rho S b / Izz * {cn_beta, damping_yaw b / 2, cn_rudder max_rudder}
     T rk_two, rk_one;                            // RK4 weights 2 and 1 as run-time values (physics_f32x2.cuh)
     T euler_rate_gain;                           // bound of |d(Euler angle)/dt| / max|body rate|: 1 + 2 / cos(max_pitch), +1 %
     T inv_ixx, inv_iyy, inv_izz;
@@ -91,6 +96,17 @@ template <typename T> static inline DynParams<T> make_dyn_params(const acb200_ai
     d.tan_max_alpha = (T)tan(host_radians(a.max_alpha));
     d.sin_max_pitch = (T)sin(host_radians(a.max_pitch_angle));
     d.cos_max_pitch = (T)cos(host_radians(a.max_pitch_angle));
+    {
+        const double hs = 0.5 * a.air_density * a.wing_area;
+        const double ql = hs * a.wing_span / a.inertia_xx, qm = hs * a.chord / a.inertia_yy, qn = hs * a.wing_span / a.inertia_zz;
+        d.half_rho_S_m = (T)(hs / a.mass);
+        d.ql_beta = (T)(ql * a.cl_beta); d.ql_damp = (T)(ql * a.damping_roll * a.wing_span * 0.5);
+        d.ql_ail = (T)(ql * a.cl_aileron * host_radians(a.max_aileron_deflection));
+        d.qm_alpha = (T)(qm * a.cm_alpha); d.qm_damp = (T)(qm * a.damping_pitch * a.chord * 0.5);
+        d.qm_elev = (T)(qm * a.cm_elevator * host_radians(a.max_elevator_deflection));
+        d.qn_beta = (T)(qn * a.cn_beta); d.qn_damp = (T)(qn * a.damping_yaw * a.wing_span * 0.5);
+        d.qn_rud = (T)(qn * a.cn_rudder * host_radians(a.max_rudder_deflection));
+    }
     d.rk_two = T(2); d.rk_one = T(1);
     d.euler_rate_gain = (T)(1.01 * (1.0 + 2.0 / fabs(cos(host_radians(a.max_pitch_angle)))));
     d.inv_ixx = (T)(1.0 / a.inertia_xx); d.inv_iyy = (T)(1.0 / a.inertia_yy); d.inv_izz = (T)(1.0 / a.inertia_zz);

@@ -135,17 +135,17 @@ struct FastF32 {
 struct HeldControlsF32 {
     float cl_c;        // cl_0 + cl_elevator * elevator_rad
     float cy;          // cy_rudder * rudder_rad
-    float l_c, m_c, n_c;   // cl_aileron * aileron_rad, cm_elevator * elevator_rad, cn_rudder * rudder_rad
+    float l_c, m_c, n_c;   // (cl_aileron aileron_rad, cm_elevator elevator_rad, cn_rudder rudder_rad) * 0.5 rho S (b|c) / I
     float thrust_max_m;  // max_thrust * throttle / mass
 };
 
 __device__ __forceinline__ HeldControlsF32 hold_controls(const DynParams<float>& P, const float (&c)[4]) {
     HeldControlsF32 H;
     H.cl_c = fmaf(P.cl_elev_rad, c[0], P.cl_0);
-    H.m_c = P.cm_elev_rad * c[0];
-    H.l_c = P.cl_ail_rad * c[1];
+    H.m_c = P.qm_elev * c[0];
+    H.l_c = P.ql_ail * c[1];
     H.cy = P.cy_rud_rad * c[2];
-    H.n_c = P.cn_rud_rad * c[2];
+    H.n_c = P.qn_rud * c[2];
     H.thrust_max_m = (P.max_thrust * P.inv_mass) * c[3];
     return H;
 }
@@ -173,10 +173,9 @@ __device__ __forceinline__ void dynamics_f32(const DynParams<float>& P, const He
 
     // sideslip (:376) and dynamic pressure * S (:379, 392)
     const float beta = FastF32::asin(FastF32::clamp(v * inv_Vs, -1.0f, 1.0f));
-    const float qS = P.half_rho_S * V2;
 
     // aerodynamic + thrust + gravity accelerations (:383-411, 455-460); 1/m is folded into qS and thrust on the way in
-    const float qS_m = qS * P.inv_mass;
+    const float qS_m = P.half_rho_S_m * V2;
     const float cl = fmaf(P.cl_alpha, alpha, H.cl_c);
     const float cd = fmaf(P.cd_alpha2, alpha * alpha, P.cd_0);
     const float lift = qS_m * cl, drag = qS_m * cd;
@@ -186,10 +185,10 @@ __device__ __forceinline__ void dynamics_f32(const DynParams<float>& P, const He
     const float ay = fmaf(gcth, sphi, qS_m * H.cy);
     const float az = fmaf(gcth, cphi, -fmaf(drag, sin_alpha, lift * cos_alpha));
 
-    // moments / inertia (:415-435, 474-482); 1/I is folded into the span/chord factors
-    const float l_a = (qS * P.b_ixx) * fmaf(P.cl_beta, beta, fmaf(P.damp_p * p, inv_Vs, H.l_c));
-    const float m_a = (qS * P.c_iyy) * fmaf(P.damp_q * q, inv_Vs, fmaf(P.cm_alpha, alpha, H.m_c));
-    const float n_a = (qS * P.b_izz) * fmaf(P.cn_beta, beta, fmaf(P.damp_r * r, inv_Vs, H.n_c));
+    // moments / inertia (:415-435, 474-482); 0.5 rho S (b or c) / I is folded into every coefficient on the host
+    const float l_a = V2 * fmaf(P.ql_beta, beta, fmaf(P.ql_damp * p, inv_Vs, H.l_c));
+    const float m_a = V2 * fmaf(P.qm_damp * q, inv_Vs, fmaf(P.qm_alpha, alpha, H.m_c));
+    const float n_a = V2 * fmaf(P.qn_beta, beta, fmaf(P.qn_damp * r, inv_Vs, H.n_c));
 
     // position kinematics (:440-452) as three plane rotations, R = Rz(psi) Ry(theta) Rx(phi)
     const float y1 = fmaf(cphi, v, -sphi * w), z1 = fmaf(sphi, v, cphi * w);
@@ -292,9 +291,12 @@ __device__ __forceinline__ int rk4_step_f32_impl(const DynParams<float>& P, cons
     // :258, 286-291 as one test: 0 * x is NaN for x = NaN or +-inf (fminf/fmaxf above turn a NaN into a bound,
     // so test the unclamped positions and attitude; velocities and rates are finite after their clamps unless NaN
     // went in, which the clamps map to a bound)
+    // Only the positions, roll and yaw can still be non-finite here: the velocity, pitch and rate clamps above have mapped
+    // NaN and +-inf to a bound.
     float chk = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 12; ++i) chk = fmaf(0.0f, s[i], chk);
+    for (int i = 0; i < 12; ++i)
+        if (i < 3 || i == 6 || i == 8) chk = fmaf(0.0f, s[i], chk);
     int repaired = 0;
     if (chk != 0.0f) {        // NaN compares unequal
         float tmp[12];

@@ -120,9 +120,8 @@ __device__ __forceinline__ void dynamics_f32x2(const DynParams<float>& P, const 
     const v2 sin_alpha = X::mul(tcl, cos_alpha);
 
     const v2 beta = X::asin(X::clamp(X::mul(v, inv_Vs), -1.0f, 1.0f));
-    const v2 qS = X::mul(X::bc(P.half_rho_S), V2);
 
-    const v2 qS_m = X::mul(qS, X::bc(P.inv_mass));
+    const v2 qS_m = X::mul(X::bc(P.half_rho_S_m), V2);
     const v2 cl = X::fma(X::bc(P.cl_alpha), alpha, H.cl_c);
     const v2 cd = X::fma(X::bc(P.cd_alpha2), X::mul(alpha, alpha), X::bc(P.cd_0));
     const v2 lift = X::mul(qS_m, cl), drag = X::mul(qS_m, cd);
@@ -132,9 +131,9 @@ __device__ __forceinline__ void dynamics_f32x2(const DynParams<float>& P, const 
     const v2 ay = X::fma(gcth, sphi, X::mul(qS_m, H.cy));
     const v2 az = X::fma(gcth, cphi, X::neg(X::fma(drag, sin_alpha, X::mul(lift, cos_alpha))));
 
-    const v2 l_a = X::mul(X::mul(qS, X::bc(P.b_ixx)), X::fma(X::bc(P.cl_beta), beta, X::fma(X::mul(X::bc(P.damp_p), p), inv_Vs, H.l_c)));
-    const v2 m_a = X::mul(X::mul(qS, X::bc(P.c_iyy)), X::fma(X::mul(X::bc(P.damp_q), q), inv_Vs, X::fma(X::bc(P.cm_alpha), alpha, H.m_c)));
-    const v2 n_a = X::mul(X::mul(qS, X::bc(P.b_izz)), X::fma(X::bc(P.cn_beta), beta, X::fma(X::mul(X::bc(P.damp_r), r), inv_Vs, H.n_c)));
+    const v2 l_a = X::mul(V2, X::fma(X::bc(P.ql_beta), beta, X::fma(X::mul(X::bc(P.ql_damp), p), inv_Vs, H.l_c)));
+    const v2 m_a = X::mul(V2, X::fma(X::mul(X::bc(P.qm_damp), q), inv_Vs, X::fma(X::bc(P.qm_alpha), alpha, H.m_c)));
+    const v2 n_a = X::mul(V2, X::fma(X::bc(P.qn_beta), beta, X::fma(X::mul(X::bc(P.qn_damp), r), inv_Vs, H.n_c)));
 
     const v2 y1 = X::fma(cphi, v, X::mul(X::neg(sphi), w)), z1 = X::fma(sphi, v, X::mul(cphi, w));
     const v2 x2 = X::fma(cth, u, X::mul(sth, z1));
@@ -249,7 +248,8 @@ __device__ __forceinline__ int rk4_step_f32x2(const DynParams<float>& P, const H
     if (s[2].y > 0.0f) { s[2].y = 0.0f; s[5].y = fmaxf(0.0f, s[5].y); }
     v2 chk = X::bc(0.0f);
 #pragma unroll
-    for (int i = 0; i < 12; ++i) chk = X::fma(X::bc(0.0f), s[i], chk);
+    for (int i = 0; i < 12; ++i)
+        if (i < 3 || i == 6 || i == 8) chk = X::fma(X::bc(0.0f), s[i], chk);   // the clamped words are finite (physics_f32.cuh)
     int repaired = 0;
     if (chk.x != 0.0f || chk.y != 0.0f) {
         float tmp[12];
