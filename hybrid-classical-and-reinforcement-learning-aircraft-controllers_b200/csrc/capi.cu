@@ -211,6 +211,19 @@ int acb200_set_controller_params(acb200_ctx* ctx, const acb200_controller_params
     return ACB200_OK;
 }
 
+// The throughput (fp32) build evaluates atan on |tan(alpha)| <= 1 and divides by cos(max_pitch) (physics_f32.cuh): parameter
+// sets outside that range are refused there instead of being integrated inaccurately; the parity build takes any value the
+// reference takes.
+static int check_f32_range(acb200_ctx* ctx, int precision) {
+    if (precision != 32) return ACB200_OK;
+    const acb200_aircraft_params& a = ctx->aircraft;
+    if (!(a.max_alpha > 0.0 && a.max_alpha <= 45.0))
+        return fail(ctx, ACB200_EVALUE, "precision 32 needs 0 < max_alpha <= 45 degrees (use precision 64 beyond)");
+    if (!(a.max_pitch_angle > 0.0 && a.max_pitch_angle <= 89.0))
+        return fail(ctx, ACB200_EVALUE, "precision 32 needs 0 < max_pitch_angle <= 89 degrees (use precision 64 beyond)");
+    return ACB200_OK;
+}
+
 int acb200_fleet_reset(acb200_ctx* ctx, const acb200_fleet* f, const uint8_t* mask, const void* init_state) {
     int rc = check_fleet(ctx, f, false);
     if (rc) return rc;
@@ -228,6 +241,7 @@ int acb200_step_surface(acb200_ctx* ctx, const acb200_fleet* f, const void* ctrl
     if (!ctrl_in) return fail(ctx, ACB200_ENULL, "ctrl_in is NULL");
     int K; double h;
     if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
+    if ((rc = check_f32_range(ctx, f->precision))) return rc;
     cudaSetDevice(ctx->device);
     const cudaError_t e = (f->precision == 64)
                               ? Launch<double>::step_surface(ctx->aircraft, typed<double>(*f), (const double*)ctrl_in, K, h, ctx->stream)
@@ -245,6 +259,7 @@ int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const
         return fail(ctx, ACB200_ENOSUP, "step_cascade supports levels 3 (attitude) and 4 (rate)");
     int K; double h;
     if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
+    if ((rc = check_f32_range(ctx, f->precision))) return rc;
     cudaSetDevice(ctx->device);
     const cudaError_t e =
         (f->precision == 64)
@@ -270,6 +285,7 @@ static int step_guided_impl(acb200_ctx* ctx, const acb200_fleet* f, float* pid_o
     }
     int K; double h;
     if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
+    if ((rc = check_f32_range(ctx, f->precision))) return rc;
     cudaSetDevice(ctx->device);
     const cudaError_t e =
         (f->precision == 64)
@@ -313,6 +329,7 @@ static int env_step_impl(acb200_ctx* ctx, const acb200_env* env, const acb200_en
     if (action && ((uintptr_t)action & 15)) return fail(ctx, ACB200_EVALUE, "action must be 16-byte aligned");
     int K; double h;
     if ((rc = substeps(ctx, cfg->dt, cfg->dt_physics, &K, &h))) return rc;
+    if ((rc = check_f32_range(ctx, env->fleet.precision))) return rc;
     cudaSetDevice(ctx->device);
     if (count < 0) count = env->fleet.n;
     const cudaStream_t st = own_stream ? stream : ctx->stream;

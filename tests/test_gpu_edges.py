@@ -55,6 +55,26 @@ def test_bad_arguments_raise_like_the_reference():
     assert ctx.lib.acb200_gae(ctx.handle, 4, 4, None, None, None, None, None, 0.99, 0.95, None, None) == -3   # ACB200_ENULL
 
 
+def test_fp32_build_refuses_parameters_outside_its_polynomial_ranges():
+    """The throughput build evaluates atan on |tan(alpha)| <= 1 (physics_f32.cuh): max_alpha beyond 45 degrees is an error
+    there, not a silent loss of accuracy; the parity build takes what the reference takes."""
+    import ctypes as C
+    import acb200
+    for precision, ok in ((32, False), (64, True)):
+        env = acb200.BatchedRateControlEnv(64, controller="rate_pid", precision=precision, seed=1)
+        env.reset()
+        p = acb200.default_aircraft_params()
+        p.max_alpha = 60.0
+        env.ctx.check(env.ctx.lib.acb200_set_aircraft_params(env.ctx.handle, C.byref(p)))
+        if ok:
+            env.step()
+        else:
+            with pytest.raises(ValueError, match="max_alpha"):
+                env.step()
+        env.ctx.check(env.ctx.lib.acb200_set_aircraft_params(env.ctx.handle, C.byref(acb200.default_aircraft_params())))
+        env.step()
+
+
 def test_non_finite_observation_stays_in_its_row():
     """A NaN observation poisons that aircraft's action only (rows are independent through every layer)."""
     import acb200
