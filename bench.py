@@ -272,8 +272,7 @@ def run_gpu(args):
     fp_peak = fp32_measured if precision == 32 else fp32_measured / 2
     traffic = None
     # fp32 fleets of even size run the two-aircraft-per-thread kernel on packed FP32 (csrc/kernels_pair_f32.cuh)
-    pair = (precision == 32 and n % 2 == 0 and os.environ.get("ACB200_ENV_PAIR", "1")[:1] != "0"
-            and (k_sub >= 4 or "ACB200_PAIR_VARIANT" in os.environ))
+    pair = precision == 32 and n % 2 == 0 and os.environ.get("ACB200_ENV_PAIR", "1")[:1] != "0"
     kernel_name = "env_step_pair_kernel" if pair else "env_step_kernel"
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:

@@ -527,6 +527,15 @@ template <typename T>
 cudaError_t Launch<T>::step_surface(const acb200_aircraft_params& ap, const FleetPtrs<T>& f, const T* ctrl_in, int K, double h,
                                     cudaStream_t st) {
     if (f.n <= 0) return cudaSuccess;
+#ifdef ACB_PAIR_KERNEL
+    if constexpr (sizeof(T) == 4) {
+        if (fleet_pair_ok(f, ctrl_in, nullptr, K)) {
+            step_fleet_pair_kernel<0><<<grid_for(f.n / 2), kBlock, 0, st>>>(make_dyn_params<float>(ap), CtrlParams<float>{}, f, ctrl_in,
+                                                                           0.0f, K, (float)h, nullptr, f.n / 2);
+            return cudaGetLastError();
+        }
+    }
+#endif
     step_surface_kernel<T><<<grid_for(f.n), kBlock, 0, st>>>(make_dyn_params<T>(ap), f, ctrl_in, K, (T)h);
     return cudaGetLastError();
 }
@@ -537,6 +546,19 @@ cudaError_t Launch<T>::step_cascade(const acb200_aircraft_params& ap, const acb2
     if (f.n <= 0) return cudaSuccess;
     const DynParams<T> P = make_dyn_params<T>(ap);
     const CtrlParams<T> C = make_ctrl_params<T>(cp);
+#ifdef ACB_PAIR_KERNEL
+    if constexpr (sizeof(T) == 4) {
+        if (fleet_pair_ok(f, cmd, surfaces_out, K)) {
+            if (level == ACB200_LEVEL_ATTITUDE)
+                step_fleet_pair_kernel<ACB200_LEVEL_ATTITUDE><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (float)h,
+                                                                                                   surfaces_out, f.n / 2);
+            else
+                step_fleet_pair_kernel<ACB200_LEVEL_RATE><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (float)h,
+                                                                                               surfaces_out, f.n / 2);
+            return cudaGetLastError();
+        }
+    }
+#endif
     if (level == ACB200_LEVEL_ATTITUDE)
         step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (T)h, surfaces_out);
     else
@@ -605,6 +627,8 @@ template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, Kerne
     else if (!strcmp(name, "env_step")) fn = (const void*)env_step_kernel<T>;
 #ifdef ACB_PAIR_KERNEL
     else if (!strcmp(name, "env_step_pair") && sizeof(T) == 4) fn = env_step_pair_entry();
+    else if (!strcmp(name, "step_surface_pair") && sizeof(T) == 4) fn = (const void*)step_fleet_pair_kernel<0>;
+    else if (!strcmp(name, "step_cascade_attitude_pair") && sizeof(T) == 4) fn = (const void*)step_fleet_pair_kernel<ACB200_LEVEL_ATTITUDE>;
 #endif
     else if (!strcmp(name, "step_hsa")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_HSA>;
     else if (!strcmp(name, "step_waypoint")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_WAYPOINT>;

@@ -10,11 +10,6 @@
 
 namespace acb {
 
-// Resident blocks per SM the register allocation aims at: 3 blocks x 128 threads = 12 warps = 168 registers.
-#ifndef ACB_PAIR_MIN_BLOCKS
-#define ACB_PAIR_MIN_BLOCKS 3
-#endif
-
 __device__ __forceinline__ v2 ld2(const float* base, int f, int64_t n, int64_t i) {
     return *reinterpret_cast<const v2*>(base + (int64_t)f * n + i);
 }
@@ -56,13 +51,11 @@ __device__ __forceinline__ void env_step_pair_body(const DynParams<float>& P, co
     const bool valid = pair_idx < pairs;
     if (threadIdx.x < ACB200_STATS_FIELDS) block_stats[threadIdx.x] = 0.0;
 
-    float o[2][18];
     float st[ACB200_STATS_FIELDS];
 #pragma unroll
     for (int k = 0; k < ACB200_STATS_FIELDS; ++k) st[k] = 0.0f;
 
     if (valid) {
-        EnvRegs<float> e[2];
         v2 s2[12], time2;
         // (A) controller, once per lane
 #pragma unroll
@@ -101,125 +94,118 @@ __device__ __forceinline__ void env_step_pair_body(const DynParams<float>& P, co
         // (B) physics: rate_env.py:234-237, both lanes on packed instructions.  What the loop does not touch (the clipped
         // action, the residual bonus, the simulation time) waits in the thread's own rows of the observation staging
         // buffer, which is idle until the end of the step: 12 registers less across the loop.
-        float* const stash = stage + threadIdx.x * (2 * ACB200_OBS_DIM);
+        if (B.f.controls) {      // the held surfaces leave now (a reset below zeroes its lane's words again)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) st2(B.f.controls, k, n, i, c[0][k], c[1][k]);
+        }
+        float* const stash = stage + threadIdx.x * (2 * ACB200_OBS_DIM) + 24;
 #pragma unroll
         for (int k = 0; k < 4; ++k) *reinterpret_cast<v2*>(stash + 2 * k) = make_float2(act[0][k], act[1][k]);
         *reinterpret_cast<v2*>(stash + 8) = make_float2(residual_bonus[0], residual_bonus[1]);
         *reinterpret_cast<v2*>(stash + 10) = time2;
         const int repaired = backend_step2(P, s2, c[0], c[1], E.K, E.h);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { const v2 a = *reinterpret_cast<const v2*>(stash + 2 * k); act[0][k] = a.x; act[1][k] = a.y; }
-        { const v2 a = *reinterpret_cast<const v2*>(stash + 8); residual_bonus[0] = a.x; residual_bonus[1] = a.y; }
         time2 = *reinterpret_cast<const v2*>(stash + 10);
-        for (int k = 0; k < E.K; ++k) time2 = P2::add(time2, P2::bc(E.h));       // t += dt once per substep (:254)
-        // (C) the env's own memory
-        {
-            v2 x;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) { x = ld2(B.rate_cmd, k, n, i); e[0].rate_cmd[k] = x.x; e[1].rate_cmd[k] = x.y; }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) { x = ld2(B.prev_action, k, n, i); e[0].prev_action[k] = x.x; e[1].prev_action[k] = x.y; }
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                x = ld2(B.rew_mem, k, n, i); e[0].prev_err[k] = x.x; e[1].prev_err[k] = x.y;
-                x = ld2(B.rew_mem, 3 + k, n, i); e[0].sign_changes[k] = x.x; e[1].sign_changes[k] = x.y;
-            }
-            x = ld2(B.rew_mem, 6, n, i); e[0].settle_timer = x.x; e[1].settle_timer = x.y;
-#pragma unroll
-            for (int k = 0; k < 7; ++k) { x = ld2(B.sched, k, n, i); e[0].sched[k] = x.x; e[1].sched[k] = x.y; }
-            x = ld2(B.env_time, 0, n, i); e[0].env_time = x.x; e[1].env_time = x.y;
-            x = ld2(B.difficulty, 0, n, i); e[0].difficulty = x.x; e[1].difficulty = x.y;
-            x = ld2(B.ep_return, 0, n, i); e[0].ep_return = x.x; e[1].ep_return = x.y;
-            const int2 sc = *reinterpret_cast<const int2*>(B.step_count + i);
-            e[0].step_count = sc.x; e[1].step_count = sc.y;
-            const uint2 ei = *reinterpret_cast<const uint2*>(B.episode_idx + i);
-            e[0].episode_idx = ei.x; e[1].episode_idx = ei.y;
-            const uchar2 is = *reinterpret_cast<const uchar2*>(B.is_settled + i);
-            e[0].is_settled = is.x; e[1].is_settled = is.y;
-            const uchar2 ct = *reinterpret_cast<const uchar2*>(B.command_type + i);
-            e[0].command_type = ct.x; e[1].command_type = ct.y;
-        }
-        float reward[2], comp[2][8];
-        bool terminated[2], truncated[2];
+        // (C) reward, termination, reset and scatter, ONE LANE AT A TIME in a rolled loop: the two lanes' bookkeeping words
+        // together (2 x ~45 registers + 2 observation rows) would be the register peak of the kernel, above the substep
+        // loop's 139; per lane they fit under it, the code is half as long, and the 4-byte accesses of the two passes
+        // meet in the same 32-byte sectors.  The lane's observation row goes straight into the staging buffer.
         st[14] = (float)repaired;
         st[15] = 2.0f;
-#pragma unroll
+        for (int k = 0; k < E.K; ++k) time2 = P2::add(time2, P2::bc(E.h));       // t += dt once per substep (:254)
+#pragma unroll 1
         for (int l = 0; l < 2; ++l) {
+            const int64_t il = i + l;
+            EnvRegs<float> e;
+            float act[4];
+            {   // parked before the loop in floats 24..35 of the thread's staging rows (lane 1's row is written last)
+                const float* stash = stage + threadIdx.x * (2 * ACB200_OBS_DIM) + 24;
 #pragma unroll
-            for (int k = 0; k < 12; ++k) e[l].s[k] = lane(s2[k], l);
-            e[l].time = lane(time2, l);
-            derived_outputs(e[l].s, e[l].d);
-            env_after_physics(E, e[l], act[l], residual_bonus[l], comp[l], reward[l], terminated[l], truncated[l], i + l);
-            env_observe(e[l], o[l]);
+                for (int k = 0; k < 4; ++k) act[k] = stash[2 * k + l];
+            }
+            const float residual_bonus = stage[threadIdx.x * (2 * ACB200_OBS_DIM) + 32 + l];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) st[6 + k] += comp[l][k];
-            if (terminated[l] || truncated[l]) {
-                st[0] += 1.0f; st[1] += e[l].ep_return; st[2] += e[l].ep_return * e[l].ep_return; st[3] += (float)e[l].step_count;
-                st[4] += (terminated[l] && !truncated[l]) ? 1.0f : 0.0f;
-                st[5] += truncated[l] ? 1.0f : 0.0f;
+            for (int k = 0; k < 12; ++k) e.s[k] = lane(s2[k], l);
+            e.time = lane(time2, l);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) e.rate_cmd[k] = ldf(B.rate_cmd, k, n, il);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) e.prev_action[k] = ldf(B.prev_action, k, n, il);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { e.prev_err[k] = ldf(B.rew_mem, k, n, il); e.sign_changes[k] = ldf(B.rew_mem, 3 + k, n, il); }
+            e.settle_timer = ldf(B.rew_mem, 6, n, il);
+#pragma unroll
+            for (int k = 0; k < 7; ++k) e.sched[k] = ldf(B.sched, k, n, il);
+            e.env_time = B.env_time[il];
+            e.step_count = B.step_count[il];
+            e.episode_idx = B.episode_idx[il];
+            e.is_settled = B.is_settled[il];
+            e.command_type = B.command_type[il];
+            e.difficulty = B.difficulty[il];
+            e.ep_return = B.ep_return[il];
+            derived_outputs(e.s, e.d);
+
+            float comp[8], reward, o[18];
+            bool terminated, truncated;
+            env_after_physics(E, e, act, residual_bonus, comp, reward, terminated, truncated, il);
+            env_observe(e, o);
+            B.reward[il] = reward;
+            if (B.reward_f32) B.reward_f32[il] = reward;
+            B.terminated[il] = (uint8_t)terminated;
+            B.truncated[il] = (uint8_t)truncated;
+            if (B.components) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) stf(B.components, k, n, il, comp[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) st[6 + k] += comp[k];
+            if (terminated || truncated) {
+                st[0] += 1.0f; st[1] += e.ep_return; st[2] += e.ep_return * e.ep_return; st[3] += (float)e.step_count;
+                st[4] += (terminated && !truncated) ? 1.0f : 0.0f;
+                st[5] += truncated ? 1.0f : 0.0f;
                 if (E.auto_reset) {
                     // SB3 VecEnv semantics: keep the terminal observation, reset, hand back the reset observation
                     if (B.terminal_obs) {
 #pragma unroll
-                        for (int k = 0; k < ACB200_OBS_DIM; ++k) B.terminal_obs[(i + l) * ACB200_OBS_DIM + k] = o[l][k];
+                        for (int k = 0; k < ACB200_OBS_DIM; ++k) B.terminal_obs[il * ACB200_OBS_DIM + k] = o[k];
                     }
-                    env_reset_one(E, i + l, e[l]);
-                    env_observe(e[l], o[l]);
+                    env_reset_one(E, il, e);
+                    env_observe(e, o);
 #pragma unroll
-                    for (int k = 0; k < ACB200_PID_FIELDS; ++k) stf(B.f.pid, k, n, i + l, 0.0f);   // agent.reset()
+                    for (int k = 0; k < ACB200_PID_FIELDS; ++k) stf(B.f.pid, k, n, il, 0.0f);   // agent.reset()
+                    if (B.f.controls) {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) c[l][k] = 0.0f;
+                        for (int k = 0; k < 4; ++k) stf(B.f.controls, k, n, il, 0.0f);
+                    }
                 }
             }
-        }
-        // scatter, 8 bytes per field and thread
-        *reinterpret_cast<v2*>(B.reward + i) = make_float2(reward[0], reward[1]);
-        if (B.reward_f32) *reinterpret_cast<v2*>(B.reward_f32 + i) = make_float2(reward[0], reward[1]);
-        *reinterpret_cast<uchar2*>(B.terminated + i) = make_uchar2((uint8_t)terminated[0], (uint8_t)terminated[1]);
-        *reinterpret_cast<uchar2*>(B.truncated + i) = make_uchar2((uint8_t)truncated[0], (uint8_t)truncated[1]);
-        if (B.components) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) st2(B.components, k, n, i, comp[0][k], comp[1][k]);
-        }
+            for (int k = 0; k < 12; ++k) stf(B.f.state, k, n, il, e.s[k]);
+            stf(B.f.state, 12, n, il, e.time);
 #pragma unroll
-        for (int k = 0; k < 12; ++k) st2(B.f.state, k, n, i, e[0].s[k], e[1].s[k]);
-        st2(B.f.state, 12, n, i, e[0].time, e[1].time);
+            for (int k = 0; k < 4; ++k) stf(B.f.derived, k, n, il, e.d[k]);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) st2(B.f.derived, k, n, i, e[0].d[k], e[1].d[k]);
-        if (B.f.controls) {
+            for (int k = 0; k < 3; ++k) stf(B.rate_cmd, k, n, il, e.rate_cmd[k]);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) st2(B.f.controls, k, n, i, c[0][k], c[1][k]);
-        }
+            for (int k = 0; k < 4; ++k) stf(B.prev_action, k, n, il, e.prev_action[k]);
 #pragma unroll
-        for (int k = 0; k < 3; ++k) st2(B.rate_cmd, k, n, i, e[0].rate_cmd[k], e[1].rate_cmd[k]);
+            for (int k = 0; k < 3; ++k) { stf(B.rew_mem, k, n, il, e.prev_err[k]); stf(B.rew_mem, 3 + k, n, il, e.sign_changes[k]); }
+            stf(B.rew_mem, 6, n, il, e.settle_timer);
+            if (e.step_count == 0) {   // the schedule only changes at a reset
 #pragma unroll
-        for (int k = 0; k < 4; ++k) st2(B.prev_action, k, n, i, e[0].prev_action[k], e[1].prev_action[k]);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            st2(B.rew_mem, k, n, i, e[0].prev_err[k], e[1].prev_err[k]);
-            st2(B.rew_mem, 3 + k, n, i, e[0].sign_changes[k], e[1].sign_changes[k]);
-        }
-        st2(B.rew_mem, 6, n, i, e[0].settle_timer, e[1].settle_timer);
-#pragma unroll
-        for (int l = 0; l < 2; ++l) {
-            if (e[l].step_count == 0) {   // the schedule only changes at a reset
-#pragma unroll
-                for (int k = 0; k < 7; ++k) stf(B.sched, k, n, i + l, e[l].sched[k]);
+                for (int k = 0; k < 7; ++k) stf(B.sched, k, n, il, e.sched[k]);
             }
+            B.env_time[il] = e.env_time;
+            B.step_count[il] = e.step_count;
+            B.episode_idx[il] = e.episode_idx;
+            B.is_settled[il] = e.is_settled;
+            B.ep_return[il] = e.ep_return;
+            float* row = stage + threadIdx.x * (2 * ACB200_OBS_DIM) + l * ACB200_OBS_DIM;
+#pragma unroll
+            for (int k = 0; k < ACB200_OBS_DIM; ++k) row[k] = o[k];
         }
-        st2(B.env_time, 0, n, i, e[0].env_time, e[1].env_time);
-        *reinterpret_cast<int2*>(B.step_count + i) = make_int2(e[0].step_count, e[1].step_count);
-        *reinterpret_cast<uint2*>(B.episode_idx + i) = make_uint2(e[0].episode_idx, e[1].episode_idx);
-        *reinterpret_cast<uchar2*>(B.is_settled + i) = make_uchar2(e[0].is_settled, e[1].is_settled);
-        st2(B.ep_return, 0, n, i, e[0].ep_return, e[1].ep_return);
     }
 
-    // observations: float[n][18] row-major; the thread's two rows are adjacent (36 floats = 9 x 16 bytes)
-    if (valid) {
-        float* row = stage + threadIdx.x * (2 * ACB200_OBS_DIM);
-#pragma unroll
-        for (int k = 0; k < ACB200_OBS_DIM; ++k) { row[k] = o[0][k]; row[ACB200_OBS_DIM + k] = o[1][k]; }
-    }
+    // observations: float[n][18] row-major; the block's rows leave as one contiguous, coalesced run
     __syncthreads();
     {
         const int64_t end = first + 2 * pairs;
@@ -255,15 +241,14 @@ env_step_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_co
     env_step_pair_body<BLOCK>(P, C, E, B, action, first, pairs);
 }
 // Block shape of the pair kernel: threads per block x resident blocks per SM the register allocation aims at.
-// ACB200_PAIR_VARIANT picks one of the compiled shapes (measurements); the default is the fastest measured on B200.
-// Measured on B200 (2^20 aircraft, profiles/r01g_pair_variants.md): at K = 20 substeps the 168-register shape without
-// spills (12 warps per SM) is fastest; the 128-register shapes spill ~250 bytes and lose what the extra warps gain.  Below
-// K = 4 the step is a memory-bound gather / scatter where the one-aircraft kernel (24 warps per SM) is as fast or
-// faster, so the launcher keeps it there (pair_variant() < 0) unless ACB200_PAIR_VARIANT names a shape.
-#define ACB_PAIR_VARIANTS(X) X(0, 128, 3) X(1, 128, 4) X(2, 64, 7)
-static inline int pair_variant(int K) {
+// ACB200_PAIR_VARIANT picks the other compiled shape (measurements).  With the post-physics part run one lane at a time the
+// kernel needs 148 registers uncapped and fits 128 without a spill, so the default is 4 blocks x 128 threads = 16 warps per
+// SM: as fast as the 12-warp shape at K = 20 (0.4726 vs 0.4731 ms per 2^20 aircraft) and faster than the one-aircraft kernel
+// at K = 1 (0.1263 vs 0.1283 ms); profiles/r01g_pair_variants.md.
+#define ACB_PAIR_VARIANTS(X) X(0, 128, 3) X(1, 128, 4)
+static inline int pair_variant(int) {
     const char* v = getenv("ACB200_PAIR_VARIANT");
-    return (v && v[0] >= '0' && v[0] <= '2') ? v[0] - '0' : (K < 4 ? -1 : 0);
+    return (v && v[0] >= '0' && v[0] <= '1') ? v[0] - '0' : 1;
 }
 static inline cudaError_t launch_env_step_pair(const DynParams<float>& P, const CtrlParams<float>& C, const EnvConst<float>& E,
                                                const EnvPtrs<float>& e, const float* action, int64_t first, int64_t pairs,
@@ -286,6 +271,81 @@ static inline const void* env_step_pair_entry() {
 #undef ACB_PAIR_CASE
     }
     return nullptr;
+}
+
+// ---- the fleet step (backend.set_controls + backend.step, with or without an agent in front) for aircraft pairs ----------
+// LEVEL 0: in = clipped-on-entry surface commands (step_surface_kernel); ACB200_LEVEL_RATE / _ATTITUDE: in = the agent's
+// command (step_cascade_kernel).  Same lane arithmetic as those kernels; the K substeps on packed FP32.
+template <int LEVEL>
+__global__ void __launch_bounds__(kBlock, 4)
+step_fleet_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C, FleetPtrs<float> f,
+                       const float* __restrict__ in, float dt_ctrl, int K, float h, float* __restrict__ surfaces_out, int64_t pairs) {
+    const int64_t n = f.n;
+    const int64_t pair_idx = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (pair_idx >= pairs) return;
+    const int64_t i = 2 * pair_idx;
+    v2 s2[12], time2;
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s2[k] = ld2(f.state, k, n, i);
+    time2 = ld2(f.state, 12, n, i);
+    float cm[2][4], surf[2][4], c[2][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const v2 a = ld2(in, k, n, i); cm[0][k] = a.x; cm[1][k] = a.y; }
+    if (LEVEL == 0) {
+#pragma unroll
+        for (int l = 0; l < 2; ++l) clip_controls(cm[l], c[l]);
+    } else {
+        PidMem rate[2][3], ang[2][3];
+        load_pid2(f.pid, n, i, 0, rate[0], rate[1]);
+        if (LEVEL == ACB200_LEVEL_ATTITUDE) load_pid2(f.pid, n, i, 1, ang[0], ang[1]);
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            float sl[12];
+#pragma unroll
+            for (int k = 0; k < 12; ++k) sl[k] = lane(s2[k], l);
+            if (LEVEL == ACB200_LEVEL_ATTITUDE) attitude_agent(C, ang[l], rate[l], cm[l][0], cm[l][1], cm[l][2], cm[l][3], sl, dt_ctrl, surf[l]);
+            else rate_agent(C, rate[l], cm[l][0], cm[l][1], cm[l][2], cm[l][3], sl[9], sl[10], sl[11], dt_ctrl, surf[l]);
+            clip_controls(surf[l], c[l]);
+        }
+        if (LEVEL == ACB200_LEVEL_ATTITUDE) store_pid2(f.pid, n, i, 1, ang[0], ang[1]);
+        store_pid2(f.pid, n, i, 0, rate[0], rate[1]);
+        if (surfaces_out) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) st2(surfaces_out, k, n, i, surf[0][k], surf[1][k]);
+        }
+    }
+    if (f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) st2(f.controls, k, n, i, c[0][k], c[1][k]);
+    }
+    backend_step2(P, s2, c[0], c[1], K, h);
+    for (int k = 0; k < K; ++k) time2 = P2::add(time2, P2::bc(h));            // t += dt once per substep (:254)
+#pragma unroll
+    for (int k = 0; k < 12; ++k) *reinterpret_cast<v2*>(f.state + (int64_t)k * n + i) = s2[k];
+    *reinterpret_cast<v2*>(f.state + 12 * n + i) = time2;
+    if (f.derived) {
+        float d[2][4];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            float sl[12];
+#pragma unroll
+            for (int k = 0; k < 12; ++k) sl[k] = lane(s2[k], l);
+            derived_outputs(sl, d[l]);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) st2(f.derived, k, n, i, d[0][k], d[1][k]);
+    }
+}
+
+// Whole fleets only (n even, 8-byte aligned fields); otherwise the one-aircraft kernels run.
+static inline bool fleet_pair_ok(const FleetPtrs<float>& f, const void* in, const void* out, int K) {
+    const char* pair_env = getenv("ACB200_ENV_PAIR");
+    if (pair_env && pair_env[0] == '0') return false;
+    if (pair_variant(K) < 0 || f.n < 2 || (f.n & 1)) return false;
+    const void* w8[] = {f.state, f.controls, f.derived, f.pid, in, out};
+    for (const void* p : w8)
+        if (p && ((uintptr_t)p & 7)) return false;
+    return true;
 }
 
 // The pair kernel needs 8-byte access to every float field (first, n even; bases 8-byte aligned) and 2-byte access to the flags.

@@ -123,3 +123,45 @@ def test_pair_kernel_repairs_nonfinite_state_like_the_one_aircraft_kernel():
             os.environ.pop("ACB200_ENV_PAIR", None)
     assert np.array_equal(outs[0][0].view(np.uint32), outs[1][0].view(np.uint32))
     assert np.isfinite(outs[1][0]).all() and outs[0][1][14] == outs[1][1][14] > 0
+
+
+@pytest.mark.parametrize("level,dt", [("surface", 0.01), ("rate", 0.01), ("attitude", 0.02), ("surface", 0.001)])
+def test_fleet_pair_kernels_are_bit_identical_to_the_one_aircraft_kernels(level, dt):
+    """AircraftFleet.step_surface / step_rate / step_attitude (backend.set_controls + backend.step, with the agents in front)
+    on aircraft pairs against the one-aircraft kernels: state, PID memory, held controls, derived outputs, surfaces."""
+    import acb200
+    n, steps = 1000, 120
+    g = torch.Generator().manual_seed(4)
+    init = torch.zeros(13, n)
+    init[2].uniform_(-200, -50, generator=g); init[3].uniform_(15, 30, generator=g)
+    init[6].uniform_(-0.3, 0.3, generator=g); init[7].uniform_(-0.2, 0.2, generator=g); init[8].uniform_(0, 6.28, generator=g)
+    init[9:12].uniform_(-0.1, 0.1, generator=g)
+    cmd = torch.zeros(4, n)
+    if level == "surface":
+        cmd[:3].uniform_(-0.3, 0.3, generator=g); cmd[3].uniform_(0.3, 0.9, generator=g)
+    elif level == "rate":
+        cmd[:3].uniform_(-0.5, 0.5, generator=g); cmd[3] = 0.7
+    else:
+        cmd[0].uniform_(-0.4, 0.4, generator=g); cmd[1].uniform_(-0.1, 0.15, generator=g); cmd[2] = float("inf"); cmd[3] = 0.6
+    outs = []
+    for pair in (False, True):
+        os.environ["ACB200_ENV_PAIR"] = "1" if pair else "0"
+        try:
+            fleet = acb200.AircraftFleet(n, precision=32)
+            fleet.reset(init.cuda())
+            surf = torch.zeros(4, n, device="cuda")
+            c = cmd.cuda()
+            for _ in range(steps):
+                if level == "surface":
+                    fleet.step_surface(c, dt)
+                elif level == "rate":
+                    fleet.step_rate(c, dt, surfaces_out=surf)
+                else:
+                    fleet.step_attitude(c, dt, surfaces_out=surf)
+            torch.cuda.synchronize()
+            outs.append([t.cpu().numpy().copy() for t in (fleet.state, fleet.pid, fleet.controls, fleet.derived, surf)])
+        finally:
+            os.environ.pop("ACB200_ENV_PAIR", None)
+    for x, y, name in zip(outs[0], outs[1], ("state", "pid", "controls", "derived", "surfaces")):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), f"{level}: {name} differs in {(x != y).sum()} places"
+    assert np.isfinite(outs[1][0]).all() and np.ptp(outs[1][0][3]) > 1.0          # the fleet really flew
