@@ -219,7 +219,7 @@ int acb200_step_waypoint(acb200_ctx* ctx, const acb200_fleet* f, float* pid_oute
 /* ---- rate-tracking environment ---- */
 int acb200_env_reset(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const uint8_t* mask);
 /* action float[n][4] (aileron, elevator, rudder, throttle); may be NULL unless controller is EXTERNAL/RESIDUAL.
- * precision 32, K >= 4 substeps: one launch of the two-aircraft-per-thread kernel on packed FP32 instructions
+ * precision 32: one launch of the two-aircraft-per-thread kernel on packed FP32 instructions
  * (csrc/kernels_pair_f32.cuh) when n and first are even and the buffers 8-byte aligned, else (and for precision 64) of the
  * one-aircraft-per-thread kernel; the two compute the same bits.  Environment: ACB200_ENV_PAIR=0 forces the latter. */
 int acb200_env_step(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg, const float* action);
