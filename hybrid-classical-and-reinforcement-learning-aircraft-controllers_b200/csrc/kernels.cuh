@@ -178,14 +178,12 @@ template <typename T> struct MissionPtrs {
     T acceptance_radius;
 };
 
+// One aircraft's whole guided step (the body of step_guided_kernel; also the cold path of the pair kernel).
 template <typename T, int LEVEL>
-__global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kernel(const __grid_constant__ DynParams<T> P,
-                                                             const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
-                                                             float* __restrict__ pid_outer, const T* __restrict__ cmd,
-                                                             MissionPtrs<T> M, float dt_ctrl, int K, T h,
-                                                             T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out) {
-    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
-    if (i >= f.n) return;
+__device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
+                                                float* __restrict__ pid_outer, const T* __restrict__ cmd, const MissionPtrs<T>& M,
+                                                float dt_ctrl, int K, T h, T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out,
+                                                int64_t i) {
     T s[12], time, hc[3], surf[4], c[4], d[4];
 #pragma unroll
     for (int k = 0; k < 12; ++k) s[k] = ldf(f.state, k, f.n, i);
@@ -241,6 +239,17 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kern
 #pragma unroll
         for (int k = 0; k < 4; ++k) stf(f.derived, k, f.n, i, d[k]);
     }
+}
+
+template <typename T, int LEVEL>
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kernel(const __grid_constant__ DynParams<T> P,
+                                                             const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
+                                                             float* __restrict__ pid_outer, const T* __restrict__ cmd,
+                                                             MissionPtrs<T> M, float dt_ctrl, int K, T h,
+                                                             T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out) {
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.n) return;
+    guided_step_one<T, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i);
 }
 
 // ---- env memory <-> registers ----------------------------------------------------------------------
@@ -574,8 +583,23 @@ cudaError_t Launch<T>::step_guided(const acb200_aircraft_params& ap, const acb20
     const DynParams<T> P = make_dyn_params<T>(ap);
     const CtrlParams<T> C = make_ctrl_params<T>(cp);
     MissionPtrs<T> M{nullptr, 0, 0, nullptr, 0, T(0)};
+    if (m) M = MissionPtrs<T>{(const T*)m->waypoints, m->n_waypoints, m->guidance, m->wp_index, m->loop, (T)m->acceptance_radius};
+#ifdef ACB_PAIR_KERNEL
+    if constexpr (sizeof(T) == 4) {
+        // measured on B200 (profiles/r01g_fleet_probe.json): with the nine PIDs and the guidance run per lane the pair kernel wins
+        // from a few substeps on (HSA level, K = 10: 0.297 -> 0.250 ms per 2^20 aircraft) and loses at K = 1 (0.074 -> 0.088 ms)
+        if (K >= 4 && fleet_pair_ok(f, cmd, surfaces_out, K, pid_outer, hsa_cmd_out, m ? m->wp_index : nullptr)) {
+            if (m)
+                step_guided_pair_kernel<ACB200_LEVEL_WAYPOINT><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K,
+                                                                                                    (float)h, surfaces_out, hsa_cmd_out, f.n / 2);
+            else
+                step_guided_pair_kernel<ACB200_LEVEL_HSA><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K,
+                                                                                               (float)h, surfaces_out, hsa_cmd_out, f.n / 2);
+            return cudaGetLastError();
+        }
+    }
+#endif
     if (m) {
-        M = MissionPtrs<T>{(const T*)m->waypoints, m->n_waypoints, m->guidance, m->wp_index, m->loop, (T)m->acceptance_radius};
         step_guided_kernel<T, ACB200_LEVEL_WAYPOINT><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K, (T)h,
                                                                                        surfaces_out, hsa_cmd_out);
     } else {
@@ -627,6 +651,7 @@ template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, Kerne
     else if (!strcmp(name, "env_step")) fn = (const void*)env_step_kernel<T>;
 #ifdef ACB_PAIR_KERNEL
     else if (!strcmp(name, "env_step_pair") && sizeof(T) == 4) fn = env_step_pair_entry();
+    else if (!strcmp(name, "step_waypoint_pair") && sizeof(T) == 4) fn = (const void*)step_guided_pair_kernel<ACB200_LEVEL_WAYPOINT>;
     else if (!strcmp(name, "step_surface_pair") && sizeof(T) == 4) fn = (const void*)step_fleet_pair_kernel<0>;
     else if (!strcmp(name, "step_cascade_attitude_pair") && sizeof(T) == 4) fn = (const void*)step_fleet_pair_kernel<ACB200_LEVEL_ATTITUDE>;
 #endif

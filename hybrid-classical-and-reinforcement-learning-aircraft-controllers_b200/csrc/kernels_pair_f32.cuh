@@ -337,12 +337,161 @@ step_fleet_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_
     }
 }
 
+// ---- levels 2 and 1 (HSAAgent / MissionPlanner + WaypointAgent on top of the cascade) for aircraft pairs ------------------
+// The guidance and the nine fp32 PIDs run per lane (the one-aircraft code of agents.cuh, one lane at a time), the K
+// substeps packed.  A pair with an aircraft whose mission is complete or completes in this step (the one-aircraft kernel
+// leaves that aircraft untouched) takes the one-aircraft code for both lanes, out of line.
+template <int LEVEL>
+static __device__ __noinline__ void guided_step_one_cold(const DynParams<float>& P, const CtrlParams<float>& C, const FleetPtrs<float>& f,
+                                                         float* pid_outer, const float* cmd, const MissionPtrs<float>& M, float dt_ctrl,
+                                                         int K, float h, float* surfaces_out, float* hsa_cmd_out, int64_t i) {
+    guided_step_one<float, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i);
+}
+
+#ifndef ACB_GUIDED_PAIR_MIN_BLOCKS
+#define ACB_GUIDED_PAIR_MIN_BLOCKS 3
+#endif
+template <int LEVEL>
+__global__ void __launch_bounds__(kBlock, ACB_GUIDED_PAIR_MIN_BLOCKS)
+step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C, FleetPtrs<float> f,
+                        float* __restrict__ pid_outer, const float* __restrict__ cmd, MissionPtrs<float> M, float dt_ctrl, int K,
+                        float h, float* __restrict__ surfaces_out, float* __restrict__ hsa_cmd_out, int64_t pairs) {
+    const int64_t n = f.n;
+    const int64_t pair_idx = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (pair_idx >= pairs) return;
+    const int64_t i = 2 * pair_idx;
+    v2 s2[12], time2;
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s2[k] = ld2(f.state, k, n, i);
+    time2 = ld2(f.state, 12, n, i);
+    int2 idx2 = make_int2(0, 0);
+    if (LEVEL == ACB200_LEVEL_WAYPOINT) {
+        idx2 = *reinterpret_cast<const int2*>(M.wp_index + i);
+        bool leaves = false;
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            const int idx = l ? idx2.y : idx2.x;
+            if (idx >= M.n_waypoints) { leaves = true; continue; }
+            const float dx = M.waypoints[idx * 4 + 0] - lane(s2[0], l), dy = M.waypoints[idx * 4 + 1] - lane(s2[1], l),
+                        dz = M.waypoints[idx * 4 + 2] - lane(s2[2], l);
+            if (Math<float>::norm3(dx, dy, dz) < M.acceptance_radius && idx + 1 >= M.n_waypoints && !M.loop) leaves = true;
+        }
+        if (leaves) {
+            guided_step_one_cold<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i);
+            guided_step_one_cold<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i + 1);
+            return;
+        }
+    }
+    // All of the pair's controller memory is requested at once (8 bytes per field and thread: one memory round trip for both
+    // lanes); the guidance and the nine PIDs then run one lane at a time on their halves.
+    v2 c2[4], pidv[ACB200_PID_FIELDS], outv[9], surf2[4], hc2[3];
+#pragma unroll
+    for (int k = 0; k < ACB200_PID_FIELDS; ++k) pidv[k] = ld2(f.pid, k, n, i);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) outv[k] = ld2(pid_outer, k, n, i);
+    if (LEVEL != ACB200_LEVEL_WAYPOINT) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) hc2[k] = ld2(cmd, k, n, i);
+    }
+#pragma unroll 1
+    for (int l = 0; l < 2; ++l) {
+        const int64_t il = i + l;
+        float sl[12], d[4], hc[3], surf[4], c[4];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) sl[k] = lane(s2[k], l);
+        derived_outputs(sl, d);
+        if (LEVEL == ACB200_LEVEL_WAYPOINT) {
+            int32_t idx = l ? idx2.y : idx2.x;
+            float wp[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
+            // MissionPlanner.update (mission_planner.py:128-171): inside the acceptance radius -> next waypoint
+            if (Math<float>::norm3(wp[0] - sl[0], wp[1] - sl[1], wp[2] - sl[2]) < M.acceptance_radius) {
+                idx += 1;
+                if (idx >= M.n_waypoints && M.loop) idx = 0;
+                M.wp_index[il] = idx;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
+            }
+            waypoint_guidance(C, M.guidance, wp, sl, d, hc);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { if (l) hc2[k].y = hc[k]; else hc2[k].x = hc[k]; }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) hc[k] = lane(hc2[k], l);
+        }
+        PidMem rate[3], ang[3], outer[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            rate[a] = PidMem{lane(pidv[a * 3], l), lane(pidv[a * 3 + 1], l), lane(pidv[a * 3 + 2], l)};
+            ang[a] = PidMem{lane(pidv[9 + a * 3], l), lane(pidv[9 + a * 3 + 1], l), lane(pidv[9 + a * 3 + 2], l)};
+            outer[a] = PidMem{lane(outv[a * 3], l), lane(outv[a * 3 + 1], l), lane(outv[a * 3 + 2], l)};
+        }
+        hsa_agent(C, outer, ang, rate, hc[0], hc[1], hc[2], sl, d, dt_ctrl, surf);
+        clip_controls(surf, c);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float r3[3] = {rate[a].integral, rate[a].error_prev, rate[a].derivative_filtered};
+            const float a3[3] = {ang[a].integral, ang[a].error_prev, ang[a].derivative_filtered};
+            const float o3[3] = {outer[a].integral, outer[a].error_prev, outer[a].derivative_filtered};
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                if (l) { pidv[a * 3 + j].y = r3[j]; pidv[9 + a * 3 + j].y = a3[j]; outv[a * 3 + j].y = o3[j]; }
+                else { pidv[a * 3 + j].x = r3[j]; pidv[9 + a * 3 + j].x = a3[j]; outv[a * 3 + j].x = o3[j]; }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (l) { c2[k].y = c[k]; surf2[k].y = surf[k]; } else { c2[k].x = c[k]; surf2[k].x = surf[k]; }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < ACB200_PID_FIELDS; ++k) *reinterpret_cast<v2*>(f.pid + (int64_t)k * n + i) = pidv[k];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) *reinterpret_cast<v2*>(pid_outer + (int64_t)k * n + i) = outv[k];
+    if (LEVEL == ACB200_LEVEL_WAYPOINT && hsa_cmd_out) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) *reinterpret_cast<v2*>(hsa_cmd_out + (int64_t)k * n + i) = hc2[k];
+    }
+    if (surfaces_out) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) *reinterpret_cast<v2*>(surfaces_out + (int64_t)k * n + i) = surf2[k];
+    }
+    if (f.controls) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) *reinterpret_cast<v2*>(f.controls + (int64_t)k * n + i) = c2[k];
+    }
+    {
+        const float c0[4] = {c2[0].x, c2[1].x, c2[2].x, c2[3].x}, c1[4] = {c2[0].y, c2[1].y, c2[2].y, c2[3].y};
+        backend_step2(P, s2, c0, c1, K, h);
+    }
+    for (int k = 0; k < K; ++k) time2 = P2::add(time2, P2::bc(h));            // t += dt once per substep (:254)
+#pragma unroll
+    for (int k = 0; k < 12; ++k) *reinterpret_cast<v2*>(f.state + (int64_t)k * n + i) = s2[k];
+    *reinterpret_cast<v2*>(f.state + 12 * n + i) = time2;
+    if (f.derived) {
+        v2 d2[4];
+#pragma unroll 1
+        for (int l = 0; l < 2; ++l) {
+            float sl[12], d[4];
+#pragma unroll
+            for (int k = 0; k < 12; ++k) sl[k] = lane(s2[k], l);
+            derived_outputs(sl, d);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { if (l) d2[k].y = d[k]; else d2[k].x = d[k]; }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) *reinterpret_cast<v2*>(f.derived + (int64_t)k * n + i) = d2[k];
+    }
+}
+
 // Whole fleets only (n even, 8-byte aligned fields); otherwise the one-aircraft kernels run.
-static inline bool fleet_pair_ok(const FleetPtrs<float>& f, const void* in, const void* out, int K) {
+static inline bool fleet_pair_ok(const FleetPtrs<float>& f, const void* in, const void* out, int K, const void* x0 = nullptr,
+                                 const void* x1 = nullptr, const void* x2 = nullptr) {
     const char* pair_env = getenv("ACB200_ENV_PAIR");
     if (pair_env && pair_env[0] == '0') return false;
     if (pair_variant(K) < 0 || f.n < 2 || (f.n & 1)) return false;
-    const void* w8[] = {f.state, f.controls, f.derived, f.pid, in, out};
+    const void* w8[] = {f.state, f.controls, f.derived, f.pid, in, out, x0, x1, x2};
     for (const void* p : w8)
         if (p && ((uintptr_t)p & 7)) return false;
     return true;

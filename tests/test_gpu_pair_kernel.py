@@ -165,3 +165,48 @@ def test_fleet_pair_kernels_are_bit_identical_to_the_one_aircraft_kernels(level,
     for x, y, name in zip(outs[0], outs[1], ("state", "pid", "controls", "derived", "surfaces")):
         assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), f"{level}: {name} differs in {(x != y).sum()} places"
     assert np.isfinite(outs[1][0]).all() and np.ptp(outs[1][0][3]) > 1.0          # the fleet really flew
+
+
+@pytest.mark.parametrize("level,dt,loop", [("hsa", 0.01, False), ("waypoint", 0.001, True), ("waypoint", 0.01, False)])
+def test_guided_pair_kernels_are_bit_identical_to_the_one_aircraft_kernels(level, dt, loop):
+    """Levels 2 and 1 (HSA / mission + waypoint guidance on top of the cascade) on aircraft pairs.  The non-looping mission
+    is short enough that aircraft complete it at different steps: pairs with a finished aircraft take the cold path and
+    the finished aircraft must stay untouched."""
+    import acb200
+    n, steps = 2000, 400 if dt == 0.01 else 300
+    g = torch.Generator().manual_seed(8)
+    init = torch.zeros(13, n)
+    init[0].uniform_(-20, 20, generator=g); init[1].uniform_(-20, 20, generator=g); init[2] = -100.0
+    init[3] = 15.0; init[8].uniform_(-0.2, 0.2, generator=g)
+    cmd = torch.zeros(3, n)
+    cmd[0].uniform_(-1.0, 1.0, generator=g); cmd[1].uniform_(13, 18, generator=g); cmd[2].uniform_(80, 120, generator=g)
+    wps = [[25.0, 0.0, -100.0, 15.0], [50.0, 20.0, -100.0, 15.0]]
+    outs = []
+    for pair in (False, True):
+        os.environ["ACB200_ENV_PAIR"] = "1" if pair else "0"
+        try:
+            fleet = acb200.AircraftFleet(n, precision=32)
+            fleet.reset(init.cuda())
+            surf = torch.zeros(4, n, device="cuda")
+            hsa_cmd = torch.zeros(3, n, device="cuda")
+            if level == "waypoint":
+                fleet.set_mission(wps, acceptance_radius=12.0, guidance="PP", loop=loop)
+            c = cmd.cuda()
+            for _ in range(steps):
+                if level == "hsa":
+                    fleet.step_hsa(c, dt, surfaces_out=surf)
+                else:
+                    fleet.step_waypoint(dt, surfaces_out=surf, hsa_cmd_out=hsa_cmd)
+            torch.cuda.synchronize()
+            outs.append([t.cpu().numpy().copy() for t in (fleet.state, fleet.pid, fleet.pid_outer, fleet.controls, fleet.derived,
+                                                           surf, hsa_cmd, fleet.wp_index)])
+        finally:
+            os.environ.pop("ACB200_ENV_PAIR", None)
+    names = ("state", "pid", "pid_outer", "controls", "derived", "surfaces", "hsa_cmd", "wp_index")
+    for x, y, name in zip(outs[0], outs[1], names):
+        assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), f"{level}: {name} differs in {(x != y).sum()} places"
+    assert np.isfinite(outs[1][0]).all()
+    if level == "waypoint" and not loop:
+        done = outs[1][7] >= 2
+        assert 0.2 < done.mean() < 1.0 or done.all()          # some aircraft finished (and at different steps)
+        assert len(np.unique(outs[1][0][12][done])) > 3        # ... they stopped at different times

@@ -1,7 +1,8 @@
 """bench.py --workload c5: BASELINE.json configs[4] -- 2^20 aircraft per GPU flying a looping square mission
 (300 m side at 100 m altitude, 15 m/s, pure-pursuit guidance) through the full 5-level cascade
 (waypoint -> HSA/TECS -> attitude -> rate -> surface), dt = dt_physics = 0.01 (K = 1: ONE RK4 substep per control step),
-initial states jittered +-20 m / +-10 deg heading by global id.  One step = one launch of step_guided_kernel<float, 1>."""
+initial states jittered +-20 m / +-10 deg heading by global id.  One step = one launch of step_guided_kernel<float, 1>
+(at K = 1 the one-aircraft kernel is the faster one; the pair kernel takes over from K = 4)."""
 from __future__ import annotations
 
 import json

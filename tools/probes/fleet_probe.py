@@ -13,7 +13,8 @@ for pair in (0, 1):
     g = torch.Generator(device="cuda").manual_seed(1)
     surf = torch.empty(4, n, device="cuda").uniform_(-0.2, 0.2, generator=g); surf[3] = 0.6
     att = torch.zeros(4, n, device="cuda"); att[0].uniform_(-0.3, 0.3, generator=g); att[2] = float("inf"); att[3] = 0.6
-    for name, fn in (("surface_K10", lambda: fleet.step_surface(surf, 0.01)), ("attitude_K10", lambda: fleet.step_attitude(att, 0.01)),
+    hsa = torch.zeros(3, n, device="cuda"); hsa[0].uniform_(-1, 1, generator=g); hsa[1] = 15.0; hsa[2] = 100.0
+    for name, fn in (("hsa_K10", lambda: fleet.step_hsa(hsa, 0.01)), ("hsa_K1", lambda: fleet.step_hsa(hsa, 0.001)), ("surface_K10", lambda: fleet.step_surface(surf, 0.01)), ("attitude_K10", lambda: fleet.step_attitude(att, 0.01)),
                      ("surface_K1", lambda: fleet.step_surface(surf, 0.001)), ("attitude_K1", lambda: fleet.step_attitude(att, 0.001))):
         fleet.reset()
         for _ in range(5):
