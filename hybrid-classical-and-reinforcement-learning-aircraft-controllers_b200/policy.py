@@ -131,6 +131,27 @@ class LearnedPolicyB200:
 
     __call__ = forward
 
+    def forward_range(self, obs: torch.Tensor, episode_start, first: int, count: int, out: Optional[torch.Tensor] = None):
+        """``forward`` for aircraft [first, first + count) only (``first`` a multiple of 256: whole tile pairs of the
+        recurrent-state layout); obs / flags / out are the WHOLE-fleet tensors.  Lets a caller pipeline host copies of one
+        part of the fleet behind the forward of another (``step_host_pipelined``).  Runs on torch's current stream."""
+        if first % 256 or first < 0 or count < 0 or first + count > self.n:
+            raise ValueError("first must be a multiple of 256 and the range must lie inside the fleet")
+        if isinstance(episode_start, (tuple, list)):
+            es, es_b = self._flags(episode_start[0]), self._flags(episode_start[1])
+        else:
+            es, es_b = self._flags(episode_start), None
+        out = self.action if out is None else out
+        self.ctx.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        tile = first // 128
+        self.ctx.check(self.lib.acb200_policy_forward(
+            self.ctx.handle, self.handle, count, obs.data_ptr() + first * OBS_DIM * 4,
+            es.data_ptr() + first if es is not None else None, es_b.data_ptr() + first if es_b is not None else None,
+            self.h_state.data_ptr() + tile * HIDDEN * 128 * 2 if self.recurrent else None,
+            self.c_state.data_ptr() + tile * HIDDEN * 128 * 4 if self.recurrent else None,
+            out.data_ptr() + first * ACT_DIM * 4))
+        return out
+
     def predict(self, observation, state=None, episode_start=None, deterministic: bool = True):
         """stable-baselines3's ``predict`` signature over numpy arrays (learned_rate_agent.py:220-227): returns
         ``(actions, state)`` where ``state`` is ``(h, c)`` with shapes (1, n, 256), as sb3-contrib hands them around."""
@@ -201,3 +222,45 @@ def random_policy_state_dict(kind: str = "lstm", seed: int = 0) -> dict:
         raise ValueError(f"unknown policy kind {kind!r}")
     torch.random.set_rng_state(g)
     return sd
+
+
+def step_host_pipelined(env, pol: "LearnedPolicyB200", obs_host, reward_host, terminated_host, truncated_host, obs_dev,
+                        chunks: int = 4, streams=None):
+    """One closed-loop step (policy forward + env step) with the observation coming from and the results going back to
+    (pinned) HOST tensors, pipelined over ``chunks`` parts of the fleet on three streams: while part k runs the policy and the
+    env kernels, part k+1's observations are on their way in and part k-1's results on their way out.  Returns when the
+    host tensors are complete.  Same results as ``obs_dev.copy_(obs_host); env.step(pol(obs_dev, flags))`` + copies out."""
+    n = env.n
+    per = ((n + chunks - 1) // chunks + 255) // 256 * 256
+    dev = env.device
+    if streams is None:
+        streams = getattr(env, "_pipe_streams", None)
+        if streams is None:
+            streams = env._pipe_streams = tuple(torch.cuda.Stream(dev) for _ in range(3))
+    s_in, s_run, s_out = streams
+    flags = (env.terminated, env.truncated)
+    start = torch.cuda.current_stream(dev).record_event()
+    for s_ in streams:
+        s_.wait_event(start)
+    reward = env.reward
+    for lo in range(0, n, per):
+        cnt = min(per, n - lo)
+        with torch.cuda.stream(s_in):
+            obs_dev[lo:lo + cnt].copy_(obs_host[lo:lo + cnt], non_blocking=True)
+            ready = s_in.record_event()
+        with torch.cuda.stream(s_run):
+            s_run.wait_event(ready)
+            pol.forward_range(obs_dev, flags, lo, cnt)
+            env._bind_stream()
+            env.ctx.check(env.ctx.lib.acb200_env_step_range(env.ctx.handle, C.byref(env.c), C.byref(env.cfg),
+                                                            C.c_void_p(pol.action.data_ptr()), lo, cnt))
+            done = s_run.record_event()
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(done)
+            obs_host[lo:lo + cnt].copy_(env.obs[lo:lo + cnt], non_blocking=True)
+            reward_host[lo:lo + cnt].copy_(reward[lo:lo + cnt], non_blocking=True)
+            terminated_host[lo:lo + cnt].copy_(env.terminated[lo:lo + cnt], non_blocking=True)
+            truncated_host[lo:lo + cnt].copy_(env.truncated[lo:lo + cnt], non_blocking=True)
+    s_out.synchronize()
+    torch.cuda.current_stream(dev).wait_stream(s_run)
+    return obs_host, reward_host, terminated_host, truncated_host

@@ -169,3 +169,39 @@ def test_policy_env_closed_loop_vs_oracle():
         assert torch.isfinite(env.obs).all()
     assert worst < F32_TOL, worst
     assert restarts >= n          # 1 s episodes: everyone restarted at least once, the recurrent state was re-zeroed
+
+
+def test_pipelined_host_step_equals_the_plain_closed_loop():
+    """policy.step_host_pipelined (H2D / policy + env / D2H over parts of the fleet on three streams) against the plain
+    sequence on one stream: observations, rewards, flags and the recurrent state bit for bit over 12 closed-loop steps."""
+    import acb200
+    from acb200.policy import random_policy_state_dict, step_host_pipelined
+    n = 3000                                     # ragged: chunks of 768 aircraft, a 696-aircraft tail
+    outs = []
+    for piped in (False, True):
+        env = acb200.BatchedRateControlEnv(n, difficulty="medium", controller="external", precision=32, seed=7,
+                                           episode_length=0.2)
+        pol = acb200.LearnedPolicyB200(random_policy_state_dict("lstm", 0), kind="lstm", n=n, ctx=env.ctx)
+        env.reset()
+        pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
+        obs_h, rew_h = pin((n, 18), torch.float32), pin((n,), torch.float32)
+        term_h, trunc_h = pin((n,), torch.uint8), pin((n,), torch.uint8)
+        obs_h.copy_(env.obs); obs_d = torch.empty_like(env.obs)
+        hist = []
+        for t in range(12):
+            if piped:
+                step_host_pipelined(env, pol, obs_h, rew_h, term_h, trunc_h, obs_d, chunks=4)
+            else:
+                obs_d.copy_(obs_h, non_blocking=True)
+                env.step(pol(obs_d, (env.terminated, env.truncated)))
+                obs_h.copy_(env.obs); rew_h.copy_(env.reward); term_h.copy_(env.terminated); trunc_h.copy_(env.truncated)
+                torch.cuda.synchronize()
+            hist.append([x.clone() for x in (obs_h, rew_h, term_h, trunc_h)])
+        torch.cuda.synchronize()
+        outs.append((hist, pol.h_state.cpu().clone(), pol.c_state.cpu().clone(), env.state.cpu().clone()))
+    for a, b in zip(outs[0][0], outs[1][0]):
+        for x, y in zip(a, b):
+            assert torch.equal(x.view(torch.uint8), y.view(torch.uint8))
+    assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2].view(torch.int32), outs[1][2].view(torch.int32))
+    assert torch.equal(outs[0][3].view(torch.int32), outs[1][3].view(torch.int32))
+    assert sum(int(h[2].sum() + h[3].sum()) for h in outs[1][0]) >= n          # episodes ended and restarted on the way

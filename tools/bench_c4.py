@@ -85,7 +85,13 @@ def run_gpu(args, ROOT, ClockSampler):
     obs_d = torch.empty_like(env.obs)
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
 
+    from acb200.policy import step_host_pipelined
+    e2e_chunks = int(os.environ.get("ACB200_C4_E2E_CHUNKS", "4"))
+
     def step_host():
+        if e2e_chunks > 1:      # the public host-buffer step: H2D / policy + env / D2H pipelined over parts of the fleet
+            step_host_pipelined(env, pol, obs_h, rew_h, term_h, trunc_h, obs_d, chunks=e2e_chunks)
+            return
         obs_d.copy_(obs_h, non_blocking=True)
         env.step(pol(obs_d, flags))
         obs_h.copy_(env.obs, non_blocking=True); rew_h.copy_(env.reward_f32 if hasattr(env, "reward_f32") else env.reward, non_blocking=True)
