@@ -18,7 +18,10 @@ namespace acbp {
 
 constexpr int kTile = 128;               // aircraft per CTA == UMMA M == tensor-memory lanes
 constexpr int kMaxLayers = 8;
-constexpr int kStages = 3;               // weight ring depth
+#ifndef ACB_POLICY_STAGES
+#define ACB_POLICY_STAGES 3
+#endif
+constexpr int kStages = ACB_POLICY_STAGES;   // weight ring depth
 constexpr uint32_t kStageBytes = 16384;
 constexpr uint32_t kXBytes = 98304;      // activation buffer X: up to K = 384 (features 128 | h 256)
 constexpr uint32_t kYBytes = 65536;      // activation buffer Y: up to K = 256
