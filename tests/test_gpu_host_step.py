@@ -1,13 +1,15 @@
-"""acb200_env_step_host (host buffers, chunked three-stream pipeline) must give exactly what acb200_env_step gives."""
+"""acb200_env_step_host (host buffers, chunked three-stream pipeline) must give exactly what acb200_env_step gives, with
+pinned and with pageable result buffers."""
 import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("precision,controller,n,chunks", [(32, "attitude_pid", 100_003, 0), (64, "external", 5_001, 7),
-                                                          (32, "residual", 777, 3), (32, "rate_pid", 64, 0)])
-def test_host_step_equals_device_step(precision, controller, n, chunks):
+@pytest.mark.parametrize("precision,controller,n,chunks,pinned", [(32, "attitude_pid", 100_003, 0, True), (64, "external", 5_001, 7, True),
+                                                                 (32, "residual", 777, 3, True), (32, "rate_pid", 64, 0, True),
+                                                                 (32, "attitude_pid", 40_000, 0, False)])
+def test_host_step_equals_device_step(precision, controller, n, chunks, pinned):
     import torch
     import acb200
     rng = np.random.default_rng(1)
@@ -23,7 +25,8 @@ def test_host_step_equals_device_step(precision, controller, n, chunks):
     a, b = envs
     b.ctx.check(b.ctx.lib.acb200_set_host_chunks(b.ctx.handle, chunks))
     pin = lambda shape, d: torch.empty(shape, dtype=d, pin_memory=True)
-    obs_h, rew_h, term_h, trunc_h = pin((n, 18), torch.float32), pin((n,), torch.float32), pin((n,), torch.uint8), pin((n,), torch.uint8)
+    res = pin if pinned else (lambda shape, d: torch.full(shape, 77, dtype=d))
+    obs_h, rew_h, term_h, trunc_h = res((n, 18), torch.float32), res((n,), torch.float32), res((n,), torch.uint8), res((n,), torch.uint8)
     att_h = pin((4, n), dt)
     act_h = pin((n, 4), torch.float32)
     needs_action = controller in ("external", "residual")
