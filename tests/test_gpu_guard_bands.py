@@ -132,3 +132,29 @@ def test_fleet_kernels_stay_inside_their_buffers(level, n, dt):
             fleet.step_waypoint(dt, surfaces_out=surf)
     _bands_intact(raws)
     assert torch.isfinite(fleet.state).all()
+
+
+@pytest.mark.parametrize("kind,n", [("lstm", 300), ("lstm", 129), ("mlp", 77)])
+def test_policy_forward_stays_inside_its_buffers(kind, n):
+    """The tensor-core policy forward works on 128-aircraft tiles (TMA loads, tensor-memory epilogue): a ragged last tile
+    must neither write past the action rows nor past the recurrent state of the aircraft that exist."""
+    import acb200
+    from acb200.policy import random_policy_state_dict
+    pol = acb200.LearnedPolicyB200(random_policy_state_dict(kind, seed=0), kind=kind, n=n)
+    raws = {}
+    for name in ("h_state", "c_state", "action"):
+        t = getattr(pol, name, None)
+        if t is None:
+            continue
+        view, raw = _rehome(t)
+        setattr(pol, name, view)
+        raws[name] = raw
+    g = torch.Generator().manual_seed(2)
+    obs, raws["obs"] = _rehome(torch.randn(n, 18, generator=g).cuda())
+    out, raws["out"] = _rehome(torch.zeros(n, 4, device="cuda"))
+    for t in range(3):
+        start = (torch.rand(n, generator=g) < (1.0 if t == 0 else 0.2)).to(torch.uint8).cuda()
+        pol.forward(obs, start, out=out)
+        pol.forward(obs, start)                       # into the policy's own action buffer
+    _bands_intact(raws)
+    assert torch.isfinite(out).all() and float(out.abs().max()) <= 1.0 + 1e-6
