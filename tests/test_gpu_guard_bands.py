@@ -158,3 +158,40 @@ def test_policy_forward_stays_inside_its_buffers(kind, n):
         pol.forward(obs, start)                       # into the policy's own action buffer
     _bands_intact(raws)
     assert torch.isfinite(out).all() and float(out.abs().max()) <= 1.0 + 1e-6
+
+
+@pytest.mark.parametrize("precision,n", [(32, 1001), (64, 333)])
+def test_sensor_update_stays_inside_its_buffers(precision, n):
+    import acb200
+    fleet = acb200.AircraftFleet(n, precision=precision)
+    cfg = {"enabled": True, "imu_gyro_stddev": 0.02, "gps_position_stddev": 2.5, "attitude_stddev": 0.05, "seed": 11}
+    sensor = acb200.NoisySensorB200(cfg, n, precision=precision)
+    raws = {}
+    for name in ("bias", "measured_state", "measured_derived"):
+        view, raw = _rehome(getattr(sensor, name))
+        setattr(sensor, name, view)
+        raws[name] = raw
+    for _ in range(20):
+        sensor.update(fleet)
+    sensor.reset((torch.arange(n) % 2 == 0).to(torch.uint8))
+    sensor.update(fleet)
+    _bands_intact(raws)
+    assert torch.isfinite(sensor.measured_state).all()
+
+
+@pytest.mark.parametrize("T,n", [(7, 1001), (33, 130)])
+def test_gae_stays_inside_its_buffers(T, n):
+    import acb200
+    buf = acb200.RolloutBufferB200(T, n)
+    raws = {}
+    for name in ("rewards", "values", "episode_starts", "advantages", "returns"):
+        view, raw = _rehome(getattr(buf, name))
+        setattr(buf, name, view)
+        raws[name] = raw
+    g = torch.Generator().manual_seed(4)
+    buf.rewards.copy_(torch.randn(T, n, generator=g)); buf.values.copy_(torch.randn(T, n, generator=g))
+    buf.episode_starts.copy_((torch.rand(T, n, generator=g) < 0.1).to(torch.uint8))
+    buf.pos, buf.full = T, True
+    buf.compute_returns_and_advantage(torch.randn(n, generator=g).cuda(), (torch.rand(n, generator=g) < 0.1).cuda())
+    _bands_intact(raws)
+    assert torch.isfinite(buf.advantages).all() and torch.isfinite(buf.returns).all()
