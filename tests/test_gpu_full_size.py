@@ -113,3 +113,39 @@ def test_field_offsets_beyond_4_GiB_are_addressed_correctly():
         for name in ("state", "pid", "controls", "derived"):
             assert torch.equal(getattr(f, name), getattr(big, name)[:, lo:lo + cnt]), (name, lo)
     assert torch.isfinite(big.state).all()
+
+
+@pytest.mark.parametrize("dt,steps", [(0.01, 260), (0.001, 200)])
+def test_slices_of_the_full_mission_fleet_equal_small_fleets(dt, steps):
+    """C5's 2^20 aircraft flying the waypoint mission through the five-level cascade (K = 10: pair kernel, K = 1: one-aircraft
+    kernel): slices against small fleets with the same initial states, waypoint indices included."""
+    import acb200
+    wps = [[25.0, 0.0, -100.0, 15.0], [50.0, 20.0, -100.0, 15.0], [20.0, 40.0, -100.0, 15.0]]
+
+    def build(cnt, lo):
+        f = acb200.AircraftFleet(cnt, precision=32)
+        ids = torch.arange(lo, lo + cnt, device="cuda")
+        init = torch.zeros(13, cnt, device="cuda")
+        init[0] = ((ids % 41).float() - 20.0)
+        init[1] = ((ids % 37).float() - 18.0)
+        init[2] = -100.0
+        init[3] = 15.0
+        init[8] = ((ids % 21).float() - 10.0) * 0.0175
+        f.reset(init)
+        f.set_mission(wps, acceptance_radius=12.0, guidance="PP", loop=True)
+        return f
+
+    big = build(N, 0)
+    slices = [(0, 2048), (N // 2 - 128, 2050), (N - 1024, 1024)]
+    small = [build(cnt, lo) for lo, cnt in slices]
+    for _ in range(steps):
+        big.step_waypoint(dt)
+        for f in small:
+            f.step_waypoint(dt)
+    for (lo, cnt), f in zip(slices, small):
+        for name in ("state", "pid", "pid_outer", "controls", "derived"):
+            assert torch.equal(getattr(f, name), getattr(big, name)[:, lo:lo + cnt]), (name, lo)
+        assert torch.equal(f.wp_index, big.wp_index[lo:lo + cnt]), lo
+    assert torch.isfinite(big.state).all()
+    if dt == 0.01:
+        assert int(big.wp_index.max()) >= 1 and len(torch.unique(big.wp_index)) >= 2        # the fleet is spread over the legs
