@@ -14,6 +14,7 @@ template <int MODE> __global__ void __launch_bounds__(256) probe(float* out, flo
     for (int i = 0; i < 8; ++i) x[i] = make_float2(tid * 1e-9f + i * 0.01f, tid * 2e-9f - i * 0.01f);
     const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
     for (int it = 0; it < ITERS; ++it) {
+        const float2 y2 = make_float2(x[7].x * 0.5f, x[6].y * 0.5f);   // a per-thread register pair that changes every pass (mode 13)
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             if (MODE == 0) {          // 16 scalar FFMA
@@ -48,6 +49,15 @@ template <int MODE> __global__ void __launch_bounds__(256) probe(float* out, flo
                 x[i] = __ffma2_rn(x[(i + 3) & 7], x[(i + 5) & 7], x[i]);
                 x[i].x = fminf(x[i].x, 3.0e38f);
                 if (i % 4 == 0) asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(x[i].y));
+            } else if (MODE == 11) {  // 8 FFMA2, three register pairs, neighbours (another register-bank pattern than mode 8)
+                x[i] = __ffma2_rn(x[(i + 1) & 7], x[(i + 2) & 7], x[i]);
+            } else if (MODE == 12) {  // 16 FFMA, three registers of mixed parity
+                x[i].x = fmaf(x[(i + 3) & 7].x, x[(i + 5) & 7].y, x[i].x);
+                x[i].y = fmaf(x[(i + 3) & 7].y, x[(i + 5) & 7].x, x[i].y);
+            } else if (MODE == 13) {  // 8 FFMA2, three register pairs, the multiplier shared by the eight (operand reuse cache)
+                x[i] = __ffma2_rn(x[(i + 3) & 7], y2, x[i]);
+            } else if (MODE == 14) {  // 8 FFMA2, two register pairs + the accumulator itself (x = x * y + x')
+                x[i] = __ffma2_rn(x[i], x[(i + 3) & 7], x[i]);
             } else if (MODE == 7) {   // the same mix, scalar
                 x[i].x = fminf(fmaf(x[i].x, a, b), 3.0e38f);
                 x[i].y = fmaf(x[i].y, a, b);
@@ -86,6 +96,8 @@ int main() {
     // three-register-operand forms, and the substep-like mix at the pair kernel's occupancy (12 warps per SM)
     const double r8 = run<8>(sms, d), r9 = run<9>(sms, d), r10 = run<10>(sms, d);
     const double m12 = run<6>(sms, d, 3, 128), m12r = run<10>(sms, d, 3, 128), m16 = run<6>(sms, d, 4, 128), m24s = run<7>(sms, d, 6, 128);
+    printf("{\"register_patterns\": {\"ffma2_neighbours\": %.4g, \"ffma_mixed_parity\": %.4g, \"ffma2_shared_multiplier\": %.4g, "
+           "\"ffma2_two_pairs\": %.4g}}\n", run<11>(sms, d), run<12>(sms, d), run<13>(sms, d), run<14>(sms, d));
     printf("{\"three_reg\": {\"ffma2\": %.4g, \"ffma\": %.4g, \"mix_ffma2\": %.4g}, \"occupancy\": {\"mix_ffma2_12warps\": %.4g, "
            "\"mix_ffma2_3reg_12warps\": %.4g, \"mix_ffma2_16warps\": %.4g, \"mix_ffma_24warps\": %.4g}}\n", r8, r9, r10, m12, m12r, m16, m24s);
     printf("{\"sms\": %d, \"fma_lane_ops_per_s\": {\"ffma\": %.4g, \"ffma2\": %.4g, \"ffma2+fmnmx\": %.4g, \"ffma+fmnmx\": %.4g, "
