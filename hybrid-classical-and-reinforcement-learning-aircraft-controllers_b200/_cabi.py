@@ -115,6 +115,8 @@ SYMBOLS = [
     "acb200_gae",
     "acb200_env_step_range", "acb200_telemetry_record",
     "acb200_default_sensor_config", "acb200_sensor_update", "acb200_sensor_reset",
+    "acb200_validate_aircraft_params", "acb200_get_aircraft_params", "acb200_get_controller_params",
+    "acb200_set_param_groups", "acb200_env_gather_done",
 ]
 
 _lib = None
@@ -142,6 +144,11 @@ def load() -> C.CDLL:
     L.acb200_default_controller_params.argtypes = [P(ControllerParamsC)]; L.acb200_default_controller_params.restype = None
     L.acb200_set_aircraft_params.argtypes = [vp, P(AircraftParamsC)]
     L.acb200_set_controller_params.argtypes = [vp, P(ControllerParamsC)]
+    L.acb200_validate_aircraft_params.argtypes = [vp, P(AircraftParamsC)]
+    L.acb200_get_aircraft_params.argtypes = [vp, P(AircraftParamsC)]
+    L.acb200_get_controller_params.argtypes = [vp, P(ControllerParamsC)]
+    L.acb200_set_param_groups.argtypes = [vp, vp, P(i64), C.c_int32]
+    L.acb200_env_gather_done.argtypes = [vp, P(EnvC), i64, vp, vp, vp, vp]
     L.acb200_fleet_reset.argtypes = [vp, P(FleetC), vp, vp]
     L.acb200_step_surface.argtypes = [vp, P(FleetC), vp, dbl, dbl]
     L.acb200_step_cascade.argtypes = [vp, P(FleetC), i32, vp, dbl, dbl, dbl, vp]

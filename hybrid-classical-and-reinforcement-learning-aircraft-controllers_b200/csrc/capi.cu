@@ -27,15 +27,15 @@ int cuda_fail(acb200_ctx* ctx, cudaError_t e, const char* where) {
 
 // K = max(1, int(dt/dt_physics)), h = dt/K (simulation_backend.py:95-96); dt range check
 // (simplified_6dof.py:241-245) applied to the substep the physics actually sees.
-int substeps(acb200_ctx* ctx, double dt, double dt_physics, int* K, double* h) {
+int substeps(acb200_ctx* ctx, double dt, double dt_physics, int* K, double* h, const acb200_aircraft_params* ap = nullptr) {
     if (!(dt_physics > 0.0) || !(dt == dt)) return fail(ctx, ACB200_EVALUE, "Invalid timestep");
+    const acb200_aircraft_params& a = ap ? *ap : ctx->aircraft;
     int k = (int)(dt / dt_physics);
     if (k < 1) k = 1;
     const double hh = dt / k;
-    if (hh <= ctx->aircraft.min_timestep || hh > ctx->aircraft.max_timestep || !(hh == hh)) {
+    if (hh <= a.min_timestep || hh > a.max_timestep || !(hh == hh)) {
         char buf[160];
-        snprintf(buf, sizeof buf, "Invalid timestep dt=%.6fs, must be in (%g, %g]", hh, ctx->aircraft.min_timestep,
-                 ctx->aircraft.max_timestep);
+        snprintf(buf, sizeof buf, "Invalid timestep dt=%.6fs, must be in (%g, %g]", hh, a.min_timestep, a.max_timestep);
         return fail(ctx, ACB200_EVALUE, buf);
     }
     *K = k;
@@ -111,6 +111,7 @@ void acb200_destroy(acb200_ctx* ctx) {
         if (ctx->pipe[s]) cudaStreamDestroy(ctx->pipe[s]);
     }
     if (ctx->fork) cudaEventDestroy(ctx->fork);
+    if (ctx->scratch_i32) cudaFree(ctx->scratch_i32);
     delete ctx;
 }
 
@@ -190,7 +191,7 @@ void acb200_default_controller_params(acb200_controller_params* c) {
 }
 
 // AircraftParams.__post_init__, simplified_6dof.py:119-143
-int acb200_set_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p) {
+int acb200_validate_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p) {
     if (!ctx || !p) return ACB200_ENULL;
     if (!(p->mass > 0)) return fail(ctx, ACB200_EVALUE, "Mass must be positive");
     if (!(p->inertia_xx > 0) || !(p->inertia_yy > 0) || !(p->inertia_zz > 0))
@@ -201,7 +202,42 @@ int acb200_set_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p)
     if (!(p->air_density > 0 && p->air_density < 10)) return fail(ctx, ACB200_EVALUE, "Invalid air density");
     if (!(p->gravity > 0 && p->gravity < 20)) return fail(ctx, ACB200_EVALUE, "Invalid gravity");
     if (p->max_thrust < 0) return fail(ctx, ACB200_EVALUE, "Max thrust cannot be negative");
+    return ACB200_OK;
+}
+
+int acb200_set_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p) {
+    const int rc = acb200_validate_aircraft_params(ctx, p);
+    if (rc) return rc;
     ctx->aircraft = *p;
+    return ACB200_OK;
+}
+
+int acb200_get_aircraft_params(const acb200_ctx* ctx, acb200_aircraft_params* out) {
+    if (!ctx || !out) return ACB200_ENULL;
+    *out = ctx->aircraft;
+    return ACB200_OK;
+}
+
+int acb200_get_controller_params(const acb200_ctx* ctx, acb200_controller_params* out) {
+    if (!ctx || !out) return ACB200_ENULL;
+    *out = ctx->controller;
+    return ACB200_OK;
+}
+
+int acb200_set_param_groups(acb200_ctx* ctx, const acb200_aircraft_params* params, const int64_t* bounds, int32_t n_groups) {
+    if (!ctx) return ACB200_ENULL;
+    if (n_groups < 0) return fail(ctx, ACB200_EVALUE, "n_groups < 0");
+    if (n_groups == 0) { ctx->groups.clear(); ctx->group_bounds.clear(); return ACB200_OK; }
+    if (!params || !bounds) return fail(ctx, ACB200_ENULL, "params / bounds is NULL");
+    if (bounds[0] != 0) return fail(ctx, ACB200_EVALUE, "bounds must rise from 0 to n in multiples of 128");
+    for (int g = 0; g < n_groups; ++g) {
+        if (bounds[g + 1] < bounds[g] || (g + 1 < n_groups && bounds[g + 1] % 128))
+            return fail(ctx, ACB200_EVALUE, "bounds must rise from 0 to n in multiples of 128");
+        const int rc = acb200_validate_aircraft_params(ctx, &params[g]);
+        if (rc) return rc;
+    }
+    ctx->groups.assign(params, params + n_groups);
+    ctx->group_bounds.assign(bounds, bounds + n_groups + 1);
     return ACB200_OK;
 }
 
@@ -214,9 +250,9 @@ int acb200_set_controller_params(acb200_ctx* ctx, const acb200_controller_params
 // The throughput (fp32) build evaluates atan on |tan(alpha)| <= 1 and divides by cos(max_pitch) (physics_f32.cuh): parameter
 // sets outside that range are refused there instead of being integrated inaccurately; the parity build takes any value the
 // reference takes.
-static int check_f32_range(acb200_ctx* ctx, int precision) {
+static int check_f32_range(acb200_ctx* ctx, int precision, const acb200_aircraft_params* ap = nullptr) {
     if (precision != 32) return ACB200_OK;
-    const acb200_aircraft_params& a = ctx->aircraft;
+    const acb200_aircraft_params& a = ap ? *ap : ctx->aircraft;
     if (!(a.max_alpha > 0.0 && a.max_alpha <= 45.0))
         return fail(ctx, ACB200_EVALUE, "precision 32 needs 0 < max_alpha <= 45 degrees (use precision 64 beyond)");
     if (!(a.max_pitch_angle > 0.0 && a.max_pitch_angle <= 89.0))
@@ -327,18 +363,31 @@ static int env_step_impl(acb200_ctx* ctx, const acb200_env* env, const acb200_en
     if (!action && (cfg->controller == ACB200_CTRL_EXTERNAL || cfg->controller == ACB200_CTRL_RESIDUAL))
         return fail(ctx, ACB200_ENULL, "action is NULL");
     if (action && ((uintptr_t)action & 15)) return fail(ctx, ACB200_EVALUE, "action must be 16-byte aligned");
-    int K; double h;
-    if ((rc = substeps(ctx, cfg->dt, cfg->dt_physics, &K, &h))) return rc;
-    if ((rc = check_f32_range(ctx, env->fleet.precision))) return rc;
     cudaSetDevice(ctx->device);
     if (count < 0) count = env->fleet.n;
     const cudaStream_t st = own_stream ? stream : ctx->stream;
-    const cudaError_t e =
-        (env->fleet.precision == 64)
-            ? Launch<double>::env_step(ctx->aircraft, ctx->controller, typed<double>(*env, reward_f32), *cfg, K, h, action, first, count, st)
-            : Launch<float>::env_step(ctx->aircraft, ctx->controller, typed<float>(*env, reward_f32), *cfg, K, h, action, first, count, st);
-    ctx->launches += 1;
-    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step");
+    auto launch = [&](const acb200_aircraft_params& ap, int64_t lo, int64_t cnt) -> int {
+        int K; double h;
+        int r = substeps(ctx, cfg->dt, cfg->dt_physics, &K, &h, &ap);
+        if (r) return r;
+        if ((r = check_f32_range(ctx, env->fleet.precision, &ap))) return r;
+        const cudaError_t e =
+            (env->fleet.precision == 64)
+                ? Launch<double>::env_step(ap, ctx->controller, typed<double>(*env, reward_f32), *cfg, K, h, action, lo, cnt, st)
+                : Launch<float>::env_step(ap, ctx->controller, typed<float>(*env, reward_f32), *cfg, K, h, action, lo, cnt, st);
+        ctx->launches += 1;
+        return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step");
+    };
+    if (ctx->groups.empty()) return launch(ctx->aircraft, first, count);
+    // parameter groups: one launch per group the range touches, that group's parameters in the constant bank
+    if (ctx->group_bounds.back() != env->fleet.n) return fail(ctx, ACB200_EVALUE, "parameter groups describe a fleet of another size");
+    for (size_t g = 0; g < ctx->groups.size(); ++g) {
+        const int64_t lo = first > ctx->group_bounds[g] ? first : ctx->group_bounds[g];
+        const int64_t hi = first + count < ctx->group_bounds[g + 1] ? first + count : ctx->group_bounds[g + 1];
+        if (hi <= lo) continue;
+        if ((rc = launch(ctx->groups[g], lo, hi - lo))) return rc;
+    }
+    return ACB200_OK;
 }
 
 int acb200_env_step(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action) {
@@ -365,8 +414,10 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
                          const void* att_cmd_host, float* action_dev, float* obs_host, float* reward_host,
                          uint8_t* terminated_host, uint8_t* truncated_host) {
     if (!ctx || !env) return ACB200_ENULL;
-    if (!action_dev || !obs_host || !reward_host || !terminated_host || !truncated_host)
-        return fail(ctx, ACB200_ENULL, "a host/scratch buffer is NULL");
+    // every OUTPUT is optional: a caller whose controller runs in the kernel (C3) needs reward + flags = 6 B per aircraft,
+    // not the 78 B with the (n, 18) float32 observation the reference's step returns
+    if (!action_dev && (action_host || reward_host))
+        return fail(ctx, ACB200_ENULL, "action_dev (device scratch of n*5 floats) is NULL");
     int rc = check_env(ctx, env, cfg);
     if (rc) return rc;
     if (att_cmd_host && !env->att_cmd) return fail(ctx, ACB200_ENULL, "env.att_cmd is NULL");
@@ -387,7 +438,7 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
     if (chunks > 64) chunks = 64;
     if (chunks < 1) chunks = 1;
     int64_t per = ((n + chunks - 1) / chunks + 127) / 128 * 128;
-    float* reward_dev = action_dev + n * 4;
+    float* reward_dev = reward_host ? action_dev + n * 4 : nullptr;
     const size_t rsz = env->fleet.precision == 64 ? 8 : 4;
     // the worker streams start after whatever is queued on the context's stream
     e = cudaEventRecord(ctx->fork, ctx->stream);
@@ -415,9 +466,11 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
         }
         rc = env_step_impl(ctx, env, cfg, action_host ? action_dev : nullptr, reward_dev, first, count, st, true);
         if (rc) return rc;
-        e = cudaMemcpyAsync(obs_host + first * ACB200_OBS_DIM, env->obs + first * ACB200_OBS_DIM,
-                            (size_t)count * ACB200_OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "D2H obs");
+        if (obs_host) {
+            e = cudaMemcpyAsync(obs_host + first * ACB200_OBS_DIM, env->obs + first * ACB200_OBS_DIM,
+                                (size_t)count * ACB200_OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st);
+            if (e != cudaSuccess) return cuda_fail(ctx, e, "D2H obs");
+        }
     }
     // join: the context's stream continues after every worker.  Reward and the two flag arrays (6 of the 78 bytes per
     // aircraft) leave in three whole-fleet copies behind the last chunk instead of three small ones per chunk: a copy
@@ -426,9 +479,12 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
         e = cudaEventRecord(ctx->pipe_done[s], ctx->pipe[s]);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->pipe_done[s], 0);
     }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(reward_host, reward_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(terminated_host, env->terminated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(truncated_host, env->truncated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && reward_host)
+        e = cudaMemcpyAsync(reward_host, reward_dev, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && terminated_host)
+        e = cudaMemcpyAsync(terminated_host, env->terminated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && truncated_host)
+        e = cudaMemcpyAsync(truncated_host, env->truncated, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step_host");
 }

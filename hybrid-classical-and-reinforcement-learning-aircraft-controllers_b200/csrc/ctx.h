@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/acb200.h"
 
@@ -20,4 +21,10 @@ struct acb200_ctx {
     cudaEvent_t pipe_done[kPipe] = {nullptr, nullptr, nullptr};
     cudaEvent_t fork = nullptr;
     int host_chunks = 0;   // 0 = automatic
+    // parameter groups (acb200_set_param_groups): group g owns aircraft [group_bounds[g], group_bounds[g+1]) of the fleet
+    std::vector<acb200_aircraft_params> groups;
+    std::vector<int64_t> group_bounds;
+    // device scratch owned by the handle (acb200_env_gather_done: one int per 1024 aircraft)
+    int32_t* scratch_i32 = nullptr;
+    int scratch_i32_len = 0;
 };

@@ -31,6 +31,13 @@ template <typename T> struct EnvConst {
     int64_t id_offset;
 };
 
+// generators.py:41-45: difficulty_scale is the Python float 0.3 / 0.5 / 0.7.  The fleet stores it as float32 (the curriculum
+// is one small tensor write); (double)0.3f is 4e-8 away from 0.3, so the value the reference multiplies with is recovered as
+// the nearest multiple of 1e-6 (a correctly rounded quotient = the literal's double).  Reset / random-walk path only.
+__device__ __forceinline__ double difficulty_scale(float difficulty) {
+    return __ddiv_rn(::rint(__dmul_rn((double)difficulty, 1e6)), 1e6);
+}
+
 __device__ __constant__ const uint8_t kPerm3[6][3] = {{0, 1, 2}, {0, 2, 1}, {1, 0, 2}, {1, 2, 0}, {2, 0, 1}, {2, 1, 0}};
 
 // RateControlEnv._get_observation, rate_env.py:374-408
@@ -87,7 +94,7 @@ __device__ __noinline__ void env_reset_draw(uint64_t seed, uint64_t global_id, u
     for (int k = 0; k < 4; ++k) out->d[k] = d[k];
 
     const double max_rates[3] = {180.0 * (PI / 180.0), 180.0 * (PI / 180.0), 160.0 * (PI / 180.0)};
-    const double scale = (double)difficulty;
+    const double scale = difficulty_scale(difficulty);
     uint32_t sel[4];
     g.block(4, sel);
     double mag[3];
@@ -183,10 +190,11 @@ template <typename T> __device__ __forceinline__ void env_update_command(const E
         const double r0 = ::sqrt(-2.0 * ::log(u0)), r1 = ::sqrt(-2.0 * ::log(u2));
         const double z[3] = {r0 * ::cos(2 * DPI * u1), r0 * ::sin(2 * DPI * u1), r1 * ::cos(2 * DPI * u3)};
         const double sdt = ::sqrt((double)E.dt);
+        const double scale = difficulty_scale(e.difficulty);
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            double delta = z[k] * 0.1 * sdt;
-            delta *= (double)e.difficulty * max_rates[k];
+            double delta = __dmul_rn(__dmul_rn(z[k], 0.1), sdt);
+            delta = __dmul_rn(delta, __dmul_rn(scale, max_rates[k]));
             e.rate_cmd[k] = (T)np_clip((double)e.rate_cmd[k] + delta, -max_rates[k], max_rates[k]);
         }
     } else if (e.command_type == ACB200_CMD_SINE) {

@@ -9,7 +9,7 @@ from typing import Optional
 import torch
 
 from . import _cabi
-from .fleet import _dtype, _ptr
+from .fleet import _dtype, _ptr, as_tensor
 
 DIFFICULTY_SCALE = {"easy": 0.3, "medium": 0.5, "hard": 0.7}          # generators.py:41-45
 COMMAND_TYPES = {"step": _cabi.CMD_STEP, "ramp": _cabi.CMD_RAMP, "sine": _cabi.CMD_SINE, "random": _cabi.CMD_RANDOM}
@@ -93,7 +93,7 @@ class BatchedRateControlEnv:
         if mask is None:
             self.difficulty.copy_(dv); self.command_type.copy_(cv)
         else:
-            m = mask.to(self.device).bool()
+            m = as_tensor(mask, self.device).bool()
             self.difficulty[m] = dv[m]; self.command_type[m] = cv[m]
 
     def _bind_stream(self):
@@ -102,7 +102,7 @@ class BatchedRateControlEnv:
     def reset(self, mask: Optional[torch.Tensor] = None):
         self._bind_stream()
         if mask is not None:
-            mask = mask.to(self.device, torch.uint8).contiguous()
+            mask = as_tensor(mask, self.device, torch.uint8)
         self.ctx.check(self.ctx.lib.acb200_env_reset(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(mask)))
         return self.obs
 
@@ -111,11 +111,12 @@ class BatchedRateControlEnv:
         """Give contiguous groups of aircraft their own ``AircraftParams`` (the reference has one per env instance,
         simulation_backend.py:55-80).  ``groups``: list of ``_cabi.AircraftParamsC``; ``bounds``: len(groups)+1 offsets,
         multiples of 128 except the last (default: an even split).  Each group is one launch with its parameters in the
-        constant bank; ``None`` / [] returns to one parameter set for the whole fleet."""
+        constant bank, on EVERY step path (``step``, ``step_host``, the VecEnv shim): the groups live in the context
+        (``acb200_set_param_groups``), which validates all of them first -- a bad group raises ``ValueError`` like
+        ``AircraftParams.__post_init__`` and changes nothing.  ``None`` / [] returns to the context's one parameter set."""
+        lib, h = self.ctx.lib, self.ctx.handle
         if not groups:
-            if getattr(self, "_groups", None):          # back to the default parameter set (simulation_backend.py:74-76)
-                base = _cabi.default_aircraft_params()
-                self.ctx.check(self.ctx.lib.acb200_set_aircraft_params(self.ctx.handle, C.byref(base)))
+            self.ctx.check(lib.acb200_set_param_groups(h, None, None, 0))
             self._groups = None
             return
         g = len(groups)
@@ -123,31 +124,27 @@ class BatchedRateControlEnv:
             per = ((self.n + g - 1) // g + 127) // 128 * 128
             bounds = [min(k * per, self.n) for k in range(g)] + [self.n]
         bounds = [int(b) for b in bounds]
-        if len(bounds) != g + 1 or bounds[0] != 0 or bounds[-1] != self.n or any(b % 128 for b in bounds[:-1]) or \
-                any(b1 < b0 for b0, b1 in zip(bounds, bounds[1:])):
+        if len(bounds) != g + 1 or bounds[-1] != self.n:
             raise ValueError("bounds must rise from 0 to n in multiples of 128")
-        for pr in groups:                      # validate now (ValueError like AircraftParams.__post_init__), restore after
-            self.ctx.check(self.ctx.lib.acb200_set_aircraft_params(self.ctx.handle, C.byref(pr)))
+        arr = (_cabi.AircraftParamsC * g)(*groups)
+        b = (C.c_int64 * (g + 1))(*bounds)
+        self.ctx.check(lib.acb200_set_param_groups(h, arr, b, g))
         self._groups = (list(groups), bounds)
 
     def step(self, action: Optional[torch.Tensor] = None):
         """One control step for every aircraft; tensors returned are views of the env's own buffers."""
         self._bind_stream()
         if action is not None:
+            action = as_tensor(action, self.device)
             assert action.dtype == torch.float32 and action.shape == (self.n, 4) and action.is_contiguous()
-        if getattr(self, "_groups", None):
-            groups, bounds = self._groups
-            lib, h = self.ctx.lib, self.ctx.handle
-            for pr, lo, hi in zip(groups, bounds, bounds[1:]):
-                self.ctx.check(lib.acb200_set_aircraft_params(h, C.byref(pr)))
-                self.ctx.check(lib.acb200_env_step_range(h, C.byref(self.c), C.byref(self.cfg), _ptr(action), lo, hi - lo))
-            return self.obs, self.reward, self.terminated, self.truncated
         self.ctx.check(self.ctx.lib.acb200_env_step(self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action)))
         return self.obs, self.reward, self.terminated, self.truncated
 
     def step_host(self, action_host, obs_host, reward_host, terminated_host, truncated_host, att_cmd_host=None):
         """Same step with (pinned) HOST tensors in and out; synchronous.  att_cmd_host [4][n] (dtype of the build)
-        is this step's attitude command for controller="attitude_pid"."""
+        is this step's attitude command for controller="attitude_pid".  Any OUTPUT may be None: it is then not copied
+        (reward + flags alone are 6 B per aircraft instead of 78 with the observation); ``gather_done`` returns the
+        finished aircraft's observations."""
         self._bind_stream()
         if att_cmd_host is not None:
             assert att_cmd_host.dtype == self.dtype and att_cmd_host.shape == (4, self.n) and att_cmd_host.is_contiguous()
@@ -155,6 +152,52 @@ class BatchedRateControlEnv:
             self.ctx.handle, C.byref(self.c), C.byref(self.cfg), _ptr(action_host), _ptr(att_cmd_host), _ptr(self._scratch),
             _ptr(obs_host), _ptr(reward_host), _ptr(terminated_host), _ptr(truncated_host)))
         return obs_host, reward_host, terminated_host, truncated_host
+
+    def gather_done(self, capacity: Optional[int] = None, to_host: bool = True):
+        """The aircraft that finished an episode in the last step, ascending ids: (ids int64 [k], terminal_obs float32
+        [k,18], reset_obs float32 [k,18]).  One compaction on the device (``acb200_env_gather_done``) and, with
+        ``to_host``, copies of k rows -- not of the fleet."""
+        self._bind_stream()
+        cap = int(capacity if capacity is not None else max(1024, self.n // 16))
+        if getattr(self, "_done_cap", 0) < cap:
+            d = self.device
+            self._done_ids = torch.empty((cap,), device=d, dtype=torch.int64)
+            self._done_term = torch.empty((cap, 18), device=d, dtype=torch.float32)
+            self._done_reset = torch.empty((cap, 18), device=d, dtype=torch.float32)
+            self._done_count = torch.zeros((1,), device=d, dtype=torch.int64)
+            self._done_cap = cap
+        self.ctx.check(self.ctx.lib.acb200_env_gather_done(self.ctx.handle, C.byref(self.c), cap, _ptr(self._done_ids),
+                                                          _ptr(self._done_term), _ptr(self._done_reset), _ptr(self._done_count)))
+        k = int(self._done_count.item())
+        if k > cap:                      # rare: more finished than the buffers hold -- grow and gather again
+            return self.gather_done(capacity=k, to_host=to_host)
+        out = (self._done_ids[:k], self._done_term[:k], self._done_reset[:k])
+        return tuple(t.cpu() for t in out) if to_host else out
+
+    # -- checkpoint (SURVEY.md section 5): everything a resumed run needs to continue bit for bit -------------------
+    _STATE_TENSORS = ("state", "controls", "derived", "pid", "att_cmd", "rate_cmd", "prev_action", "rew_mem", "sched", "env_time",
+                      "step_count", "is_settled", "command_type", "difficulty", "episode_idx", "ep_return", "obs", "reward",
+                      "terminated", "truncated", "terminal_obs", "stats")
+
+    def state_dict(self) -> dict:
+        """The SoA tensors (incl. the Philox counter word ``episode_idx``) + the config words the random streams are keyed
+        by.  CPU copies: a checkpoint written on one GPU loads on another."""
+        sd = {k: getattr(self, k).detach().cpu().clone() for k in self._STATE_TENSORS}
+        sd["config"] = {"n": self.n, "precision": self.precision, "dt": self.cfg.dt, "dt_physics": self.cfg.dt_physics,
+                        "max_steps": self.cfg.max_steps, "controller": self.cfg.controller, "auto_reset": self.cfg.auto_reset,
+                        "pid_throttle": self.cfg.pid_throttle, "residual_scale": self.cfg.residual_scale, "seed": self.cfg.seed,
+                        "id_offset": self.cfg.id_offset}
+        return sd
+
+    def load_state_dict(self, sd: dict):
+        c = sd["config"]
+        if c["n"] != self.n or c["precision"] != self.precision:
+            raise ValueError(f"checkpoint is for n={c['n']} precision={c['precision']}, env is n={self.n} precision={self.precision}")
+        for k in self._STATE_TENSORS:
+            getattr(self, k).copy_(sd[k].to(self.device))
+        for k in ("dt", "dt_physics", "max_steps", "controller", "auto_reset", "pid_throttle", "residual_scale", "seed", "id_offset"):
+            setattr(self.cfg, k, c[k])
+        self.dt = self.cfg.dt
 
     def episode_stats(self, reset: bool = False) -> dict:
         v = self.stats.cpu().tolist()

@@ -27,6 +27,21 @@ def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+def as_tensor(x, device, dtype=None) -> torch.Tensor:
+    """Tensor intake of the adapters: a torch tensor, or ANY object with ``__dlpack__`` (CuPy, JAX, numba device arrays,
+    another framework's CUDA buffer -- consumed zero-copy through ``torch.from_dlpack``, north_star's "exchanges DLPack /
+    PyTorch tensors"), or a numpy array / nested list (copied).  The library itself only ever sees ``data_ptr()``."""
+    if isinstance(x, torch.Tensor):
+        t = x
+    elif hasattr(x, "__dlpack__"):
+        t = torch.from_dlpack(x)
+    else:
+        t = torch.as_tensor(x)
+    if t.device != device or (dtype is not None and t.dtype != dtype):
+        t = t.to(device=device, dtype=dtype if dtype is not None else t.dtype)
+    return t.contiguous()
+
+
 class AircraftFleet:
     """N aircraft.  state[13][n] = N,E,D,u,v,w,roll,pitch,yaw,p,q,r,time; controls[4][n] = elevator,
     aileron, rudder, throttle; derived[4][n] = airspeed, altitude, ground_speed, heading; pid[18][n]."""
@@ -65,10 +80,10 @@ class AircraftFleet:
         """Simplified6DOF.reset: initial_state [13][n] or None for level flight at 100 m, 20 m/s."""
         self._bind_stream()
         if initial_state is not None:
-            initial_state = initial_state.to(self.device, self.dtype).contiguous()
+            initial_state = as_tensor(initial_state, self.device, self.dtype)
             assert initial_state.shape == (13, self.n)
         if mask is not None:
-            mask = mask.to(self.device, torch.uint8).contiguous()
+            mask = as_tensor(mask, self.device, torch.uint8)
         self.ctx.check(self.ctx.lib.acb200_fleet_reset(self.ctx.handle, C.byref(self.c), _ptr(mask), _ptr(initial_state)))
         if mask is None:                       # agent.reset() / mission.start() of the outer levels
             self.pid_outer.zero_(); self.wp_index.zero_()
@@ -79,7 +94,7 @@ class AircraftFleet:
 
     def set_controls(self, surfaces: torch.Tensor):
         """surfaces [4][n] in ControlSurfaces.to_array order; clipped when the step consumes them."""
-        self._pending.copy_(surfaces.to(self.device, self.dtype))
+        self._pending.copy_(as_tensor(surfaces, self.device, self.dtype))
 
     def step(self, dt: float):
         self._bind_stream()
@@ -93,7 +108,7 @@ class AircraftFleet:
 
     def _cascade(self, level, cmd, dt, dt_ctrl, surfaces_out):
         self._bind_stream()
-        cmd = cmd.to(self.device, self.dtype).contiguous()
+        cmd = as_tensor(cmd, self.device, self.dtype)
         assert cmd.shape == (4, self.n)
         self.ctx.check(self.ctx.lib.acb200_step_cascade(self.ctx.handle, C.byref(self.c), level, _ptr(cmd),
                                                         dt if dt_ctrl is None else dt_ctrl, dt, self.dt_physics,
@@ -111,7 +126,7 @@ class AircraftFleet:
     def step_hsa(self, cmd: torch.Tensor, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None):
         """HSAAgent.compute_action (hsa_agent.py:119-231) + set_controls + step(dt); cmd [3][n] = heading, speed, altitude."""
         self._bind_stream()
-        cmd = cmd.to(self.device, self.dtype).contiguous()
+        cmd = as_tensor(cmd, self.device, self.dtype)
         assert cmd.shape == (3, self.n)
         self.ctx.check(self.ctx.lib.acb200_step_hsa(self.ctx.handle, C.byref(self.c), _ptr(self.pid_outer), _ptr(cmd),
                                                     dt if dt_ctrl is None else dt_ctrl, dt, self.dt_physics, _ptr(surfaces_out)))
@@ -120,7 +135,7 @@ class AircraftFleet:
     def set_mission(self, waypoints, acceptance_radius: float = 40.0, guidance: str = "PP", loop: bool = False):
         """MissionPlanner(waypoints, acceptance_radius).start() for every aircraft (mission_planner.py:56-93).
         waypoints [n_wp][4] = north, east, down, speed (NaN = None); guidance 'LOS' | 'PP' (waypoint_agent.py:33-52)."""
-        wp = torch.as_tensor(waypoints).to(self.device, self.dtype).contiguous()
+        wp = as_tensor(waypoints, self.device, self.dtype)
         assert wp.ndim == 2 and wp.shape[1] == 4 and wp.shape[0] >= 1
         g = {"LOS": _cabi.GUIDANCE_LOS, "PP": _cabi.GUIDANCE_PP, "PURE_PURSUIT": _cabi.GUIDANCE_PP}[guidance.upper()]
         self.waypoints = wp

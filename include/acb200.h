@@ -189,6 +189,19 @@ void acb200_cessna_aircraft_params(acb200_aircraft_params* p);        /* 'cessna
 void acb200_default_controller_params(acb200_controller_params* c);
 int acb200_set_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p);
 int acb200_set_controller_params(acb200_ctx* ctx, const acb200_controller_params* c);
+/* AircraftParams.__post_init__ (simplified_6dof.py:119-143) alone: 0 or ACB200_EVALUE with the reference's message in
+ * acb200_last_error; the context's parameters are not touched. */
+int acb200_validate_aircraft_params(acb200_ctx* ctx, const acb200_aircraft_params* p);
+int acb200_get_aircraft_params(const acb200_ctx* ctx, acb200_aircraft_params* out);
+int acb200_get_controller_params(const acb200_ctx* ctx, acb200_controller_params* out);
+/* Parameter groups: group g of n_groups owns aircraft [bounds[g], bounds[g+1]) (bounds[0] = 0,
+ * non-decreasing, every bound but the last a multiple of 128) and flies with params[g] -- what the reference is with one
+ * AircraftParams per env instance (simulation_backend.py:55-80).  Every env step entry point (acb200_env_step, _range,
+ * _host) then launches one kernel per group it touches, each with its group's parameters in the constant bank; the
+ * context's own parameters (acb200_set_aircraft_params) are neither used by those calls nor changed.  All groups are
+ * validated first; on ACB200_EVALUE nothing changes.  n_groups = 0 removes the groups.  The fleet the groups describe is
+ * the one whose n equals bounds[n_groups]; a step on a fleet of another size fails with ACB200_EVALUE. */
+int acb200_set_param_groups(acb200_ctx* ctx, const acb200_aircraft_params* params, const int64_t* bounds, int32_t n_groups);
 
 /* ---- physics ---- */
 /* Simplified6DOF.reset for aircraft with mask[i] != 0 (mask NULL = all).  init_state real[13][n] or
@@ -234,10 +247,20 @@ int acb200_env_step_range(acb200_ctx* ctx, const acb200_env* e, const acb200_env
  * (real[4][n], nullable: the per-step attitude command of ACB200_CTRL_ATTITUDE_PID) in, obs / reward / terminated /
  * truncated out, pipelined in chunks over three internal streams so that the two PCIe directions and the kernel
  * overlap, and returns when the host buffers are complete.  reward_host is float[n].  action_dev: caller-owned
- * device scratch of n*5 floats. */
+ * device scratch of n*5 floats (needed when action_host or reward_host is given).  Every output pointer may be NULL: that
+ * output is then not copied (the device buffers of `e` still hold it) -- with the controller in the kernel a trainer that
+ * only wants reward + flags moves 6 B per aircraft instead of 78.  acb200_env_gather_done returns the finished aircraft. */
 int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_config* cfg,
                          const float* action_host, const void* att_cmd_host, float* action_dev, float* obs_host,
                          float* reward_host, uint8_t* terminated_host, uint8_t* truncated_host);
+/* The aircraft that finished an episode in the LAST step (terminated | truncated), as a compact list in ascending id
+ * order: ids_out int64[capacity], their terminal observations (terminal_obs_out float[capacity][18], nullable; what SB3's
+ * VecEnv reports as infos[i]["terminal_observation"]) and the observations of the episodes that started (reset_obs_out
+ * float[capacity][18], nullable); *count_out = how many finished (may exceed capacity: only the first `capacity` are
+ * written).  All pointers device memory; three small launches on the context's stream; about 0.2 % of the fleet per step
+ * at 500-step episodes, so a trainer whose controller runs in the kernel never moves the (n, 18) matrix to the host. */
+int acb200_env_gather_done(acb200_ctx* ctx, const acb200_env* e, int64_t capacity, int64_t* ids_out, float* terminal_obs_out,
+                           float* reset_obs_out, int64_t* count_out);
 /* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 128k aircraft per chunk) */
 int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 

@@ -677,6 +677,11 @@ static inline double u53(uint32_t a, uint32_t b) {
 /* RandomState.uniform(lo, hi) = lo + (hi-lo)*random_sample() */
 static inline double uniform_lh(double lo, double hi, double u) { return lo + (hi - lo) * u; }
 
+/* generators.py:41-45: difficulty_scale is the Python float 0.3 / 0.5 / 0.7.  The fleet keeps it as float32 (so that the
+ * curriculum is one small tensor write); (double)0.3f = 0.30000001192..., 4e-8 away.  The value the reference multiplies
+ * with is recovered as the nearest multiple of 1e-6 (correctly rounded quotient = the literal's double). */
+double orc_difficulty_scale(float difficulty) { return rint((double)difficulty * 1e6) / 1e6; }
+
 typedef struct { uint32_t key[2]; uint32_t ctr[4]; } rng_t;
 
 static inline void rng_init(rng_t* g, uint64_t seed, int64_t global_id, uint32_t episode) {
@@ -883,7 +888,7 @@ static void env_reset_one(const orc_env_config* E, int64_t local_i, env_t* e) {
 
     /* command generation */
     const double max_rates[3] = {np_radians(180.0), np_radians(180.0), np_radians(160.0)}; /* generators.py:16-18 */
-    const double scale = (double)e->difficulty;
+    const double scale = orc_difficulty_scale(e->difficulty);
     uint32_t sel[4];
     rng_block(&g, 4, sel);
     double mag[3], ufreq;
@@ -936,7 +941,19 @@ static void env_reset_one(const orc_env_config* E, int64_t local_i, env_t* e) {
 }
 
 /* RateControlEnv._update_command, rate_env.py:342-372 (+ generators.py:145-164 for the random walk) */
-static void env_update_command(const orc_env_config* E, int64_t local_i, env_t* e) {
+void orc_walk_normals(uint64_t seed, int64_t global_id, uint32_t episode, int32_t step_count, double z[3]) {
+    rng_t g;
+    uint32_t w[4];
+    rng_init(&g, seed, global_id, episode);
+    rng_block(&g, 16u + (uint32_t)step_count, w);
+    /* Box-Muller on (0,1] x [0,1) uniforms built from 32-bit words */
+    const double u0 = ((double)w[0] + 1.0) / 4294967296.0, u1 = (double)w[1] / 4294967296.0;
+    const double u2 = ((double)w[2] + 1.0) / 4294967296.0, u3 = (double)w[3] / 4294967296.0;
+    const double r0 = sqrt(-2.0 * log(u0)), r1 = sqrt(-2.0 * log(u2));
+    z[0] = r0 * cos(2 * ORC_PI * u1); z[1] = r0 * sin(2 * ORC_PI * u1); z[2] = r1 * cos(2 * ORC_PI * u3);
+}
+
+static void env_update_command(const orc_env_config* E, int64_t local_i, env_t* e, const double* walk_z) {
     if (e->command_type == ORC_CMD_RAMP) {
         const double t = e->env_time - 0.0, duration = 3.0;
         if (t < duration) {
@@ -946,20 +963,17 @@ static void env_update_command(const orc_env_config* E, int64_t local_i, env_t* 
             for (int k = 0; k < 3; ++k) e->rate_cmd[k] = e->sched[k];
         }
     } else if (e->command_type == ORC_CMD_RANDOM) {
+        /* rate_env.py:358-365 with generators.py:145-164:
+         *   delta = randn(3) * diffusion * sqrt(dt);  delta *= difficulty_scale * max_rates;  cmd += delta;  clip */
         const double max_rates[3] = {np_radians(180.0), np_radians(180.0), np_radians(160.0)};
-        rng_t g;
-        uint32_t w[4];
-        rng_init(&g, E->seed, E->id_offset + local_i, e->episode_idx);
-        rng_block(&g, 16u + (uint32_t)e->step_count, w);
-        /* Box-Muller on (0,1] uniforms built from 32-bit words */
-        const double u0 = ((double)w[0] + 1.0) / 4294967296.0, u1 = (double)w[1] / 4294967296.0;
-        const double u2 = ((double)w[2] + 1.0) / 4294967296.0, u3 = (double)w[3] / 4294967296.0;
-        const double r0 = sqrt(-2.0 * log(u0)), r1 = sqrt(-2.0 * log(u2));
-        const double z[3] = {r0 * cos(2 * ORC_PI * u1), r0 * sin(2 * ORC_PI * u1), r1 * cos(2 * ORC_PI * u3)};
+        double z[3];
+        if (walk_z) { for (int k = 0; k < 3; ++k) z[k] = walk_z[k]; }
+        else orc_walk_normals(E->seed, E->id_offset + local_i, e->episode_idx, e->step_count, z);
         const double sdt = sqrt(E->dt);
+        const double scale = orc_difficulty_scale(e->difficulty);
         for (int k = 0; k < 3; ++k) {
             double delta = z[k] * 0.1 * sdt;
-            delta *= (double)e->difficulty * max_rates[k];
+            delta *= scale * max_rates[k];
             e->rate_cmd[k] = np_clip(e->rate_cmd[k] + delta, -max_rates[k], max_rates[k]);
         }
     } else if (e->command_type == ORC_CMD_SINE) {
@@ -1042,7 +1056,9 @@ int orc_env_step(const orc_aircraft_params* P, const orc_controller_params* C, c
         /* :241-245 */
         e.env_time += E->dt;
         e.step_count += 1;
-        env_update_command(E, i, &e);
+        double wz[3];
+        if (B->walk_z) for (int k = 0; k < 3; ++k) wz[k] = B->walk_z[(int64_t)k * n + i];
+        env_update_command(E, i, &e, B->walk_z ? wz : NULL);
         /* :248-252 */
         const double err[3] = {e.rate_cmd[0] - e.s[9], e.rate_cmd[1] - e.s[10], e.rate_cmd[2] - e.s[11]};
         const double airspeed = e.derived[0], altitude = e.derived[1], roll = e.s[6], pitch = e.s[7];

@@ -149,6 +149,10 @@ typedef struct {
     float*  terminal_obs; /* [n][18] written for finished aircraft only (SB3 terminal_observation) */
     double* components;   /* [8][n] tracking,smoothness,stability,oscillation,survival,settle_bonus,crash_penalty,residual_bonus; nullable */
     double* stats;        /* [16] accumulated over calls; nullable */
+    /* ORACLE ONLY (no counterpart in acb200_env): standard normals [3][n] that replace this step's Philox/Box-Muller
+     * draw of the random-walk command, so that the reference's own MT19937 `randn(3)` values (generators.py:159) can
+     * be replayed through the restatement (tests/golden/rate_env_random.npz); NULL = the Philox stream. */
+    const double* walk_z;
 } orc_env_buffers;
 
 typedef struct {
@@ -171,6 +175,13 @@ int orc_env_reset(const orc_aircraft_params* P, const orc_env_config* E, orc_env
 /* RateControlEnv.step (rate_env.py:212-300) for all n aircraft.  action[n][4] float, env order. */
 int orc_env_step(const orc_aircraft_params* P, const orc_controller_params* C, const orc_env_config* E,
                  orc_env_buffers* B, const float* action, int nthreads);
+
+/* The three standard normals the random-walk command of (seed, global id, episode, step_count) consumes
+ * (block 16 + step_count of the aircraft's Philox stream, Box-Muller); exposed for the distribution test. */
+void orc_walk_normals(uint64_t seed, int64_t global_id, uint32_t episode, int32_t step_count, double z[3]);
+/* difficulty_scale as the reference holds it (a Python float 0.3 / 0.5 / 0.7, generators.py:41-45) recovered from the
+ * float32 the fleet stores: the nearest multiple of 1e-6. */
+double orc_difficulty_scale(float difficulty);
 
 /* Philox4x32-10 block, exposed for the known-answer test. */
 void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);

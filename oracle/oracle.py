@@ -70,6 +70,7 @@ class EnvBuffers(C.Structure):
         ("ep_return", C.c_void_p),
         ("obs", C.c_void_p), ("reward", C.c_void_p), ("terminated", C.c_void_p), ("truncated", C.c_void_p),
         ("terminal_obs", C.c_void_p), ("components", C.c_void_p), ("stats", C.c_void_p),
+        ("walk_z", C.c_void_p),      # oracle only: injected standard normals [3][n] of the random-walk command
     ]
 
 
@@ -135,6 +136,9 @@ def lib() -> C.CDLL:
         L.orc_env_step.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.POINTER(EnvConfig),
                                    C.POINTER(EnvBuffers), C.c_void_p, C.c_int]
         L.orc_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_walk_normals.argtypes = [C.c_uint64, C.c_int64, C.c_uint32, C.c_int32, C.c_void_p]
+        L.orc_difficulty_scale.argtypes = [C.c_float]
+        L.orc_difficulty_scale.restype = C.c_double
         L.orc_sensor_normals.argtypes = [C.c_uint64, C.c_int64, C.c_uint32, C.c_void_p]
         L.orc_sensor_update.argtypes = [C.POINTER(SensorConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
                                         C.c_void_p, C.c_void_p, C.c_void_p]
@@ -281,20 +285,36 @@ class Env:
         self.stats = np.zeros(16, f8)
         self.buf = EnvBuffers(n=n)
         for name, _ in EnvBuffers._fields_[1:]:
-            setattr(self.buf, name, getattr(self, name).ctypes.data)
+            if name != "walk_z":
+                setattr(self.buf, name, getattr(self, name).ctypes.data)
+        self._walk_z = None
 
     def reset(self, mask=None):
         m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
         lib().orc_env_reset(C.byref(self.params), C.byref(self.cfg), C.byref(self.buf), _ptr(m), self.nthreads)
         return self.obs
 
-    def step(self, action=None):
+    def step(self, action=None, walk_z=None):
+        """walk_z [3][n] float64: standard normals that replace this step's Philox draw of the random-walk command
+        (the reference's own ``randn(3)`` values, replayed)."""
         a = None if action is None else _chk(np.ascontiguousarray(action, np.float32), np.float32, (self.n, 4))
+        self._walk_z = None if walk_z is None else _chk(np.ascontiguousarray(walk_z, np.float64), np.float64, (3, self.n))
+        self.buf.walk_z = _ptr(self._walk_z)
         k = lib().orc_env_step(C.byref(self.params), C.byref(self.cparams), C.byref(self.cfg), C.byref(self.buf),
                                _ptr(a), self.nthreads)
         if k < 0:
             raise ValueError("Invalid timestep")
         return self.obs, self.reward, self.terminated, self.truncated
+
+
+def walk_normals(seed: int, global_id: int, episode: int, step_count: int) -> np.ndarray:
+    z = np.zeros(3)
+    lib().orc_walk_normals(seed, global_id, episode, step_count, z.ctypes.data)
+    return z
+
+
+def difficulty_scale(d: float) -> float:
+    return lib().orc_difficulty_scale(d)
 
 
 def philox(ctr, key):

@@ -19,6 +19,11 @@ import numpy as np
 
 logging.disable(logging.CRITICAL)
 HERE = os.path.dirname(os.path.abspath(__file__))
+# The fixtures pin the reference AS RUN UNDER NumPy >= 2 (NEP 50 weak scalars): with float32 actions the env's smoothness
+# term and the residual bonus are float32 arithmetic (rate_env.py:260-265,282; residual_rate_env.py:153-155).  The reference's
+# requirements.txt pins numpy<2, where the same expressions promote to float64 -- a difference of <= ~1e-8 in the reward,
+# inside the 1e-7 reward tolerance of the tests but outside bit parity.  DESIGN.md section 3 states this assumption.
+assert int(np.__version__.split(".")[0]) >= 2, f"fixtures are defined under NumPy >= 2, found {np.__version__}"
 
 import aircraft_controls_bindings as acb  # noqa: E402  (reference C++ PID, oracle/_ref)
 from controllers.attitude_agent import AttitudeAgent  # noqa: E402
@@ -296,6 +301,177 @@ def gen_env(pool):
     np.savez_compressed(os.path.join(HERE, "rate_env.npz"), **out)
 
 
+class _RecordingRandomState:
+    """Stands in for RateCommandGenerator.rng (a plain attribute, generators.py:35): forwards every call to the real
+    RandomState and keeps what randn() returned, so that the fixture can carry the reference's own normals."""
+
+    def __init__(self, rs):
+        self._rs = rs
+        self.normals = []
+
+    def randn(self, *shape):
+        z = self._rs.randn(*shape)
+        self.normals.append(np.array(z, dtype=np.float64).copy())
+        return z
+
+    def __getattr__(self, name):
+        return getattr(self._rs, name)
+
+
+def _env_random_worker(args):
+    """command_type="random" (rate_env.py:333-336,358-365; generators.py:145-164): the command is a clipped random walk,
+    one randn(3) per env step.  The fixture records those normals next to everything _env_worker records."""
+    from learned_controllers.envs.rate_env import RateControlEnv
+    from learned_controllers.envs.residual_rate_env import ResidualRateControlEnv
+    seed, difficulty, controller, steps, boost = args
+    rng = np.random.default_rng(seed)
+    if controller == 3:
+        env = ResidualRateControlEnv(difficulty=difficulty, command_type="random", rng_seed=seed)
+        base = env.base_env
+    else:
+        env = RateControlEnv(difficulty=difficulty, command_type="random", rng_seed=seed)
+        base = env
+    rec = _RecordingRandomState(base.cmd_generator.rng)
+    base.cmd_generator.rng = rec
+    obs0, info = env.reset(seed=seed)
+    obs0 = obs0.copy()
+    s0 = state_vec(base.sim)
+    assert not rec.normals and np.all(base.rate_command == 0.0)        # the walk starts from zero, no draw at reset
+    agent = RateAgent(ControllerConfig()) if controller == 1 else None
+    A, O, R, TE, TR, CMP, S, CMD, SET, Z = [], [], [], [], [], [], [], [], [], []
+    for t in range(steps):
+        if boost and t == boost:
+            # push the walk to the command limit once so that the fixture exercises the clip (rate_env.py:362-365):
+            # the command is the env's public attribute, callers set it (eval_rate.py:104-108)
+            base.rate_command[:] = np.array([0.999, -0.999, 0.999]) * base._max_rates
+        if controller == 0:
+            a = (rng.uniform(-1.2, 1.2, 4) * 0.1).astype(np.float32); a[3] = np.float32(0.6)
+        elif controller == 3:
+            a = rng.uniform(-1.0, 1.0, 4).astype(np.float32)
+        else:
+            st = base.sim.get_state()
+            p, q, r = base.rate_command
+            sf = agent.compute_action(ControlCommand(mode=ControlMode.RATE, roll_rate=p, pitch_rate=q, yaw_rate=r,
+                                                     throttle=0.6), st, dt=0.02)
+            a = np.array([sf.aileron, sf.elevator, sf.rudder, sf.throttle], dtype=np.float32)
+        obs, rew, term, trunc, info = env.step(a)
+        rc = info["reward_components"]
+        comp = [rc["tracking"], rc["smoothness"], rc["stability"], rc["oscillation"], rc["survival"],
+                0.0, rc.get("crash_penalty", 0.0), 0.0]
+        comp[5] = float(rew) - float(rc["total"]) - comp[6]
+        A.append(a); O.append(obs.copy()); R.append(float(rew)); TE.append(term); TR.append(trunc)
+        CMP.append(comp); S.append(state_vec(base.sim)); CMD.append(base.rate_command.copy())
+        SET.append(base.settle_bonus.is_settled)
+        assert len(rec.normals) == t + 1
+        Z.append(rec.normals[-1])
+        if term or trunc:
+            break
+    return dict(s0=s0, obs0=obs0, actions=np.array(A), obs=np.array(O), reward=np.array(R), terminated=np.array(TE),
+                truncated=np.array(TR), components=np.array(CMP), states=np.array(S), rate_cmd=np.array(CMD),
+                is_settled=np.array(SET), walk_z=np.array(Z), boost=np.array(boost))
+
+
+def gen_env_random(pool):
+    """Random-walk command episodes: external / rate-PID / residual control, all three difficulties."""
+    scale = {"easy": 0.3, "medium": 0.5, "hard": 0.7}
+    cases = []
+    for ctrl in (0, 1, 3):
+        for diff in ("easy", "medium", "hard"):
+            cases.append((2000 + len(cases), diff, ctrl, 500, 40 if diff == "hard" else 0))
+    res = pool.map(_env_random_worker, cases)
+    out = {"n_cases": len(cases)}
+    for k, (c, r) in enumerate(zip(cases, res)):
+        out[f"c{k}_meta"] = np.array([c[0], scale[c[1]], 3, c[2]], dtype=np.float64)
+        for key, v in r.items():
+            out[f"c{k}_{key}"] = v
+        hit = np.abs(r["rate_cmd"]) >= np.radians([180, 180, 160]) - 1e-15
+        print("env random-walk case", k, c, "steps", len(r["reward"]), "return", r["reward"].sum(), "clip hits", int(hit.sum()))
+    np.savez_compressed(os.path.join(HERE, "rate_env_random.npz"), **out)
+
+
+# ------------------------------------------------------------------------------------------------
+ENVELOPE_SUPPORT = [(15.0, 30.0), (50.0, 200.0), (-np.radians(15), np.radians(15)), (-np.radians(15), np.radians(15)),
+                    (0.0, 2 * np.pi), (-0.1, 0.1), (-0.1, 0.1), (-0.1, 0.1)]     # generators.py:173-176,199-209
+ENV_BINS, MAG_BINS, Z_BINS, Z_RANGE = 4096, 1024, 4096, 6.0
+
+
+def _reset_distribution_worker(args):
+    """R resets of ONE unmodified RateControlEnv (the three MT19937 streams run on, rate_env.py:64-77): what the envelope
+    sampler and the command generator drew, reduced to counts -- exact supports and fine histograms (= the empirical CDF on
+    a grid), so that the fixture stays small whatever R is."""
+    from learned_controllers.envs.rate_env import RateControlEnv
+    difficulty, ctype, seed, R = args
+    scale = {"easy": 0.3, "medium": 0.5, "hard": 0.7}[difficulty]
+    env = RateControlEnv(difficulty=difficulty, command_type=ctype, rng_seed=seed)
+    max_rates = env._max_rates
+    env_q = np.zeros((R, 8)); cmd = np.zeros((R, 3)); freq = np.zeros(R)
+    for i in range(R):
+        env.reset()
+        st = env.sim.get_state()
+        env_q[i] = [st.airspeed, st.altitude, st.roll, st.pitch, st.yaw, st.p, st.q, st.r]
+        assert st.position[0] == 0.0 and st.position[1] == 0.0 and st.velocity[1] == 0.0 and st.velocity[2] == 0.0
+        assert st.velocity[0] == st.airspeed and st.position[2] == -st.altitude                  # rate_env.py:174-183
+        if ctype == "step":
+            cmd[i] = env.rate_command
+        elif ctype == "ramp":
+            cmd[i] = env.command_schedule["end"]
+            assert np.all(env.rate_command == 0.0) and env.command_schedule["duration"] == 3.0
+        else:
+            cmd[i] = env.sine_params["amplitudes"]; freq[i] = env.sine_params["frequency"]
+            assert np.all(env.rate_command == 0.0)
+    env_hist = np.stack([np.histogram(env_q[:, j], bins=ENV_BINS, range=ENVELOPE_SUPPORT[j])[0] for j in range(8)])
+    assert env_hist.sum() == 8 * R                                     # nothing outside the stated support
+    active = cmd != 0.0
+    subset = np.bincount((active * np.array([1, 2, 4])).sum(axis=1), minlength=8)
+    norm = np.abs(cmd) / ((0.5 if ctype == "sine" else 1.0) * scale * max_rates)        # U(0.3, 1) where active
+    mag_hist = np.stack([np.histogram(norm[active[:, a], a], bins=MAG_BINS, range=(0.3, 1.0))[0] for a in range(3)])
+    assert mag_hist.sum() == active.sum()
+    out = dict(n=np.array(R), env_hist=env_hist, env_corr=np.corrcoef(env_q.T), subset=subset,
+               active=active.sum(axis=0), positive=(cmd > 0).sum(axis=0), mag_hist=mag_hist,
+               mag_mean=np.array([norm[active[:, a], a].mean() for a in range(3)]))
+    if ctype == "sine":
+        out["freq_hist"] = np.histogram(freq, bins=MAG_BINS, range=(0.1, 2.0))[0]
+        assert out["freq_hist"].sum() == R
+    return out
+
+
+def _walk_distribution_worker(args):
+    """RateCommandGenerator.generate_random_walk(dt=0.02) (generators.py:145-164), R calls: the delta per axis, normalised by
+    diffusion * sqrt(dt) * difficulty_scale * max_rate, is a standard normal."""
+    from learned_controllers.data.generators import RateCommandGenerator
+    difficulty, seed, R = args
+    scale = {"easy": 0.3, "medium": 0.5, "hard": 0.7}[difficulty]
+    gen = RateCommandGenerator(difficulty=difficulty, rng_seed=seed)
+    d = np.stack([gen.generate_random_walk(dt=0.02)[0] for _ in range(R)])
+    z = d / (0.1 * np.sqrt(0.02) * scale * gen._max_rates)
+    return dict(n=np.array(R), delta_std=d.std(axis=0), delta_mean=d.mean(axis=0),
+                z_hist=np.stack([np.histogram(z[:, a], bins=Z_BINS, range=(-Z_RANGE, Z_RANGE))[0] for a in range(3)]),
+                z_outside=np.array(int((np.abs(z) >= Z_RANGE).sum())), z_corr=np.corrcoef(z.T))
+
+
+def gen_reset_distributions(pool):
+    """What the reference's FlightEnvelopeSampler / RateCommandGenerator / RateControlEnv._generate_new_command DRAW
+    (generators.py:47-164,190-214; rate_env.py:302-340), 100 000 resets per (difficulty, command type): the pin for the
+    Philox reset sampler, whose stream cannot replay MT19937 (RNG row, item ii)."""
+    R = 100_000
+    combos = [(d, c) for d in ("easy", "medium", "hard") for c in ("step", "ramp", "sine")]
+    res = pool.map(_reset_distribution_worker, [(d, c, 7000 + k, R) for k, (d, c) in enumerate(combos)])
+    out = {"combos": np.array([f"{d}/{c}" for d, c in combos]), "env_support": np.array(ENVELOPE_SUPPORT),
+           "env_hist": sum(r["env_hist"] for r in res), "env_n": np.array(R * len(combos)),
+           "env_corr_max_offdiag": np.array(max(float(np.max(np.abs(r["env_corr"] - np.eye(8)))) for r in res))}
+    for (d, c), r in zip(combos, res):
+        for key, v in r.items():
+            if key not in ("env_hist", "env_corr"):
+                out[f"{d}/{c}/{key}"] = v
+        print("reset distribution", d, c, "subsets", r["subset"].tolist(), "positive/active", r["positive"].tolist(), r["active"].tolist())
+    walk = pool.map(_walk_distribution_worker, [(d, 7100 + k, 400_000) for k, d in enumerate(("easy", "medium", "hard"))])
+    for d, r in zip(("easy", "medium", "hard"), walk):
+        for key, v in r.items():
+            out[f"{d}/walk/{key}"] = v
+        print("random walk", d, "delta std", r["delta_std"], "outside", int(r["z_outside"]))
+    np.savez_compressed(os.path.join(HERE, "reset_distributions.npz"), **out)
+
+
 # ------------------------------------------------------------------------------------------------
 def _hsa_worker(args):
     """HSAAgent closed loop through the backend (tests/test_control_integration.py:435-540 shape)."""
@@ -481,13 +657,15 @@ def gen_telemetry():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "guidance", "sensor", "telemetry"]
+    which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "env_random", "reset_dist", "guidance", "sensor", "telemetry"]
     with mp.Pool(8) as pool:
         if "pid" in which: gen_pid_kat()
         if "dyn" in which: gen_dynamics_kat()
         if "open" in which: gen_open_loop(pool)
         if "cascade" in which: gen_cascade(pool)
         if "env" in which: gen_env(pool)
+        if "env_random" in which: gen_env_random(pool)
+        if "reset_dist" in which: gen_reset_distributions(pool)
         if "guidance" in which: gen_guidance(pool)
         if "sensor" in which: gen_sensor()
         if "telemetry" in which: gen_telemetry()

@@ -82,7 +82,7 @@ def test_env_vs_oracle_with_auto_reset(mods, controller, steps):
     torch, acb200, orc = mods
     n = 2048
     rng = np.random.default_rng(7)
-    ct = (np.arange(n) % 3).astype(np.uint8)                       # step / ramp / sine (random walk: distribution test)
+    ct = (np.arange(n) % 4).astype(np.uint8)                       # step / ramp / sine / random walk
     diff = np.array([0.3, 0.5, 0.7], np.float32)[rng.integers(0, 3, n)]
     # the attitude cascade keeps every aircraft inside the envelope: shorten its episodes so that truncation
     # exercises the in-kernel auto-reset too
@@ -136,3 +136,53 @@ def test_env_vs_oracle_with_auto_reset(mods, controller, steps):
         assert np.allclose(got[[0, 3, 4, 5, 15]], rst[[0, 3, 4, 5, 15]])
         assert np.allclose(got[[1, 6, 7, 8, 9, 10, 11, 12, 13]], rst[[1, 6, 7, 8, 9, 10, 11, 12, 13]], rtol=1e-9, atol=1e-6)
     print(f"{controller}: worst state rel err {worst:.3e}, {done_total} episodes finished, {diverged} aircraft left bit-identity")
+
+
+@pytest.mark.parametrize("controller", ["rate_pid", "external"])
+def test_random_walk_command_vs_oracle(mods, controller):
+    """command_type="random" (rate_env.py:333-336,358-365; generators.py:145-164) on 2048 aircraft: the kernel's per-step
+    Philox / Box-Muller draw and clipped walk against the restatement on the shared stream.  The restatement itself is
+    pinned on the reference's own normals (tests/test_oracle_golden.py::test_rate_env_random_walk_episodes) and the stream
+    on the reference's randn distribution (tests/test_reset_sampler.py)."""
+    torch, acb200, orc = mods
+    n = 2048
+    rng = np.random.default_rng(3)
+    diff = np.array([0.3, 0.5, 0.7], np.float32)[np.arange(n) % 3]
+    env = acb200.BatchedRateControlEnv(n, controller=controller, precision=64, seed=77, id_offset=4096, command_type=3,
+                                       episode_length=4.0)
+    env.set_curriculum(torch.as_tensor(diff), "random")
+    ref = orc.Env(n, controller=acb200.envs.CONTROLLERS[controller], seed=77, id_offset=4096, difficulty=diff,
+                  command_type=orc.CMD_RANDOM, episode_length=4.0)
+    env.reset(); ref.reset()
+    assert torch.all(env.rate_cmd == 0)
+    max_rates = np.radians([180.0, 180.0, 160.0])[:, None]
+    worst, moved, done_total = 0.0, 0, 0
+    ok = np.ones(n, bool)
+    for t in range(450):                       # 200-step episodes: every aircraft restarts its walk at least twice
+        a = None
+        if controller == "external":
+            a = (rng.uniform(-1, 1, (n, 4)) * 0.03).astype(np.float32); a[:, 3] = 0.6
+        obs, rew, term, trunc = env.step(None if a is None else torch.as_tensor(a, device="cuda"))
+        robs, rrew, rterm, rtrunc = ref.step(a)
+        gterm, gtrunc = term.cpu().numpy(), trunc.cpu().numpy()
+        same = (gterm == rterm) & (gtrunc == rtrunc)
+        if controller == "rate_pid":
+            same &= np.all(env.pid.cpu().numpy().view(np.uint32) == ref.pid.view(np.uint32), axis=0)
+        ok &= same
+        cmd, rcmd = env.rate_cmd.cpu().numpy(), ref.rate_cmd
+        # the command does not depend on the flight: it is compared for EVERY aircraft that is in the same episode step
+        e = np.max(np.abs(cmd - rcmd) / max_rates, axis=0)
+        in_step = env.step_count.cpu().numpy() == ref.step_count
+        worst = max(worst, float(e[in_step].max()))
+        assert (e[in_step] <= 1e-12).all(), f"step {t + 1}: command err {e[in_step].max():.3e}"
+        assert np.all(np.abs(cmd) <= max_rates)
+        moved += int(np.sum(np.any(cmd != 0, axis=0)))
+        se = rel_err_cols(env.state.cpu().numpy(), ref.state)
+        assert (se[ok] <= TOL).all(), f"step {t + 1}: state err {se[ok].max():.3e}"
+        assert np.max(np.abs(rew.cpu().numpy()[ok] - rrew[ok])) <= 1e-7
+        done = (rterm | rtrunc).astype(bool)
+        done_total += int(done.sum())
+        ok |= done & (gterm == rterm) & (gtrunc == rtrunc)
+    assert done_total >= n and moved > 0.9 * n * 400
+    assert ok.mean() >= 0.97, ok.mean()
+    print(f"random walk / {controller}: worst command err {worst:.3e}, {done_total} episodes, {int((~ok).sum())} aircraft out of bit-identity")

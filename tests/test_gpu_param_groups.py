@@ -108,3 +108,37 @@ def test_argument_errors():
     assert lib.acb200_env_step_range(h, C.byref(env.c), C.byref(env.cfg), None, 64, 64) == acb200._cabi.EVALUE
     assert lib.acb200_env_step_range(h, C.byref(env.c), C.byref(env.cfg), None, 384, 256) == acb200._cabi.EVALUE
     assert lib.acb200_env_step_range(h, C.byref(env.c), C.byref(env.cfg), None, 128, 0) == 0
+
+
+def test_host_step_and_vecenv_honour_the_groups_and_failed_validation_changes_nothing():
+    """the groups live in the context (acb200_set_param_groups), so step_host -- and every
+    B200VecEnv.step -- flies the same aircraft as step(); a rejected group list leaves groups and parameters untouched."""
+    import acb200
+    n, bounds = 1024, [0, 256, 640, 1024]
+    base = acb200.default_aircraft_params()
+    groups = acb200.envs.randomize_aircraft_params(base, 3, spread=0.25, seed=9)
+    mk = lambda: acb200.BatchedRateControlEnv(n, controller="rate_pid", precision=32, seed=4)
+    a, b, plain = mk(), mk(), mk()
+    a.set_param_groups(groups, bounds); b.set_param_groups(groups, bounds)
+    bad = acb200.default_aircraft_params(); bad.mass = -1.0
+    with pytest.raises(ValueError, match="Mass must be positive"):
+        b.set_param_groups([groups[1], bad])                         # rejected as a whole
+    got = acb200._cabi.AircraftParamsC()
+    assert b.ctx.lib.acb200_get_aircraft_params(b.ctx.handle, C.byref(got)) == 0 and bytes(got) == bytes(base)
+    a.reset(); b.reset(); plain.reset()
+    pin = lambda *shape, dt=torch.float32: torch.empty(shape, dtype=dt).pin_memory()
+    obs_h, rew_h, te_h, tr_h = pin(n, 18), pin(n), pin(n, dt=torch.uint8), pin(n, dt=torch.uint8)
+    for _ in range(25):
+        a.step(); plain.step()
+        b.step_host(None, obs_h, rew_h, te_h, tr_h)
+    torch.cuda.synchronize()
+    assert torch.equal(a.state, b.state) and torch.equal(a.obs.cpu(), obs_h) and torch.equal(a.reward.cpu(), rew_h)
+    assert torch.equal(a.state[:, :256], plain.state[:, :256]) and not torch.equal(a.state[:, 256:], plain.state[:, 256:])
+    # outputs are optional: nothing but reward + flags leaves the device, results unchanged
+    a.step(); b.step_host(None, None, rew_h, te_h, None)
+    assert torch.equal(a.reward.cpu(), rew_h) and torch.equal(a.terminated.cpu(), te_h) and torch.equal(a.state, b.state)
+    # a fleet of another size under the same context is refused, not silently simulated with the wrong split
+    other = acb200.BatchedRateControlEnv(512, controller="rate_pid", precision=32, ctx=a.ctx)
+    other.reset()
+    with pytest.raises(ValueError):
+        other.step()

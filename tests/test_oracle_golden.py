@@ -173,6 +173,50 @@ def test_rate_env_episodes():
         assert bool(term[0]) or bool(trunc[0]) or T == 500
 
 
+def test_rate_env_random_walk_episodes():
+    """command_type="random" (rate_env.py:333-336,358-365; generators.py:145-164): the reference's own MT19937 randn(3) values,
+    recorded per step, are replayed through the restatement's hook -- the command after the clip must match to 1e-12, the
+    rest of the step to the usual bars.  Cases: external / rate-PID / residual control x easy / medium / hard; the hard cases
+    are pushed to the command limit at step `boost` so that the clip is exercised."""
+    g = _load("rate_env_random.npz")
+    max_rates = np.radians([180.0, 180.0, 160.0])
+    clip_hits = 0
+    for k in range(int(g["n_cases"])):
+        seed, scale, ctype, ctrl = g[f"c{k}_meta"]
+        assert int(ctype) == orc.CMD_RANDOM
+        env = orc.Env(1, controller=int(ctrl), difficulty=float(scale), command_type=orc.CMD_RANDOM, auto_reset=False)
+        env.state[:, 0] = g[f"c{k}_s0"]
+        env.derived[:, 0] = orc.derived(np.ascontiguousarray(g[f"c{k}_s0"][:12]))
+        env.prev_action[:, 0] = [0, 0, 0, 0.5]
+        acts, T, boost = g[f"c{k}_actions"], len(g[f"c{k}_reward"]), int(g[f"c{k}_boost"])
+        for t in range(T):
+            if boost and t == boost:
+                env.rate_cmd[:, 0] = np.array([0.999, -0.999, 0.999]) * max_rates
+            a = acts[t][None, :] if int(ctrl) in (0, 3) else None
+            obs, rew, term, trunc = env.step(a, walk_z=g[f"c{k}_walk_z"][t][:, None])
+            ctx = f"random-walk case {k} step {t + 1}"
+            assert rel_err(env.rate_cmd[:, 0], g[f"c{k}_rate_cmd"][t]) <= 1e-12, ctx
+            assert rel_err(env.state[:, 0], g[f"c{k}_states"][t]) <= TOL, ctx
+            assert rel_err(obs[0], g[f"c{k}_obs"][t]) <= 2e-7, ctx
+            assert abs(rew[0] - g[f"c{k}_reward"][t]) <= 1e-7, (ctx, rew[0], g[f"c{k}_reward"][t])
+            assert bool(term[0]) == bool(g[f"c{k}_terminated"][t]) and bool(trunc[0]) == bool(g[f"c{k}_truncated"][t]), ctx
+            assert bool(env.is_settled[0]) == bool(g[f"c{k}_is_settled"][t]), ctx
+            comp, exp = env.components[:, 0], g[f"c{k}_components"][t]
+            assert np.allclose(comp[:5], exp[:5], rtol=0, atol=1e-7), ctx
+            assert abs((comp[5] + comp[7]) - exp[5]) <= 1e-7 and comp[6] == exp[6], ctx
+            if int(ctrl) == 1:
+                assert np.array_equal(env.prev_action[:, 0], acts[t]), ctx
+            clip_hits += int(np.sum(np.abs(env.rate_cmd[:, 0]) == max_rates))
+        assert bool(term[0]) or bool(trunc[0]) or T == 500
+    assert clip_hits > 50, "the fixture must exercise the command clip"
+
+
+def test_difficulty_scale_is_the_reference_python_float():
+    """generators.py:41-45: 0.3 / 0.5 / 0.7 as Python floats; the fleet stores float32 ((double)0.3f is 4e-8 off)."""
+    for v in (0.3, 0.5, 0.7):
+        assert orc.difficulty_scale(np.float32(v)) == v
+
+
 def test_hsa_agent_trajectories():
     """Level 2: HSAAgent (heading PID -> bank, TECS energy/balance PIDs -> throttle/pitch) closed loop, 3000 control steps."""
     g = _load("hsa_agent.npz")
