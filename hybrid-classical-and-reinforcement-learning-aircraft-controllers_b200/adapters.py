@@ -30,6 +30,18 @@ class ControlMode(enum.IntEnum):           # controllers/types.py:9-24
     RATE = 4
     SURFACE = 5
 
+    # equal to the reference's own (non-int) ``ControlMode`` members of the same value, so that either side's objects can be
+    # compared with ``==`` (reference tests assert ``agent.get_control_level() == ControlMode.RATE`` with THEIR enum)
+    def __eq__(self, other):
+        v = getattr(other, "value", other)
+        return int(self) == v if isinstance(v, int) else NotImplemented
+
+    def __ne__(self, other):
+        r = self.__eq__(other)
+        return r if r is NotImplemented else not r
+
+    __hash__ = int.__hash__
+
 
 @dataclass
 class AircraftState:                       # controllers/types.py:27-96
@@ -98,12 +110,36 @@ class PIDGains:                            # controllers/types.py:277-291
 
 
 @dataclass
-class ControllerConfig:                    # controllers/types.py:294-350 (the fields the attitude/rate/surface levels read)
+class Waypoint:                            # controllers/types.py:99-132
+    north: float
+    east: float
+    down: float
+    speed: Optional[float] = None
+    heading: Optional[float] = None
+
+    @property
+    def altitude(self) -> float:
+        return -self.down
+
+    @classmethod
+    def from_ned(cls, north, east, down, **kw):
+        return cls(north=north, east=east, down=down, **kw)
+
+    @classmethod
+    def from_altitude(cls, north, east, altitude, **kw):
+        return cls(north=north, east=east, down=-altitude, **kw)
+
+
+@dataclass
+class ControllerConfig:                    # controllers/types.py:294-350
     roll_angle_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=8.0, ki=2.0, kd=0.3))
     pitch_angle_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=6.0, ki=1.5, kd=0.2))
     roll_rate_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=1.3, ki=0.4, kd=0.012))
     pitch_rate_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=0.6, ki=0.2, kd=0.008))
     yaw_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=1.6, ki=0.15, kd=0.01))
+    heading_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=1.0, ki=0.05, kd=0.2))      # only i_limit is read (hsa_agent.py:64-65)
+    speed_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=0.1, ki=0.01, kd=0.0))
+    altitude_gains: PIDGains = field(default_factory=lambda: PIDGains(kp=0.2, ki=0.01, kd=0.1))
     max_roll: float = 30.0          # degrees
     max_pitch: float = 30.0
     max_roll_rate: float = 180.0    # degrees / s
@@ -111,6 +147,10 @@ class ControllerConfig:                    # controllers/types.py:294-350 (the f
     max_yaw_rate: float = 160.0
     rate_loop_dt: float = 0.001
     dt: float = 0.01
+    max_bank_angle_hsa: float = 25.0
+    baseline_throttle: float = 0.1
+    waypoint_acceptance_radius: float = 40.0
+    proportional_navigation_gain: float = 3.0
 
 
 def _same_mode(a, b) -> bool:

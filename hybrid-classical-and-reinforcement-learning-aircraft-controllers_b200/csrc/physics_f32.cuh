@@ -242,15 +242,21 @@ __device__ __forceinline__ bool substep_angles_in_sfu_range(const DynParams<floa
 }
 
 // One RK4 substep (:248-254) and the post-step clamps (:258-291).
-template <bool GUARDED>
+// MASKED (cold path only, backend_step_f32_nan_controls): derivative words whose bit is set in `mask` are zeroed after every
+// stage -- what the reference's nan_to_num (:496-501) does to the words a NaN control surface poisons.
+template <bool GUARDED, bool MASKED = false>
 __device__ __forceinline__ int rk4_step_f32_impl(const DynParams<float>& P, const HeldControlsF32& H, float (&s)[12], float& time,
-                                                 float dt) {
+                                                 float dt, unsigned mask = 0u) {
     float k[12], acc[12], t[12];
     const float half_dt = 0.5f * dt;
     float sphi, cphi, sth, cth, spsi, cpsi;
     // stage 1 at the state itself
     FastF32::attitude_trig<GUARDED>(s[6], s[7], s[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
     dynamics_f32(P, H, s, sphi, cphi, sth, cth, spsi, cpsi, k);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 3; i < 12; ++i) k[i] = ((mask >> i) & 1u) ? 0.0f : k[i];
+    }
 #pragma unroll
     for (int i = 0; i < 12; ++i) acc[i] = k[i];
     // stages 2-4 at s + a k; weights 2, 2, 1.  Rolled: one more copy of the derivative code in the
@@ -267,6 +273,10 @@ __device__ __forceinline__ int rk4_step_f32_impl(const DynParams<float>& P, cons
         for (int i = 0; i < 12; ++i) t[i] = fmaf(a, k[i], s[i]);
         FastF32::attitude_trig<GUARDED>(t[6], t[7], t[8], &sphi, &cphi, &sth, &cth, &spsi, &cpsi);
         dynamics_f32(P, H, t, sphi, cphi, sth, cth, spsi, cpsi, k);
+        if (MASKED) {
+#pragma unroll
+            for (int i = 3; i < 12; ++i) k[i] = ((mask >> i) & 1u) ? 0.0f : k[i];
+        }
 #pragma unroll
         for (int i = 0; i < 12; ++i) acc[i] = fmaf(wgt, k[i], acc[i]);
     }
@@ -327,9 +337,57 @@ static __device__ __noinline__ int rk4_step_f32_guarded(const DynParams<float>& 
     return repaired;
 }
 
+// A NaN held control (np.clip and set_controls let NaN through, simplified_6dof.py:221-226; +-inf are clipped to a bound)
+// poisons, in the reference's _dynamics, exactly the derivative words that control enters, and nan_to_num zeroes them
+// (:496-501): elevator -> CL -> Fx, Fz and the pitch moment (u', w', q'); aileron -> roll moment (p'); rudder -> side force and
+// yaw moment (v', r'); throttle -> thrust (u').  Those words then stay frozen for the whole control step while the rest of
+// the state integrates on.  fminf / fmaxf clamps would instead turn the NaN into a saturated acceleration, so a
+// control step with a NaN control leaves the hot loop: this cold function evaluates the derivative with the control at 0 and
+// zeroes the poisoned words after every stage.  Returns the number of zeroed derivative words per substep, summed (they are
+// counted in the env's nonfinite_repairs statistic like the reference's logged "NaN/Inf detected in derivatives").
+__device__ __forceinline__ unsigned nan_control_mask(const float (&c)[4]) {
+    unsigned m = 0u;
+    if (c[0] != c[0]) m |= (1u << 3) | (1u << 5) | (1u << 10);
+    if (c[1] != c[1]) m |= (1u << 9);
+    if (c[2] != c[2]) m |= (1u << 4) | (1u << 11);
+    if (c[3] != c[3]) m |= (1u << 3);
+    return m;
+}
+static __device__ __noinline__ int backend_step_f32_nan_controls(const DynParams<float>& P, float* s, float* time, const float* c,
+                                                                 int K, float h) {
+    float cc[4], x[12], t = *time;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) cc[i] = c[i];
+    const unsigned mask = nan_control_mask(cc);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) cc[i] = (cc[i] != cc[i]) ? 0.0f : cc[i];
+    const HeldControlsF32 H = hold_controls(P, cc);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) x[i] = s[i];
+    int repaired = 0;
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) repaired += rk4_step_f32_impl<true, true>(P, H, x, t, h, mask) + __popc(mask);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) s[i] = x[i];
+    *time = t;
+    return repaired;
+}
+
 // SimulationAircraftBackend.step for the throughput build: K substeps of h under zero-order hold.
 __device__ __forceinline__ int backend_step(const DynParams<float>& P, float (&s)[12], float& time, const float (&c)[4], int K,
                                             float h) {
+    if (fmaf(0.0f, c[0], fmaf(0.0f, c[1], fmaf(0.0f, c[2], 0.0f * c[3]))) != 0.0f) {     // a NaN control: cold path
+        float tmp[12], cc[4], tt = time;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) tmp[i] = s[i];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cc[i] = c[i];
+        const int r = backend_step_f32_nan_controls(P, tmp, &tt, cc, K, h);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) s[i] = tmp[i];
+        time = tt;
+        return r;
+    }
     const HeldControlsF32 H = hold_controls(P, c);
     int repaired = 0;
 #pragma unroll 1

@@ -271,10 +271,47 @@ __device__ __forceinline__ int rk4_step_f32x2(const DynParams<float>& P, const H
     return repaired;
 }
 
+static __device__ __noinline__ int backend_step2_lanes(const DynParams<float>& P, v2* s, const float* c0, const float* c1, int K, float h) {
+    int repaired = 0;
+#pragma unroll 1
+    for (int l = 0; l < 2; ++l) {
+        float x[12], c[4], time = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 12; ++i) x[i] = l ? s[i].y : s[i].x;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) c[i] = l ? c1[i] : c0[i];
+        repaired += backend_step(P, x, time, c, K, h);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) { if (l) s[i].y = x[i]; else s[i].x = x[i]; }
+    }
+    return repaired;
+}
+__device__ __forceinline__ int backend_step2_cold(const DynParams<float>& P, v2 (&s)[12], const float (&c0)[4], const float (&c1)[4],
+                                                  int K, float h) {
+    v2 tmp[12];
+    float a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) tmp[i] = s[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i] = c0[i]; b[i] = c1[i]; }
+    const int r = backend_step2_lanes(P, tmp, a, b, K, h);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) s[i] = tmp[i];
+    return r;
+}
+
 // K substeps of h under zero-order hold for the pair (simulation_backend.py:95-99).
 // The simulation time (t += h per substep, :254) is advanced by the caller: nothing in the substep reads it.
 __device__ __forceinline__ int backend_step2(const DynParams<float>& P, v2 (&s)[12], const float (&c0)[4],
                                              const float (&c1)[4], int K, float h) {
+    // a NaN control in either lane: both lanes take the one-aircraft code for this control step (physics_f32.cuh,
+    // backend_step_f32_nan_controls) -- the same bits as the one-aircraft kernel, nothing added to the hot loop
+    {
+        float chk = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) chk = fmaf(0.0f, c0[i], fmaf(0.0f, c1[i], chk));
+        if (chk != 0.0f) return backend_step2_cold(P, s, c0, c1, K, h);
+    }
     const HeldControlsF32x2 H = hold_controls2(P, c0, c1);
     int repaired = 0;
 #pragma unroll 1

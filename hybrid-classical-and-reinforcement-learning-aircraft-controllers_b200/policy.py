@@ -102,6 +102,11 @@ class LearnedPolicyB200:
         if self.recurrent:
             self.h_state.zero_(); self.c_state.zero_()
 
+    def _bind_stream(self):
+        """Enqueue on torch's CURRENT stream (as envs._bind_stream does): with a policy-owned context a caller that
+        switches streams would otherwise race the producer of obs and the consumer of the action."""
+        self.ctx.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
     def _flags(self, t):
         if t is None:
             return None
@@ -123,6 +128,7 @@ class LearnedPolicyB200:
         out = self.action if out is None else out
         if not (out.is_cuda and out.dtype == torch.float32 and out.is_contiguous() and tuple(out.shape) == (self.n, ACT_DIM)):
             raise ValueError(f"out must be a contiguous CUDA float32 tensor of shape ({self.n}, {ACT_DIM})")
+        self._bind_stream()
         self.ctx.check(self.lib.acb200_policy_forward(
             self.ctx.handle, self.handle, self.n, obs.data_ptr(), es.data_ptr() if es is not None else None,
             es_b.data_ptr() if es_b is not None else None, self.h_state.data_ptr() if self.recurrent else None, self.c_state.data_ptr() if self.recurrent else None,
@@ -168,6 +174,7 @@ class LearnedPolicyB200:
     def get_lstm_states(self):
         h = torch.empty((self.n, HIDDEN), dtype=torch.float32, device=self.device)
         c = torch.empty_like(h)
+        self._bind_stream()
         self.ctx.check(self.lib.acb200_policy_state_export(self.ctx.handle, self.handle, self.n, self.h_state.data_ptr(),
                                                            self.c_state.data_ptr(), h.data_ptr(), c.data_ptr()))
         return h.cpu().numpy()[None], c.cpu().numpy()[None]
@@ -175,6 +182,7 @@ class LearnedPolicyB200:
     def set_lstm_states(self, h, c) -> None:
         ht = torch.as_tensor(np.asarray(h, np.float32).reshape(self.n, HIDDEN)).to(self.device).contiguous()
         ct = torch.as_tensor(np.asarray(c, np.float32).reshape(self.n, HIDDEN)).to(self.device).contiguous()
+        self._bind_stream()
         self.ctx.check(self.lib.acb200_policy_state_import(self.ctx.handle, self.handle, self.n, ht.data_ptr(), ct.data_ptr(),
                                                            self.h_state.data_ptr(), self.c_state.data_ptr()))
         self.ctx.synchronize()

@@ -656,7 +656,51 @@ def gen_telemetry():
     print("telemetry.json", len(text), "bytes")
 
 
+def gen_policy_features():
+    """The half of the learned policy that lives in the reference: LSTMFeaturesExtractor (networks/lstm_policy.py:13-97)
+    run as it is (its SB3 base class comes from oracle/sb3_stub.py: an nn.Module that stores features_dim), plus what
+    LSTMPolicy / SimpleMLPPolicy.get_policy_kwargs (:107-164) hand to sb3-contrib.  The fixture keeps the extractor's
+    state_dict (torch default init under manual_seed(0)), 512 observations, the features of the single-step call and of
+    a 3-step sequence call (the [:, -1, :] branch, :88-91)."""
+    import torch
+    from gymnasium import spaces
+    from learned_controllers.networks.lstm_policy import LSTMFeaturesExtractor, LSTMPolicy, SimpleMLPPolicy
+    sys.path.insert(0, os.path.join(HERE, "..", ".."))
+    from oracle.policy_oracle import synthetic_obs
+    torch.manual_seed(0)
+    space = spaces.Box(low=-np.inf, high=np.inf, shape=(18,), dtype=np.float32)
+    kw = LSTMPolicy.get_policy_kwargs()
+    assert kw["features_extractor_class"] is LSTMFeaturesExtractor
+    fe = kw["features_extractor_class"](space, **kw["features_extractor_kwargs"]).eval()
+    obs = synthetic_obs(512, seed=123)
+    seq = torch.stack([synthetic_obs(64, seed=200 + t) for t in range(3)], dim=1)          # [64, 3, 18]
+    # the sequence branch needs weight_hh (h is non-zero from the second step on): pinned on a SMALL instance of the same
+    # class (hidden 32, features 16) whose whole state_dict is a few kB
+    small = LSTMFeaturesExtractor(space, features_dim=16, lstm_hidden_size=32, n_lstm_layers=2).eval()
+    with torch.no_grad():
+        feats = fe(obs); feats_seq = small(seq); feats_small = small(obs[:64])
+    out = {"obs": obs.numpy(), "features": feats.numpy(), "obs_seq": seq.numpy(), "features_seq": feats_seq.numpy(), "features_small": feats_small.numpy(),
+           "features_dim": np.array(fe.features_dim),
+           "lstm_kwargs": np.array([kw["features_extractor_kwargs"][k] for k in ("features_dim", "lstm_hidden_size", "n_lstm_layers")]),
+           "lstm_pi": np.array(kw["net_arch"]["pi"]), "lstm_vf": np.array(kw["net_arch"]["vf"]),
+           "lstm_activation": np.array(kw["activation_fn"].__name__),
+           "mlp_pi": np.array(SimpleMLPPolicy.get_policy_kwargs()["net_arch"]["pi"]),
+           "mlp_activation": np.array(SimpleMLPPolicy.get_policy_kwargs()["activation_fn"].__name__),
+           "torch_version": np.array(torch.__version__)}
+    for k, v in fe.state_dict().items():
+        if "weight_hh" in k:        # 2 MB that only ever multiply h0 = 0 (no state is passed, :86): the test loads random ones
+            continue
+        out["sd/" + k] = v.numpy()
+    for k, v in small.state_dict().items():
+        out["small/" + k] = v.numpy()
+    np.savez_compressed(os.path.join(HERE, "policy_features.npz"), **out)
+    print("policy_features", feats.shape, "state_dict", [k for k in fe.state_dict()], "|features| max", float(feats.abs().max()))
+
+
 if __name__ == "__main__":
+    if "policy" in sys.argv[1:]:
+        gen_policy_features()
+        sys.exit(0)
     which = sys.argv[1:] or ["pid", "dyn", "open", "cascade", "env", "env_random", "reset_dist", "guidance", "sensor", "telemetry"]
     with mp.Pool(8) as pool:
         if "pid" in which: gen_pid_kat()

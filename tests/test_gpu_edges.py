@@ -88,3 +88,52 @@ def test_non_finite_observation_stays_in_its_row():
     keep = torch.ones(n, dtype=torch.bool, device="cuda"); keep[5] = False; keep[200] = False
     assert torch.equal(dirty[keep], clean[keep])
     assert not torch.isfinite(dirty[5]).all()
+
+
+def test_nan_action_freezes_the_poisoned_derivatives_in_both_builds(monkeypatch):
+    """a NaN action passes np.clip and set_controls as NaN (rate_env.py:225, simplified_6dof.py:221-226); the
+    reference's _dynamics then zeroes exactly the derivative words that control enters (nan_to_num, :496-501) -- those state
+    words stay frozen over the control step, everything else integrates on.  The fp64 build does that op for op (checked
+    against the oracle); the fp32 build takes a cold path that must agree with it to the fp32 per-step tolerance instead of
+    saturating the accelerations (fminf/fmaxf clamps map NaN to a bound), counts the repairs, and stays bit-identical
+    between the pair and the one-aircraft kernel."""
+    import acb200
+    from oracle import oracle as orc
+    n = 512
+    rng = np.random.default_rng(17)
+    act = (rng.uniform(-1, 1, (n, 4)) * 0.05).astype(np.float32); act[:, 3] = 0.6
+    slot = np.arange(n) % 8                       # slots 0..3: that control is NaN; 4: all four; 5..7: healthy aircraft
+    for k in range(4):
+        act[slot == k, k] = np.nan
+    act[slot == 4] = np.nan
+    a_t = torch.as_tensor(act, device="cuda")
+    mk = lambda prec: acb200.BatchedRateControlEnv(n, controller="external", precision=prec, seed=21, auto_reset=False)
+    e64, e32 = mk(64), mk(32)
+    ref = orc.Env(n, controller=orc.CTRL_EXTERNAL, seed=21, auto_reset=False)
+    e64.reset(); e32.reset(); ref.reset()
+    before = e64.state.clone()
+    for _ in range(2):
+        e64.step(a_t); e32.step(a_t); ref.step(act)
+    s64, s32 = e64.state.cpu().numpy(), e32.state.double().cpu().numpy()
+    assert np.max(np.abs(s64 - ref.state) / np.maximum(np.abs(ref.state), 1.0)) <= 1e-9
+    err = np.abs(s32 - s64) / np.maximum(np.abs(s64), 1.0)
+    assert err.max() <= 2e-5, err.max()
+    # frozen words: elevator (env action slot 1) -> u, w, q; aileron (slot 0) -> p; rudder (slot 2) -> v, r; throttle -> u
+    b = before.cpu().numpy()
+    for sl, words in ((0, [9]), (1, [3, 5, 10]), (2, [4, 11]), (3, [3]), (4, [3, 4, 5, 9, 10, 11])):
+        m = slot == sl
+        assert np.array_equal(s64[np.ix_(words, np.where(m)[0])], b[np.ix_(words, np.where(m)[0])])
+        assert np.array_equal(e32.state.cpu().numpy()[np.ix_(words, np.where(m)[0])], before.float().cpu().numpy()[np.ix_(words, np.where(m)[0])])
+    assert np.all(np.isfinite(s32))
+    st = e32.episode_stats()
+    assert st["nonfinite_repairs"] > 0
+    # pair kernel == one-aircraft kernel, bit for bit, with NaN actions in one or both lanes
+    monkeypatch.setenv("ACB200_ENV_PAIR", "0")
+    e1 = mk(32); e1.reset()
+    for _ in range(2):
+        e1.step(a_t)
+    for name in ("state", "obs", "prev_action", "derived"):
+        x, y = getattr(e32, name), getattr(e1, name)
+        assert torch.equal(torch.nan_to_num(x, nan=-77.0), torch.nan_to_num(y, nan=-77.0)), name
+    rw, r1 = e32.reward, e1.reward
+    assert torch.equal(torch.isnan(rw), torch.isnan(r1)) and torch.equal(rw[~torch.isnan(rw)], r1[~torch.isnan(r1)])

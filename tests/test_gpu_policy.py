@@ -19,8 +19,12 @@ F32_TOL = 5e-3      # LSTM policy: max |action - fp32 oracle|                   
 # The MLP policy has no gates: the raw observation (altitude ~100 m, airspeed ~20 m/s) drives hidden activations to
 # O(30), and ONE bf16 rounding of such an activation is 0.06 -- an fp32-accumulation-order difference of one ulp that
 # flips a rounding already moves the action by ~3e-3.  Its bars are therefore wider (measured 2.6e-3 / 1.0e-2, r01).
-EMU_TOL_MLP = 1.5e-2
-F32_TOL_MLP = 5e-2  # SURVEY.md §8 suggested "<= 2e-2 abs on actions for bf16"; it holds for the LSTM policy only
+# r02: both bars narrowed to what SURVEY.md 8c asks for bf16 ("<= 2e-2 abs on actions").  A CPU study with the emulated
+# forward (hi+lo split of the first hidden layer's activations and of its weights as well) showed the 1e-2 is spread over
+# EVERY layer of the un-normalised net (relative bf16 precision 2^-9 of pre-clip actions of a few units), not the first one:
+# the split moved 1.1e-2 to 1.0e-2, so it was not built.
+EMU_TOL_MLP = 8e-3
+F32_TOL_MLP = 2e-2
 
 
 def _policy(kind, n, seed=0, scale=1.0):
