@@ -128,11 +128,36 @@ class B200VecEnv:
         lookup = {int(i): k for k, i in enumerate(finished)}
         elapsed = time.time() - self._t0
 
+        # The reference's per-step info keys (rate_env.py:410-435): time, step, position, rate_command, rate_error, airspeed,
+        # altitude, is_settled.  Pulled from the device ONCE per step and only if some info dict is actually built.  For an
+        # aircraft that finished this step the device already holds the NEW episode (SB3 auto-reset), so its values are
+        # rebuilt from what was kept of the old one: the terminal observation (float32) and the episode length; the
+        # terminal position is not kept anywhere and reads NaN.
+        env, dt = self.env, self.env.dt
+        cache = {}
+
+        def extras():
+            if not cache:
+                st = env.state.double().cpu().numpy()
+                cache.update(time=env.env_time.double().cpu().numpy(), step=env.step_count.cpu().numpy(), pos=st[0:3],
+                             cmd=env.rate_cmd.double().cpu().numpy(), rates=st[9:12], der=env.derived.double().cpu().numpy(),
+                             settled=env.is_settled.cpu().numpy())
+            return cache
+
         def make(i):
-            info = {}
-            if comps is not None:     # info["reward_components"], rate_env.py:410-435 (read by the flight plugin's callback)
-                info["reward_components"] = {nm: float(comps[k, i]) for k, nm in enumerate(COMPONENT_NAMES)}
+            x = extras()
             k = lookup.get(i)
+            if k is None:
+                info = {"time": float(x["time"][i]), "step": int(x["step"][i]), "position": x["pos"][:, i].copy(),
+                        "rate_command": x["cmd"][:, i].copy(), "rate_error": x["cmd"][:, i] - x["rates"][:, i],
+                        "airspeed": float(x["der"][0, i]), "altitude": float(x["der"][1, i]), "is_settled": bool(x["settled"][i])}
+            else:
+                to = term_obs[k].astype(np.float64)
+                info = {"time": float(ep_l[k] * dt), "step": int(ep_l[k]), "position": np.full(3, np.nan),
+                        "rate_command": to[3:6].copy(), "rate_error": to[6:9].copy(), "airspeed": float(to[9]),
+                        "altitude": float(to[10]), "is_settled": False}
+            if comps is not None:     # info["reward_components"], rate_env.py:410-435 (read by the flight plugin's callback)
+                info["reward_components"] = {nm: float(comps[k_, i]) for k_, nm in enumerate(COMPONENT_NAMES)}
             if k is not None:
                 info["terminal_observation"] = term_obs[k]
                 info["TimeLimit.truncated"] = bool(trunc[i] and not term[i])

@@ -60,3 +60,26 @@ def test_vecenv_lazy_infos_and_internal_controller():
     assert dones.all()                                   # 10-step episodes: everyone truncates (or crashed) on step 10
     i = int(np.flatnonzero(dones)[0])
     assert infos[i]["episode"]["l"] in range(1, 11) and infos[i]["terminal_observation"].shape == (18,)
+
+
+def test_vecenv_infos_carry_the_reference_info_keys():
+    """rate_env.py:410-435: time, step, position, rate_command, rate_error, airspeed, altitude, is_settled on every info."""
+    import acb200
+    n = 300
+    venv = acb200.B200VecEnv(n, controller="rate_pid", precision=64, seed=4, episode_length=0.2, reward_components=True)   # 10-step episodes
+    venv.reset()
+    keys = {"time", "step", "position", "rate_command", "rate_error", "airspeed", "altitude", "is_settled", "reward_components"}
+    for t in range(12):
+        obs, rew, dones, infos = venv.step(None)
+        assert len(infos) == n
+        for i in (0, 7, n - 1):
+            info = infos[i]
+            assert keys <= set(info)
+            if dones[i]:
+                assert info["step"] == info["episode"]["l"] and np.isnan(info["position"]).all()
+                assert np.allclose(info["rate_command"], info["terminal_observation"][3:6])
+            else:
+                assert info["step"] == (t % 10) + 1 and abs(info["time"] - info["step"] * 0.02) < 1e-12
+                assert np.allclose(info["rate_command"], obs[i, 3:6], atol=1e-6) and np.allclose(info["rate_error"], obs[i, 6:9], atol=1e-6)
+                assert abs(info["airspeed"] - obs[i, 9]) < 1e-4 and abs(info["altitude"] - obs[i, 10]) < 1e-3
+    assert dones.any() or t > 0
