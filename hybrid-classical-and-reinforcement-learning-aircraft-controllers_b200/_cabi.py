@@ -117,6 +117,7 @@ SYMBOLS = [
     "acb200_default_sensor_config", "acb200_sensor_update", "acb200_sensor_reset",
     "acb200_validate_aircraft_params", "acb200_get_aircraft_params", "acb200_get_controller_params",
     "acb200_set_param_groups", "acb200_env_gather_done",
+    "acb200_env_gather_done_noalloc", "acb200_noalloc_max_aircraft",
 ]
 
 _lib = None
@@ -149,6 +150,8 @@ def load() -> C.CDLL:
     L.acb200_get_controller_params.argtypes = [vp, P(ControllerParamsC)]
     L.acb200_set_param_groups.argtypes = [vp, vp, P(i64), C.c_int32]
     L.acb200_env_gather_done.argtypes = [vp, P(EnvC), i64, vp, vp, vp, vp]
+    L.acb200_env_gather_done_noalloc.argtypes = [vp, P(EnvC), i64, vp, vp, vp, vp]
+    L.acb200_noalloc_max_aircraft.argtypes = []; L.acb200_noalloc_max_aircraft.restype = i64
     L.acb200_fleet_reset.argtypes = [vp, P(FleetC), vp, vp]
     L.acb200_step_surface.argtypes = [vp, P(FleetC), vp, dbl, dbl]
     L.acb200_step_cascade.argtypes = [vp, P(FleetC), i32, vp, dbl, dbl, dbl, vp]

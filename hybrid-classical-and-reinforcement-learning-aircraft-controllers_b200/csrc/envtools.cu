@@ -149,3 +149,79 @@ extern "C" int acb200_env_gather_done(acb200_ctx* ctx, const acb200_env* e, int6
     const cudaError_t err = cudaGetLastError();
     return err == cudaSuccess ? ACB200_OK : fail(ACB200_ECUDA, cudaGetErrorString(err));
 }
+
+// =====================================================================================================================
+// acb200_env_gather_done_noalloc -- the same compaction for callers that may not allocate (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The per-tile counts live in a file-scope device array instead of the handle's cudaMalloc'ed scratch:
+//   * size: kNoAllocMaxTiles ints = 64 KiB, held by every GPU that loads the library until the process exits;
+//   * limit: fleets of at most ACB200_NOALLOC_MAX_AIRCRAFT = kNoAllocMaxTiles * 1024 = 16 777 216 aircraft; larger n is
+//     refused with ACB200_EVALUE (use acb200_env_gather_done);
+//   * the array is SHARED by every call on that device and keeps the last call's contents.  Nothing in it has to start at
+//     zero: pass 1 overwrites every tile count [0, tiles) the later passes read, so no clearing is needed; *count_out is
+//     written by pass 2.  Two calls that overlap on the GPU (different streams, or two contexts on one device) race on
+//     it: keep the calls of one device on one stream, or order them with events.
+// In host code `g_noalloc_tile_counts` is only a host-side stand-in for the symbol, not a device address; the address
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+// =====================================================================================================================
+#include <mutex>
+
+namespace {
+
+constexpr int kNoAllocMaxTiles = 16384;
+static __device__ __align__(256) int32_t g_noalloc_tile_counts[kNoAllocMaxTiles];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+int32_t* g_noalloc_ptr[kMaxDevices] = {};      // device address of the array on device d, resolved on first use
+
+// Call with `device` current.  Returns cudaSuccess and the device-side address of the scratch array.
+cudaError_t noalloc_scratch(int device, int32_t** out) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        int32_t* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_tile_counts);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" int64_t acb200_noalloc_max_aircraft(void) { return (int64_t)kNoAllocMaxTiles * kTile; }
+
+extern "C" int acb200_env_gather_done_noalloc(acb200_ctx* ctx, const acb200_env* e, int64_t capacity, int64_t* ids_out,
+                                              float* terminal_obs_out, float* reset_obs_out, int64_t* count_out) {
+    if (!ctx) return ACB200_ENULL;
+    auto fail = [&](int code, const std::string& msg) { ctx->error = msg; return code; };
+    if (!e || !e->terminated || !e->truncated || !e->obs) return fail(ACB200_ENULL, "env / flags / obs is NULL");
+    if (!ids_out || !count_out) return fail(ACB200_ENULL, "ids_out / count_out is NULL");
+    if (capacity < 0) return fail(ACB200_EVALUE, "capacity < 0");
+    if (terminal_obs_out && !e->terminal_obs) return fail(ACB200_ENULL, "env.terminal_obs is NULL");
+    const int64_t n = e->fleet.n;
+    if (n < 0) return fail(ACB200_EVALUE, "fleet.n < 0");
+    if (n > (int64_t)kNoAllocMaxTiles * kTile)
+        return fail(ACB200_EVALUE, "env_gather_done_noalloc: fleet of " + std::to_string(n) + " aircraft exceeds the static scratch (max " +
+                                       std::to_string((int64_t)kNoAllocMaxTiles * kTile) + "); use acb200_env_gather_done");
+    cudaError_t err = cudaSetDevice(ctx->device);
+    if (err != cudaSuccess) return fail(ACB200_ECUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(err));
+    if (n == 0) {
+        err = cudaMemsetAsync(count_out, 0, sizeof(int64_t), ctx->stream);
+        return err == cudaSuccess ? ACB200_OK : fail(ACB200_ECUDA, cudaGetErrorString(err));
+    }
+    int32_t* scratch = nullptr;
+    if ((err = noalloc_scratch(ctx->device, &scratch)) != cudaSuccess)
+        return fail(ACB200_ECUDA, std::string("cudaGetSymbolAddress(g_noalloc_tile_counts): ") + cudaGetErrorString(err));
+    const int tiles = (int)((n + kTile - 1) / kTile);
+    done_count_kernel<<<tiles, 256, 0, ctx->stream>>>(e->terminated, e->truncated, n, scratch);
+    done_scan_kernel<<<1, 1024, 0, ctx->stream>>>(scratch, tiles, count_out);
+    done_write_kernel<<<tiles, 256, 0, ctx->stream>>>(e->terminated, e->truncated, e->terminal_obs, e->obs, n, scratch, capacity, ids_out,
+                                                      terminal_obs_out, reset_obs_out);
+    ctx->launches += 3;
+    err = cudaGetLastError();
+    return err == cudaSuccess ? ACB200_OK : fail(ACB200_ECUDA, cudaGetErrorString(err));
+}

@@ -261,6 +261,17 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* e, const acb200_env_
  * at 500-step episodes, so a trainer whose controller runs in the kernel never moves the (n, 18) matrix to the host. */
 int acb200_env_gather_done(acb200_ctx* ctx, const acb200_env* e, int64_t capacity, int64_t* ids_out, float* terminal_obs_out,
                            float* reset_obs_out, int64_t* count_out);
+/* acb200_env_gather_done without any allocation, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same results (bit for bit) as acb200_env_gather_done; the per-tile scratch is a file-scope
+ * device array of 64 KiB (csrc/envtools.cu) that every GPU loading the library holds until exit, which limits the fleet to
+ * acb200_noalloc_max_aircraft() = 16 777 216 aircraft -- a larger fleet.n returns ACB200_EVALUE with a message naming the
+ * limit.  Calls no cudaMalloc / cudaFree and no allocating library routine.  The array is shared by every call on a device
+ * and keeps the last call's contents (each call overwrites what it reads, nothing needs clearing); calls that OVERLAP on
+ * the GPU -- two streams, or two contexts on one device -- race on it: issue them on one stream or order them with events. */
+int acb200_env_gather_done_noalloc(acb200_ctx* ctx, const acb200_env* e, int64_t capacity, int64_t* ids_out,
+                                   float* terminal_obs_out, float* reset_obs_out, int64_t* count_out);
+int64_t acb200_noalloc_max_aircraft(void);
 /* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 128k aircraft per chunk) */
 int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 
