@@ -61,7 +61,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -169,24 +169,62 @@ def run_reference(args):
     }))
 
 
-def run_gpu(args):
-    import numpy as np
-    import torch
-    import acb200
+class Runtime:
+    """One process per GPU: rank / device / process group, the barrier and the max-over-ranks the contract asks for."""
 
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0")); self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+        self.peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                self.peaks = json.load(f)
+        except Exception:
+            pass
+        self.traffic = {}
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                self.traffic = json.load(f)
+        except Exception:
+            pass
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, ms):
+        if self.dist is None:
+            return ms
+        t = self.torch.tensor([ms], device=self.dev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def measure_c3(args, rt, k_sub, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
+    """C3 (k_sub = 20) or its K = 1 end (k_sub = 1) on every rank; returns the result object (meaningful on rank 0)."""
+    import numpy as np
+    import acb200
+    torch, dist, dev = rt.torch, rt.dist, rt.dev
+    rank, world, local = rt.rank, rt.world, rt.local
+    barrier, max_over_ranks = rt.barrier, rt.max_over_ranks
     n = args.envs
     precision = args.precision
-    k_sub = 1 if args.workload == "k1" else K_SUB          # k1: control step == physics step, the HBM-bound end of the path
     flop_per_env_step = 1014 * k_sub + 320
     env = acb200.BatchedRateControlEnv(n, controller="attitude_pid", precision=precision, device=local, seed=42,
                                        id_offset=rank * n, command_type="step", dt=0.001 * k_sub)
@@ -197,38 +235,37 @@ def run_gpu(args):
     env.step_count.copy_(torch.as_tensor(phase))
     torch.cuda.synchronize()
 
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(ms):
-        if dist is None:
-            return ms
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
     # ---- device-resident arm: `value` -------------------------------------------------------------
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         env.step()
+    stats = acb200.sharding.allreduce_episode_stats(env.stats)       # warm the communicator outside the timed region
     barrier()
-    clocks = ClockSampler(local)
-    if rank == 0:
+    if clocks is not None and rank == 0:
         clocks.start()
     l0 = env.ctx.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cev = []
     barrier()
     ev0.record()
-    for _ in range(args.steps):
+    for s_ in range(steps):
         env.step()
+        # the one collective of the path -- episode statistics summed over ranks, once per report interval (100 steps)
+        # and at the end of the run -- INSIDE the timed region, bracketed by its own events
+        if (s_ + 1) % 100 == 0 or s_ + 1 == steps:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            stats = acb200.sharding.allreduce_episode_stats(env.stats)
+            b.record()
+            cev.append((a, b))
     ev1.record()
     barrier()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = env.ctx.launch_count - l0
-    # the one collective of the path: episode statistics summed over ranks (outside the per-step loop)
-    stats = acb200.sharding.allreduce_episode_stats(env.stats)
-    value = n * world * args.steps / (ms * 1e-3)
+    coll_us = [1e3 * a.elapsed_time(b) for a, b in cev]
+    collective = {"op": "all_reduce(sum) of the episode statistics, float64[16]" + ("" if world > 1 else " (one rank: a device copy, no NCCL call)"),
+                  "bytes": 128, "calls_in_timed_region": len(cev), "us_mean": sum(coll_us) / len(coll_us), "us_max": max(coll_us),
+                  "backend": "nccl" if world > 1 else None, "interval_steps": 100}
+    value = n * world * steps / (ms * 1e-3)
 
     # ---- end-to-end arm: host buffers, H2D of the step's commands + D2H of obs/reward/done every step
     numa_cores = acb200.sharding.bind_host_to_gpu(local) if world > 1 else []   # staging buffers on the GPU's own NUMA node
@@ -236,7 +273,6 @@ def run_gpu(args):
     att_host = pin((4, n), env.dtype); att_host.copy_(torch.as_tensor(att).to(env.dtype))
     obs_h, rew_h = pin((n, 18), torch.float32), pin((n,), torch.float32)
     term_h, trunc_h = pin((n,), torch.uint8), pin((n,), torch.uint8)
-    e2e_steps = max(3, min(args.steps, args.e2e_steps))
     for _ in range(2):
         env.step_host(None, obs_h, rew_h, term_h, trunc_h, att_cmd_host=att_host)
     barrier()
@@ -247,21 +283,30 @@ def run_gpu(args):
     barrier()
     e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
     e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
-    clk = clocks.stop() if rank == 0 else None           # sampled over both timed regions
+    clk = clocks.stop() if (clocks is not None and rank == 0) else None           # sampled over both timed regions
     h2d = att_host.numel() * att_host.element_size()
     d2h = sum(t.numel() * t.element_size() for t in (obs_h, rew_h, term_h, trunc_h))
 
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
+    # ---- the same call with fewer bytes: the controller runs in the kernel, so a trainer needs reward + flags (6 B per
+    # aircraft) and the observations of the aircraft that FINISHED (acb200_env_gather_done), not the (n, 18) matrix.
+    # Reported beside the full-copy number, which stays the headline (it is the reference-shaped call).
+    done_rows = 0
+    for _ in range(2):
+        env.step_host(None, None, rew_h, term_h, trunc_h, att_cmd_host=att_host); env.gather_done()
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        env.step_host(None, None, rew_h, term_h, trunc_h, att_cmd_host=att_host)
+        done_rows += len(env.gather_done()[0])
+    ev1.record()
+    barrier()
+    red_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    e2e_reduced = {"value": n * world * e2e_steps / (red_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                   "d2h_bytes_per_step": 6 * n + int(done_rows / e2e_steps * (8 + 2 * 72)) + 8, "steps": e2e_steps,
+                   "ms_per_step": red_ms / e2e_steps,
+                   "note": "obs output NULL: reward + flags for every aircraft, ids + terminal/reset observations of the finished ones only"}
 
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except Exception:
-        pass
+    peaks = rt.peaks
     per_gpu = value / world
     bytes_step = env_bytes_per_step(precision)
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
@@ -274,26 +319,22 @@ def run_gpu(args):
     # fp32 fleets of even size run the two-aircraft-per-thread kernel on packed FP32 (csrc/kernels_pair_f32.cuh)
     pair = precision == 32 and n % 2 == 0 and os.environ.get("ACB200_ENV_PAIR", "1")[:1] != "0"
     kernel_name = "env_step_pair_kernel" if pair else "env_step_kernel"
-    try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get(f"env_step{'_pair' if pair else ''}{'_k1' if k_sub == 1 else ''}_f{precision}_{n}")
-    except Exception:
-        pass
+    traffic = rt.traffic.get(f"env_step{'_pair' if pair else ''}{'_k1' if k_sub == 1 else ''}_f{precision}_{n}")
     achieved_tflops = per_gpu * flop_per_env_step / 1e12
     achieved_gbs = per_gpu * bytes_step / 1e9
     roof_fp = {"bound": "fp32", "note": "non-tensor FP32 issue-bound; the path is neither HBM- nor tensor-bound (DESIGN.md 4); HBM view in roofline_hbm",
                "achieved": achieved_tflops, "peak": fp_peak, "unit": "TFLOP/s", "frac": achieved_tflops / fp_peak,
                "peak_source": "measured here: FMA-chain kernel, all SMs (derived nominal: %.1f)" % FP32_PEAK_DERIVED_TFLOPS,
-               "flop_per_env_step": flop_per_env_step, "kernel": kernel_name, "kernel_ms": ms / args.steps,
-               "traffic": traffic}
+               "flop_per_env_step": flop_per_env_step, "kernel": kernel_name, "kernel_ms": ms / steps,
+               "traffic": traffic, "traffic_source": rt.traffic.get("_source")}
     roof_hbm = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
                 "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
                 "bytes_per_env_step": bytes_step, "algorithmic_bytes_per_launch": bytes_step * n, "kernel": kernel_name,
-                "kernel_ms": ms / args.steps, "traffic": traffic}
-    k1 = args.workload == "k1"
+                "kernel_ms": ms / steps, "traffic": traffic, "traffic_source": rt.traffic.get("_source")}
+    k1 = k_sub == 1
     out = {
-        "metric": METRIC.replace("20 RK4 substeps", "1 RK4 substep") if k1 else METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC.replace("20 RK4 substeps", "1 RK4 substep") if k1 else METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if precision == 32 else "f64", "data": "synthetic",
         "config": {"workload": workload_name(n).replace("C3:", "C3 at K=1 (HBM-bound end of the path):").replace("dt=0.02 K=20 RK4 substeps", "dt=0.001 K=1 RK4 substep") if k1 else workload_name(n),
                    "envs_per_gpu": n, "controller": "attitude_pid", "substeps": k_sub,
@@ -303,18 +344,56 @@ def run_gpu(args):
         ("roofline_fp32" if k1 else "roofline_hbm"): roof_fp if k1 else roof_hbm,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": e2e_ms / e2e_steps, "host_cores_bound": len(numa_cores)},
+        "e2e_reduced": e2e_reduced,
+        "collective": collective,
         "gpu_launches": int(launches),
         "clocks": clk,
         "episode_stats": dict(zip(acb200.envs.STATS_NAMES, stats.cpu().tolist())),
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and cpu_baseline and rank == 0:
         cores = os.cpu_count() or 1
         v, done, el = time_oracle(args.ref_envs, cores, 1, budget_s=args.cpu_seconds, dt=0.001 * k_sub)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"{args.ref_envs} aircraft x {done} env steps ({el:.1f} s) of the same workload, C oracle with OpenMP"}
-    print(json.dumps(out))
-    if dist is not None:
-        dist.destroy_process_group()
+    del env
+    torch.cuda.empty_cache()
+    return out
+
+
+# what a sub-workload contributes to the headline line's "workloads" object
+_BRIEF = ("metric", "value", "unit", "steps", "warmup", "ms_per_step", "dtype", "config", "roofline", "e2e", "gpu_launches",
+          "kernels_ms", "mission", "collective")
+
+
+def run_gpu(args):
+    """The workload --workload names on every rank; with the default (c3, the BASELINE metric) the other three are
+    measured right after it in the same process and reported in "workloads", so that one driver run of
+    `bench.py --gpus N` puts k1, C4 and C5 under the same clock (about a second each)."""
+    from tools import bench_c4, bench_c5
+    rt = Runtime()
+    clocks = ClockSampler(rt.local)
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    cpu = not args.no_cpu_baseline
+    if args.workload in ("c3", "k1"):
+        out = measure_c3(args, rt, 1 if args.workload == "k1" else K_SUB, args.steps, args.warmup, e2e_steps, cpu, clocks)
+    elif args.workload == "c4":
+        out = bench_c4.measure(args, rt, args.steps, args.warmup, e2e_steps, cpu, clocks)
+    else:
+        out = bench_c5.measure(args, rt, args.steps, args.warmup, e2e_steps, cpu, clocks)
+    if args.workload == "c3" and not args.no_extra_workloads:
+        import copy
+        extra = {}
+        sub = copy.copy(args)
+        sub.envs = args.envs
+        extra["k1"] = measure_c3(sub, rt, 1, 300, 5, 20, False)
+        sub = copy.copy(args); sub.envs = 262144 if args.envs == 1 << 20 else max(256, args.envs // 4 // 256 * 256)
+        extra["c4"] = bench_c4.measure(sub, rt, 100, 5, 20, False)
+        sub = copy.copy(args)
+        extra["c5"] = bench_c5.measure(sub, rt, 300, 5, 20, False)
+        out["workloads"] = {k: {f: v[f] for f in _BRIEF if f in v} for k, v in extra.items()}
+    if rt.rank == 0:
+        print(json.dumps(out))
+    rt.close()
 
 
 def main():
@@ -335,6 +414,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--e2e-steps", type=int, default=50)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-workloads", action="store_true", help="c3 only: skip the k1 / c4 / c5 lines of the \"workloads\" object")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5", "k1"],
                     help="c3 (default, BASELINE metric): 2^20 aircraft, cascaded PID, K=20; c4: 262144 aircraft, learned LSTM policy; "
                          "k1: c3 with one RK4 substep per env step (the HBM-bound K=1 path); c5: 2^20 aircraft, waypoint mission, 5-level cascade, K=1")
@@ -345,7 +425,7 @@ def main():
         args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
         if args.steps == 1000 and args.impl == "reference":
             args.steps = 20
-        return bench_c5.run_reference(args) if args.impl == "reference" else bench_c5.run_gpu(args, ROOT, ClockSampler)
+        return bench_c5.run_reference(args) if args.impl == "reference" else run_gpu(args)
     if args.workload == "c4":
         from tools import bench_c4
         if args.envs == 1 << 20:
@@ -353,7 +433,7 @@ def main():
         args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
         if args.steps == 1000:
             args.steps = 200 if args.impl == "b200" else 5
-        return bench_c4.run_reference(args) if args.impl == "reference" else bench_c4.run_gpu(args, ROOT, ClockSampler)
+        return bench_c4.run_reference(args) if args.impl == "reference" else run_gpu(args)
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args)

@@ -16,21 +16,13 @@ def workload_name(n):
             f"-> RateControlEnv (external action, medium, step commands), dt=0.02 K=20 RK4 substeps")
 
 
-def run_gpu(args, ROOT, ClockSampler):
-    import torch
+def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
+    """Every rank runs it; returns the result object (bench.py prints rank 0's)."""
     import acb200
     from acb200.policy import random_policy_state_dict
-
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+    torch, dist, dev = rt.torch, rt.dist, rt.dev
+    rank, world, local = rt.rank, rt.world, rt.local
+    barrier, max_over_ranks = rt.barrier, rt.max_over_ranks
     n = args.envs
     env = acb200.BatchedRateControlEnv(n, difficulty="medium", controller="external", precision=32, device=local, seed=42,
                                        id_offset=rank * n, command_type="step")
@@ -38,30 +30,17 @@ def run_gpu(args, ROOT, ClockSampler):
     env.reset()
     flags = (env.terminated, env.truncated)
 
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(ms):
-        if dist is None:
-            return ms
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
     def step():
         env.step(pol(env.obs, flags))
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     barrier()
-    clocks = ClockSampler(local)
-    if rank == 0:
+    if clocks is not None and rank == 0:
         clocks.start()
     l0 = env.ctx.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    pev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    pev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     barrier()
     ev0.record()
     for a, b in pev:                       # events bracket the policy kernel on its own (the launching) stream
@@ -72,10 +51,10 @@ def run_gpu(args, ROOT, ClockSampler):
     ev1.record()
     barrier()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
-    policy_ms = sum(a.elapsed_time(b) for a, b in pev) / args.steps
+    policy_ms = sum(a.elapsed_time(b) for a, b in pev) / steps
     launches = env.ctx.launch_count - l0
     stats = acb200.sharding.allreduce_episode_stats(env.stats)
-    value = n * world * args.steps / (ms * 1e-3)
+    value = n * world * steps / (ms * 1e-3)
 
     # ---- end to end: the observation comes from host memory every step, results go back to host memory
     pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
@@ -83,8 +62,6 @@ def run_gpu(args, ROOT, ClockSampler):
     term_h, trunc_h = pin((n,), torch.uint8), pin((n,), torch.uint8)
     obs_h.copy_(env.obs); term_h.copy_(env.terminated); trunc_h.copy_(env.truncated)
     obs_d = torch.empty_like(env.obs)
-    e2e_steps = max(3, min(args.steps, args.e2e_steps))
-
     from acb200.policy import step_host_pipelined
     e2e_chunks = int(os.environ.get("ACB200_C4_E2E_CHUNKS", "4"))
 
@@ -108,33 +85,18 @@ def run_gpu(args, ROOT, ClockSampler):
     barrier()
     e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
     e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
-    clk = clocks.stop() if rank == 0 else None
+    clk = clocks.stop() if (clocks is not None and rank == 0) else None
     h2d = obs_h.numel() * 4
     d2h = sum(t.numel() * t.element_size() for t in (obs_h, rew_h, term_h, trunc_h))
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
-
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except Exception:
-        pass
+    peaks = rt.peaks
     info = pol.info()
     flops = info["flops_per_aircraft"] * n
     achieved = flops / (policy_ms * 1e-3) / 1e12
     peak = peaks.get("bf16_tflops_sustained", 1401.4)     # a kernel timed inside a long step: the sustained figure
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get(f"policy_forward_{n}")
-    except Exception:
-        pass
+    traffic = rt.traffic.get(f"policy_forward_{n}")
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16 operands / f32 accumulate and gates (policy), f32 (env)", "data": "synthetic",
         "config": {"workload": workload_name(n), "envs_per_gpu": n, "policy": "lstm", "substeps": 20,
                    "l2": "per-step working set (recurrent state 805 MB + env state) > 126 MB L2 (inputs larger than L2)",
@@ -143,20 +105,20 @@ def run_gpu(args, ROOT, ClockSampler):
                      "frac": achieved / peak, "kernel_ms": policy_ms,
                      "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if "bf16_tflops_sustained" in peaks else "fallback",
                      "flop_per_aircraft": info["flops_per_aircraft"], "algorithmic_flop_per_launch": flops,
-                     "weight_bytes_per_tile": info["weight_bytes"], "traffic": traffic},
-        "kernels_ms": {"policy_forward_kernel": policy_ms, "env_step_kernel": ms / args.steps - policy_ms},
+                     "weight_bytes_per_tile": info["weight_bytes"], "traffic": traffic, "traffic_source": rt.traffic.get("_source")},
+        "kernels_ms": {"policy_forward_kernel": policy_ms, "env_step_kernel": ms / steps - policy_ms},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": e2e_ms / e2e_steps},
         "gpu_launches": int(launches),
         "clocks": clk,
         "episode_stats": dict(zip(acb200.envs.STATS_NAMES, stats.cpu().tolist())),
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and cpu_baseline and rank == 0:
         v, done, el, cores, sample = time_cpu(args.ref_envs_c4, budget_s=args.cpu_seconds)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
-    print(json.dumps(out))
-    if dist is not None:
-        dist.destroy_process_group()
+    del env, pol
+    torch.cuda.empty_cache()
+    return out
 
 
 def time_cpu(n, budget_s=None, steps=None, warmup=1):

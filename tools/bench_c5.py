@@ -42,61 +42,38 @@ def initial_states(n, id_offset, seed=7):
     return s
 
 
-def run_gpu(args, ROOT, ClockSampler):
-    import torch
+def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
+    """Every rank runs it; returns the result object (bench.py prints rank 0's)."""
     import acb200
-
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device: the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+    torch, dist, dev = rt.torch, rt.dist, rt.dev
+    rank, world, local = rt.rank, rt.world, rt.local
+    barrier, max_over_ranks = rt.barrier, rt.max_over_ranks
     n = args.envs
     fleet = acb200.AircraftFleet(n, precision=32, device=local, config={"dt_physics": DT})
     fleet.reset(torch.as_tensor(initial_states(n, rank * n)))
     fleet.set_mission(SQUARE, acceptance_radius=40.0, guidance="PP", loop=True)
 
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(ms):
-        if dist is None:
-            return ms
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         fleet.step_waypoint(DT)
     barrier()
-    clocks = ClockSampler(local)
-    if rank == 0:
+    if clocks is not None and rank == 0:
         clocks.start()
     l0 = fleet.ctx.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         fleet.step_waypoint(DT)
     ev1.record()
     barrier()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = fleet.ctx.launch_count - l0
-    value = n * world * args.steps / (ms * 1e-3)
+    value = n * world * steps / (ms * 1e-3)
 
     # end to end: the caller reads every aircraft's state back each step (AircraftInterface.step returns the state);
     # the mission is autonomous, so nothing travels host -> device per step
     state_h = torch.empty((13, n), dtype=torch.float32, pin_memory=True)
     derived_h = torch.empty((4, n), dtype=torch.float32, pin_memory=True)
-    e2e_steps = max(3, min(args.steps, args.e2e_steps))
-
     def step_host():
         fleet.step_waypoint(DT)
         state_h.copy_(fleet.state, non_blocking=True); derived_h.copy_(fleet.derived, non_blocking=True)
@@ -112,36 +89,22 @@ def run_gpu(args, ROOT, ClockSampler):
     barrier()
     e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
     e2e_value = n * world * e2e_steps / (e2e_ms * 1e-3)
-    clk = clocks.stop() if rank == 0 else None
+    clk = clocks.stop() if (clocks is not None and rank == 0) else None
     wp = fleet.wp_index.cpu()
     alt = fleet.derived[1].float().cpu()
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except Exception:
-        pass
+    peaks = rt.peaks
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     achieved = value / world * BYTES_PER_STEP / 1e9
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get(f"step_waypoint_f32_{n}")
-    except Exception:
-        pass
+    traffic = rt.traffic.get(f"step_waypoint_f32_{n}")
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": workload_name(n), "envs_per_gpu": n, "substeps": 1,
                    "l2": f"working set {n * BYTES_PER_STEP / 2 / 1e6:.0f} MB per step > 126 MB L2 (inputs larger than L2)",
                    "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
         "roofline": {"bound": "hbm", "kernel": "step_guided_kernel<float,1>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "kernel_ms": ms / args.steps, "bytes_per_env_step": BYTES_PER_STEP,
+                     "frac": achieved / hbm_peak, "kernel_ms": ms / steps, "bytes_per_env_step": BYTES_PER_STEP,
                      "algorithmic_bytes_per_launch": BYTES_PER_STEP * n,
                      "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback", "traffic": traffic},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": (13 + 4) * 4 * n,
@@ -150,14 +113,14 @@ def run_gpu(args, ROOT, ClockSampler):
         "gpu_launches": int(launches),
         "clocks": clk,
         "mission": {"mean_waypoint_index": float(wp.float().mean()), "altitude_mean": float(alt.mean()), "altitude_min": float(alt.min()),
-                    "sim_seconds": (args.warmup + args.steps + e2e_steps + 2) * DT},
+                    "sim_seconds": (warmup + steps + e2e_steps + 2) * DT},
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and cpu_baseline and rank == 0:
         v, done, el, cores, sample = time_cpu(args.ref_envs, budget_s=args.cpu_seconds)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
-    print(json.dumps(out))
-    if dist is not None:
-        dist.destroy_process_group()
+    del fleet
+    torch.cuda.empty_cache()
+    return out
 
 
 def time_cpu(n, budget_s=None, steps=None, warmup=1):
