@@ -118,6 +118,7 @@ SYMBOLS = [
     "acb200_validate_aircraft_params", "acb200_get_aircraft_params", "acb200_get_controller_params",
     "acb200_set_param_groups", "acb200_env_gather_done",
     "acb200_env_gather_done_noalloc", "acb200_noalloc_max_aircraft",
+    "acb200_param_table_words", "acb200_build_param_table", "acb200_set_param_table",
 ]
 
 _lib = None
@@ -150,6 +151,9 @@ def load() -> C.CDLL:
     L.acb200_get_controller_params.argtypes = [vp, P(ControllerParamsC)]
     L.acb200_set_param_groups.argtypes = [vp, vp, P(i64), C.c_int32]
     L.acb200_env_gather_done.argtypes = [vp, P(EnvC), i64, vp, vp, vp, vp]
+    L.acb200_param_table_words.argtypes = []
+    L.acb200_build_param_table.argtypes = [vp, vp, i64, i64, i64, C.c_int32, vp]
+    L.acb200_set_param_table.argtypes = [vp, vp, i64, C.c_int32]
     L.acb200_env_gather_done_noalloc.argtypes = [vp, P(EnvC), i64, vp, vp, vp, vp]
     L.acb200_noalloc_max_aircraft.argtypes = []; L.acb200_noalloc_max_aircraft.restype = i64
     L.acb200_fleet_reset.argtypes = [vp, P(FleetC), vp, vp]

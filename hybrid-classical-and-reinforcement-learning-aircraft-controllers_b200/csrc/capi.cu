@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "ctx.h"
 #include "kernels.h"
@@ -228,6 +229,7 @@ int acb200_set_param_groups(acb200_ctx* ctx, const acb200_aircraft_params* param
     if (!ctx) return ACB200_ENULL;
     if (n_groups < 0) return fail(ctx, ACB200_EVALUE, "n_groups < 0");
     if (n_groups == 0) { ctx->groups.clear(); ctx->group_bounds.clear(); return ACB200_OK; }
+    if (ctx->param_table) return fail(ctx, ACB200_EVALUE, "a per-aircraft parameter table is set: remove it before setting parameter groups");
     if (!params || !bounds) return fail(ctx, ACB200_ENULL, "params / bounds is NULL");
     if (bounds[0] != 0) return fail(ctx, ACB200_EVALUE, "bounds must rise from 0 to n in multiples of 128");
     for (int g = 0; g < n_groups; ++g) {
@@ -247,10 +249,54 @@ int acb200_set_controller_params(acb200_ctx* ctx, const acb200_controller_params
     return ACB200_OK;
 }
 
+int acb200_param_table_words(void) { return Launch<float>::dyn_param_words(); }
+
+int acb200_set_param_table(acb200_ctx* ctx, const void* table, int64_t n, int32_t precision) {
+    if (!ctx) return ACB200_ENULL;
+    if (!table) { ctx->param_table = nullptr; ctx->table_n = 0; ctx->table_precision = 0; return ACB200_OK; }
+    if (n <= 0) return fail(ctx, ACB200_EVALUE, "param table: n <= 0");
+    if (precision != 32 && precision != 64) return fail(ctx, ACB200_EVALUE, "param table: precision must be 64 or 32");
+    if (!ctx->groups.empty()) return fail(ctx, ACB200_EVALUE, "parameter groups are set: remove them before setting a table");
+    ctx->param_table = table; ctx->table_n = n; ctx->table_precision = precision;
+    return ACB200_OK;
+}
+
+static int check_f32_range(acb200_ctx* ctx, int precision, const acb200_aircraft_params* ap);
+
+int acb200_build_param_table(acb200_ctx* ctx, const acb200_aircraft_params* params, int64_t count, int64_t first, int64_t n,
+                             int32_t precision, void* table) {
+    if (!ctx) return ACB200_ENULL;
+    if (!params || !table) return fail(ctx, ACB200_ENULL, "param table: params / table is NULL");
+    if (precision != 32 && precision != 64) return fail(ctx, ACB200_EVALUE, "param table: precision must be 64 or 32");
+    if (count < 0 || first < 0 || first + count > n) return fail(ctx, ACB200_EVALUE, "param table: rows outside the table");
+    if (count == 0) return ACB200_OK;
+    const acb200_aircraft_params& ref = ctx->aircraft;
+    for (int64_t i = 0; i < count; ++i) {       // all rows first: a bad one changes nothing
+        int rc = acb200_validate_aircraft_params(ctx, &params[i]);
+        if (!rc) rc = check_f32_range(ctx, precision, &params[i]);
+        // the substep length is validated per launch against the context's timestep limits: the rows must share them
+        if (!rc && (params[i].min_timestep != ref.min_timestep || params[i].max_timestep != ref.max_timestep))
+            rc = fail(ctx, ACB200_EVALUE, "param table: min_timestep / max_timestep must equal the context's");
+        if (rc) { ctx->error += " (row " + std::to_string(first + i) + ")"; return rc; }
+    }
+    const int words = Launch<float>::dyn_param_words();
+    const size_t rsz = precision == 64 ? 8 : 4;
+    std::vector<unsigned char> host((size_t)words * count * rsz);
+    for (int64_t i = 0; i < count; ++i) {
+        if (precision == 64) Launch<double>::fold_params(params[i], reinterpret_cast<double*>(host.data()) + i, count);
+        else Launch<float>::fold_params(params[i], reinterpret_cast<float*>(host.data()) + i, count);
+    }
+    cudaSetDevice(ctx->device);
+    cudaError_t e = cudaMemcpy2DAsync((char*)table + first * rsz, (size_t)n * rsz, host.data(), (size_t)count * rsz, (size_t)count * rsz,
+                                      (size_t)words, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);     // `host` dies with this frame
+    return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "param table upload");
+}
+
 // The throughput (fp32) build evaluates atan on |tan(alpha)| <= 1 and divides by cos(max_pitch) (physics_f32.cuh): parameter
 // sets outside that range are refused there instead of being integrated inaccurately; the parity build takes any value the
 // reference takes.
-static int check_f32_range(acb200_ctx* ctx, int precision, const acb200_aircraft_params* ap = nullptr) {
+static int check_f32_range(acb200_ctx* ctx, int precision, const acb200_aircraft_params* ap) {
     if (precision != 32) return ACB200_OK;
     const acb200_aircraft_params& a = ap ? *ap : ctx->aircraft;
     if (!(a.max_alpha > 0.0 && a.max_alpha <= 45.0))
@@ -277,7 +323,7 @@ int acb200_step_surface(acb200_ctx* ctx, const acb200_fleet* f, const void* ctrl
     if (!ctrl_in) return fail(ctx, ACB200_ENULL, "ctrl_in is NULL");
     int K; double h;
     if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
-    if ((rc = check_f32_range(ctx, f->precision))) return rc;
+    if ((rc = check_f32_range(ctx, f->precision, nullptr))) return rc;
     cudaSetDevice(ctx->device);
     const cudaError_t e = (f->precision == 64)
                               ? Launch<double>::step_surface(ctx->aircraft, typed<double>(*f), (const double*)ctrl_in, K, h, ctx->stream)
@@ -295,7 +341,7 @@ int acb200_step_cascade(acb200_ctx* ctx, const acb200_fleet* f, int level, const
         return fail(ctx, ACB200_ENOSUP, "step_cascade supports levels 3 (attitude) and 4 (rate)");
     int K; double h;
     if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
-    if ((rc = check_f32_range(ctx, f->precision))) return rc;
+    if ((rc = check_f32_range(ctx, f->precision, nullptr))) return rc;
     cudaSetDevice(ctx->device);
     const cudaError_t e =
         (f->precision == 64)
@@ -321,7 +367,7 @@ static int step_guided_impl(acb200_ctx* ctx, const acb200_fleet* f, float* pid_o
     }
     int K; double h;
     if ((rc = substeps(ctx, dt, dt_physics, &K, &h))) return rc;
-    if ((rc = check_f32_range(ctx, f->precision))) return rc;
+    if ((rc = check_f32_range(ctx, f->precision, nullptr))) return rc;
     cudaSetDevice(ctx->device);
     const cudaError_t e =
         (f->precision == 64)
@@ -378,6 +424,20 @@ static int env_step_impl(acb200_ctx* ctx, const acb200_env* env, const acb200_en
         ctx->launches += 1;
         return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step");
     };
+    if (ctx->param_table) {
+        // per-aircraft parameters: the table variant of the kernel; limits were checked row by row when the table was built
+        if (!ctx->groups.empty()) return fail(ctx, ACB200_EVALUE, "parameter groups and a parameter table are both set");
+        if (ctx->table_n != env->fleet.n || ctx->table_precision != env->fleet.precision)
+            return fail(ctx, ACB200_EVALUE, "the parameter table was built for another fleet size or precision");
+        int K; double h;
+        if ((rc = substeps(ctx, cfg->dt, cfg->dt_physics, &K, &h))) return rc;
+        const cudaError_t e =
+            (env->fleet.precision == 64)
+                ? Launch<double>::env_step_table(ctx->param_table, ctx->controller, typed<double>(*env, reward_f32), *cfg, K, h, action, first, count, st)
+                : Launch<float>::env_step_table(ctx->param_table, ctx->controller, typed<float>(*env, reward_f32), *cfg, K, h, action, first, count, st);
+        ctx->launches += 1;
+        return e == cudaSuccess ? ACB200_OK : cuda_fail(ctx, e, "env_step_table");
+    }
     if (ctx->groups.empty()) return launch(ctx->aircraft, first, count);
     // parameter groups: one launch per group the range touches, that group's parameters in the constant bank
     if (ctx->group_bounds.back() != env->fleet.n) return fail(ctx, ACB200_EVALUE, "parameter groups describe a fleet of another size");

@@ -24,6 +24,10 @@ struct acb200_ctx {
     // parameter groups (acb200_set_param_groups): group g owns aircraft [group_bounds[g], group_bounds[g+1]) of the fleet
     std::vector<acb200_aircraft_params> groups;
     std::vector<int64_t> group_bounds;
+    // per-aircraft parameter table (acb200_set_param_table): caller-owned device memory, table[words][table_n] of `real`
+    const void* param_table = nullptr;
+    int64_t table_n = 0;
+    int32_t table_precision = 0;
     // device scratch owned by the handle (acb200_env_gather_done: one int per 1024 aircraft)
     int32_t* scratch_i32 = nullptr;
     int scratch_i32_len = 0;

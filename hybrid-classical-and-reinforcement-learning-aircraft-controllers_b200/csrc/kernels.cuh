@@ -350,10 +350,8 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvPtrs<T> B, const _
 // -> controller -> PID memory stored back; (B) K RK4 substeps on 12 states + held controls; (C) the
 // env's bookkeeping words are loaded only now -> reward / termination / (cold) Philox reset -> scatter.
 template <typename T>
-__global__ void __launch_bounds__(kBlock, MinBlocks<T>::env) env_step_kernel(const __grid_constant__ DynParams<T> P,
-                                                          const __grid_constant__ CtrlParams<T> C,
-                                                          const __grid_constant__ EnvConst<T> E, EnvPtrs<T> B,
-                                                          const float* __restrict__ action, int64_t first, int64_t count) {
+__device__ __forceinline__ void env_step_body(const DynParams<T>& P, const CtrlParams<T>& C, const EnvConst<T>& E, const EnvPtrs<T>& B,
+                                              const float* __restrict__ action, int64_t first, int64_t count) {
     // aircraft [first, first + count) of the fleet; n stays the field stride of the SoA buffers
     __shared__ __align__(16) float stage[kBlock * ACB200_OBS_DIM];
     __shared__ double block_stats[ACB200_STATS_FIELDS];
@@ -495,6 +493,38 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::env) env_step_kernel(con
     }
 }
 
+// Default: ONE parameter set per launch, in the constant bank (__grid_constant__).
+template <typename T>
+__global__ void __launch_bounds__(kBlock, MinBlocks<T>::env) env_step_kernel(const __grid_constant__ DynParams<T> P,
+                                                          const __grid_constant__ CtrlParams<T> C,
+                                                          const __grid_constant__ EnvConst<T> E, EnvPtrs<T> B,
+                                                          const float* __restrict__ action, int64_t first, int64_t count) {
+    env_step_body<T>(P, C, E, B, action, first, count);
+}
+
+// Per-aircraft parameters (second half): the same step with every aircraft's OWN DynParams block,
+// folded on the host by make_dyn_params exactly as the constant-bank block is and stored field-major, table[word][n] --
+// a warp reads 128 contiguous bytes per word.  The block is loaded once per env step into registers (the compiler drops
+// the words the build does not read) and held across the K substeps; with ~45 live parameters on top of the state the
+// register allocation is wider than the default kernel's, hence the separate launch bound.  Throughput: the loads are
+// ~200 B per aircraft against 553 B of state traffic, and the kernel stays compute-bound at K = 20.
+constexpr int kDynParamWords = (int)(sizeof(DynParams<float>) / sizeof(float));
+static_assert(sizeof(DynParams<float>) == kDynParamWords * sizeof(float) && sizeof(DynParams<double>) == kDynParamWords * sizeof(double),
+              "DynParams must be a plain block of T");
+template <typename T>
+__global__ void __launch_bounds__(kBlock, sizeof(T) == 4 ? 3 : 1) env_step_table_kernel(const T* __restrict__ table,
+                                                          const __grid_constant__ CtrlParams<T> C,
+                                                          const __grid_constant__ EnvConst<T> E, EnvPtrs<T> B,
+                                                          const float* __restrict__ action, int64_t first, int64_t count) {
+    int64_t i = first + (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    if (i >= first + count) i = first + count - 1;          // tail threads read a valid row; env_step_body masks them out
+    DynParams<T> P;
+    T* w = reinterpret_cast<T*>(&P);
+#pragma unroll
+    for (int k = 0; k < kDynParamWords; ++k) w[k] = table[(int64_t)k * B.f.n + i];
+    env_step_body<T>(P, C, E, B, action, first, count);
+}
+
 }  // namespace acb
 #ifdef ACB_PAIR_KERNEL
 #include "kernels_pair_f32.cuh"   // throughput build: two aircraft per thread on packed FP32 instructions
@@ -617,6 +647,24 @@ cudaError_t Launch<T>::env_reset(const EnvPtrs<T>& e, const acb200_env_config& c
 }
 
 template <typename T>
+cudaError_t Launch<T>::env_step_table(const void* table, const acb200_controller_params& cp, const EnvPtrs<T>& e,
+                                      const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
+                                      cudaStream_t st) {
+    if (count <= 0) return cudaSuccess;
+    env_step_table_kernel<T><<<grid_for(count), kBlock, 0, st>>>((const T*)table, make_ctrl_params<T>(cp), make_env_const<T>(cfg, K, h), e,
+                                                                 action, first, count);
+    return cudaGetLastError();
+}
+
+template <typename T> int Launch<T>::dyn_param_words() { return kDynParamWords; }
+
+template <typename T> void Launch<T>::fold_params(const acb200_aircraft_params& ap, T* out, int64_t stride) {
+    const DynParams<T> d = make_dyn_params<T>(ap);
+    const T* w = reinterpret_cast<const T*>(&d);
+    for (int k = 0; k < kDynParamWords; ++k) out[(int64_t)k * stride] = w[k];
+}
+
+template <typename T>
 cudaError_t Launch<T>::env_step(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const EnvPtrs<T>& e,
                                 const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
                                 cudaStream_t st) {
@@ -649,6 +697,7 @@ template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, Kerne
     else if (!strcmp(name, "step_cascade_rate")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_RATE>;
     else if (!strcmp(name, "step_cascade_attitude")) fn = (const void*)step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE>;
     else if (!strcmp(name, "env_step")) fn = (const void*)env_step_kernel<T>;
+    else if (!strcmp(name, "env_step_table")) fn = (const void*)env_step_table_kernel<T>;
 #ifdef ACB_PAIR_KERNEL
     else if (!strcmp(name, "env_step_pair") && sizeof(T) == 4) fn = env_step_pair_entry();
     else if (!strcmp(name, "step_waypoint_pair") && sizeof(T) == 4) fn = (const void*)step_guided_pair_kernel<ACB200_LEVEL_WAYPOINT>;

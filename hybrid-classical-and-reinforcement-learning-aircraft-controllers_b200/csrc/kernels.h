@@ -57,6 +57,12 @@ template <typename T> struct Launch {
     static cudaError_t env_step(const acb200_aircraft_params& ap, const acb200_controller_params& cp, const EnvPtrs<T>& e,
                                 const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
                                 cudaStream_t st);
+    // per-aircraft parameter table: table[dyn_param_words()][e.f.n] of T on the device, rows folded by fold_params
+    static cudaError_t env_step_table(const void* table, const acb200_controller_params& cp, const EnvPtrs<T>& e,
+                                      const acb200_env_config& cfg, int K, double h, const float* action, int64_t first, int64_t count,
+                                      cudaStream_t st);
+    static int dyn_param_words();
+    static void fold_params(const acb200_aircraft_params& ap, T* out /* host, word k at out[k * stride] */, int64_t stride);
     static cudaError_t kernel_info(const char* name, KernelInfo* out);
 };
 

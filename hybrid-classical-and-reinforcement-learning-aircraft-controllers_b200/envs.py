@@ -41,6 +41,27 @@ def randomize_aircraft_params(base, n_groups: int, spread: float = 0.2, seed: in
     return out
 
 
+def randomize_aircraft_params_table(base, n: int, spread: float = 0.2, seed: int = 0, fields=RANDOMIZED_FIELDS, id_offset: int = 0):
+    """One ``AircraftParams`` per aircraft: a ctypes array of n ``AircraftParamsC`` with each listed field of ``base`` scaled by
+    U(1 - spread, 1 + spread), drawn per GLOBAL aircraft id (a hash of (seed, id, field), so the draw does not depend on
+    the sharding).  Vectorised on the host: a million aircraft are a few hundred milliseconds."""
+    import numpy as np
+    nf = len(_cabi.AIRCRAFT_FIELDS)
+    tab = np.tile(np.frombuffer(bytes(base), dtype=np.float64), (n, 1))
+    ids = np.arange(id_offset, id_offset + n, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        for f in fields:                         # splitmix64 of (seed, global id, field): shard-independent uniforms
+            k = _cabi.AIRCRAFT_FIELDS.index(f)
+            x = ids * np.uint64(0x9E3779B97F4A7C15) + np.uint64((seed * 0xD1B54A32D192ED03 + (k + 1) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF)
+            x ^= x >> np.uint64(30); x *= np.uint64(0xBF58476D1CE4E5B9)
+            x ^= x >> np.uint64(27); x *= np.uint64(0x94D049BB133111EB)
+            x ^= x >> np.uint64(31)
+            u = (x >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+            tab[:, k] *= 1.0 - spread + 2.0 * spread * u
+    assert C.sizeof(_cabi.AircraftParamsC) == nf * 8
+    return (_cabi.AircraftParamsC * n).from_buffer_copy(np.ascontiguousarray(tab).tobytes())
+
+
 class BatchedRateControlEnv:
     """obs float32 [n,18]; action float32 [n,4] = aileron, elevator, rudder, throttle (rate_env.py:228-233)."""
 
@@ -130,6 +151,25 @@ class BatchedRateControlEnv:
         b = (C.c_int64 * (g + 1))(*bounds)
         self.ctx.check(lib.acb200_set_param_groups(h, arr, b, g))
         self._groups = (list(groups), bounds)
+
+    def set_param_table(self, params):
+        """Per-AIRCRAFT ``AircraftParams``: ``params`` is a sequence / ctypes array of n
+        ``_cabi.AircraftParamsC`` (``randomize_aircraft_params_table``), or None to return to one parameter set.  The
+        folded table ([words][n] of the build's real type) lives in a torch tensor this env owns; every step path then runs the
+        table variant of the kernel.  A bad row raises ``ValueError`` like ``AircraftParams.__post_init__`` and changes nothing."""
+        lib, h = self.ctx.lib, self.ctx.handle
+        if params is None:
+            self.ctx.check(lib.acb200_set_param_table(h, None, 0, 0))
+            self.param_table = None
+            return
+        if len(params) != self.n:
+            raise ValueError(f"need one AircraftParams per aircraft: {len(params)} given for {self.n}")
+        arr = params if isinstance(params, C.Array) else (_cabi.AircraftParamsC * self.n)(*params)
+        table = torch.zeros((lib.acb200_param_table_words(), self.n), device=self.device, dtype=self.dtype)
+        self._bind_stream()
+        self.ctx.check(lib.acb200_build_param_table(h, arr, self.n, 0, self.n, self.precision, _ptr(table)))
+        self.ctx.check(lib.acb200_set_param_table(h, _ptr(table), self.n, self.precision))
+        self.param_table = table
 
     def step(self, action: Optional[torch.Tensor] = None):
         """One control step for every aircraft; tensors returned are views of the env's own buffers."""

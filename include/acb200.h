@@ -203,6 +203,21 @@ int acb200_get_controller_params(const acb200_ctx* ctx, acb200_controller_params
  * the one whose n equals bounds[n_groups]; a step on a fleet of another size fails with ACB200_EVALUE. */
 int acb200_set_param_groups(acb200_ctx* ctx, const acb200_aircraft_params* params, const int64_t* bounds, int32_t n_groups);
 
+/* Per-AIRCRAFT parameters: every aircraft flies its own AircraftParams -- what n reference env
+ * instances each constructed with its own params are (simulation_backend.py:55-80).  The table is caller-owned device
+ * memory of acb200_param_table_words() * n values of `real` (float for precision 32, double for 64), field-major
+ * table[word][n]; acb200_build_param_table validates params[0..count) (AircraftParams.__post_init__; for precision 32
+ * also the throughput build's ranges), folds each exactly as the constant-bank block is folded and writes rows
+ * [first, first + count) (synchronises the context's stream; a failed validation writes nothing).  After
+ * acb200_set_param_table every env step entry point (acb200_env_step, _range, _host) runs the table variant of the kernel
+ * (one aircraft per thread, block loaded once per env step into registers) for a fleet with fleet.n == n and the same
+ * precision, anything else fails with ACB200_EVALUE; table NULL returns to the context's parameters.  Parameter groups and
+ * a table cannot be active together.  The constant-bank kernels stay the default and the faster path. */
+int acb200_param_table_words(void);
+int acb200_build_param_table(acb200_ctx* ctx, const acb200_aircraft_params* params, int64_t count, int64_t first, int64_t n,
+                             int32_t precision, void* table);
+int acb200_set_param_table(acb200_ctx* ctx, const void* table, int64_t n, int32_t precision);
+
 /* ---- physics ---- */
 /* Simplified6DOF.reset for aircraft with mask[i] != 0 (mask NULL = all).  init_state real[13][n] or
  * NULL for the default level flight at 100 m / 20 m/s (simplified_6dof.py:197-204).  Zeroes their PID
