@@ -66,7 +66,11 @@ class SensorConfigC(C.Structure):
 
 class MissionC(C.Structure):
     _fields_ = [("waypoints", C.c_void_p), ("n_waypoints", C.c_int32), ("guidance", C.c_int32), ("wp_index", C.c_void_p),
-                ("loop", C.c_int32), ("_pad", C.c_int32), ("acceptance_radius", C.c_double)]
+                ("loop", C.c_int32), ("_pad", C.c_int32), ("acceptance_radius", C.c_double), ("stats", C.c_void_p)]
+
+
+MISSION_STATS_NAMES = ("aircraft_steps", "waypoints_reached", "laps", "missions_completed", "cross_track_abs_sum", "cross_track_sq_sum",
+                       "altitude_error_abs_sum", "distance_to_waypoint_sum", "airspeed_sum", "steps_below_5m")
 
 
 class FleetC(C.Structure):

@@ -176,14 +176,83 @@ template <typename T> struct MissionPtrs {
     int32_t* wp_index;
     int32_t loop;
     T acceptance_radius;
+    double* stats;      // double[ACB200_MISSION_STATS_FIELDS] accumulated over calls; nullable
 };
+
+// Mission statistics (BASELINE config 5: "episode-stat allreduce"): what one aircraft adds in one control step, from the state
+// the guidance sees (before the physics step).  Field order = ACB200_MISSION_STATS_* in acb200.h.
+constexpr int kMissionStats = 10;
+template <typename T>
+__device__ __forceinline__ void mission_stats_one(const MissionPtrs<T>& M, int32_t idx, const T (&wp)[4], const T (&s)[12], const T (&d)[4],
+                                                  bool advanced, bool lapped, T (&ms)[kMissionStats]) {
+    using Mt = Math<T>;
+    ms[0] += T(1);                                   // aircraft-steps flown
+    ms[1] += advanced ? T(1) : T(0);                 // waypoints reached (MissionPlanner.update returned True)
+    ms[2] += lapped ? T(1) : T(0);                   // laps closed (looping missions)
+    // cross-track error: horizontal distance from the leg (previous waypoint -> active waypoint)
+    int32_t prev = idx - 1;
+    if (prev < 0) prev = M.loop ? M.n_waypoints - 1 : -1;
+    T ct = T(0);
+    if (prev >= 0) {
+        const T ax = M.waypoints[prev * 4 + 0], ay = M.waypoints[prev * 4 + 1];
+        const T bx = wp[0] - ax, by = wp[1] - ay, px = s[0] - ax, py = s[1] - ay;
+        const T len2 = bx * bx + by * by;
+        if (len2 > T(1e-12)) ct = Mt::kParity ? Mt::abs(Mt::div(px * by - py * bx, Mt::sqrt(len2))) : Mt::abs(px * by - py * bx) * (T)rsqrtf((float)len2);
+    }
+    ms[4] += ct; ms[5] += ct * ct;
+    ms[6] += Mt::abs(d[1] - (-wp[2]));               // |altitude - waypoint altitude|
+    ms[7] += Mt::norm3(wp[0] - s[0], wp[1] - s[1], wp[2] - s[2]);
+    ms[8] += d[0];                                   // airspeed
+    ms[9] += (d[1] < T(5)) ? T(1) : T(0);            // below the env's crash floor (rate_env.py:437-460)
+}
+
+// Sum of every thread's mission contributions into the global vector.  Every thread of the block must call it.
+// At K = 1 the guided kernel is issue-bound, so the reduction is written for instruction count: the five 0/1 counts go
+// through the integer warp reduction (one REDUX each), four of the five float sums through a TRANSPOSED warp reduction
+// (lanes split the fields between them while they fold: 2 + 1 + 3 = 6 shuffles for four values instead of 20), the fifth
+// through a plain tree; warp results meet in shared memory without atomics and ten threads add them to the global
+// (double) accumulator.  First version (a five-step tree per field, shared double atomics): +0.017 ms on a 0.106 ms step.
+template <typename T>
+__device__ __forceinline__ void block_accumulate_mission(const T (&v)[kMissionStats], double* __restrict__ global) {
+    __shared__ T part[kBlock / 32][kMissionStats];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // counts: fields 0, 1, 2, 3, 9
+    const int c0 = __reduce_add_sync(full, (int)v[0]), c1 = __reduce_add_sync(full, (int)v[1]), c2 = __reduce_add_sync(full, (int)v[2]),
+              c3 = __reduce_add_sync(full, (int)v[3]), c9 = __reduce_add_sync(full, (int)v[9]);
+    // float sums 4..7, transposed: after the xor-16 step a lane keeps two fields, after xor-8 one
+    const bool hi = (lane & 16) != 0, mid = (lane & 8) != 0;
+    T x0 = hi ? v[6] : v[4], x1 = hi ? v[7] : v[5];
+    const T y0 = hi ? v[4] : v[6], y1 = hi ? v[5] : v[7];
+    x0 += __shfl_xor_sync(full, y0, 16); x1 += __shfl_xor_sync(full, y1, 16);
+    T z = mid ? x1 : x0;
+    const T w = mid ? x0 : x1;
+    z += __shfl_xor_sync(full, w, 8);
+    z += __shfl_xor_sync(full, z, 4); z += __shfl_xor_sync(full, z, 2); z += __shfl_xor_sync(full, z, 1);
+    // lanes 0 / 8 / 16 / 24 now hold the warp totals of fields 4 / 5 / 6 / 7
+    T a = v[8];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) a += __shfl_xor_sync(full, a, off);
+    if ((lane & 7) == 0) part[warp][4 + (lane >> 3)] = z;
+    if (lane == 0) {
+        part[warp][0] = (T)c0; part[warp][1] = (T)c1; part[warp][2] = (T)c2; part[warp][3] = (T)c3; part[warp][9] = (T)c9;
+        part[warp][8] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x < kMissionStats) {
+        double t = 0.0;
+#pragma unroll
+        for (int wv = 0; wv < kBlock / 32; ++wv) t += (double)part[wv][threadIdx.x];
+        if (t != 0.0) atomicAdd(&global[threadIdx.x], t);
+    }
+}
 
 // One aircraft's whole guided step (the body of step_guided_kernel; also the cold path of the pair kernel).
 template <typename T, int LEVEL>
 __device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
                                                 float* __restrict__ pid_outer, const T* __restrict__ cmd, const MissionPtrs<T>& M,
                                                 float dt_ctrl, int K, T h, T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out,
-                                                int64_t i) {
+                                                int64_t i, T (&ms)[kMissionStats]) {
     T s[12], time, hc[3], surf[4], c[4], d[4];
 #pragma unroll
     for (int k = 0; k < 12; ++k) s[k] = ldf(f.state, k, f.n, i);
@@ -196,14 +265,17 @@ __device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const Ctr
 #pragma unroll
         for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
         // MissionPlanner.update (mission_planner.py:128-171): 3-D distance below the acceptance radius -> next waypoint
+        bool advanced = false, lapped = false;
         if (Math<T>::norm3(wp[0] - s[0], wp[1] - s[1], wp[2] - s[2]) < M.acceptance_radius) {
             idx += 1;
-            if (idx >= M.n_waypoints && M.loop) idx = 0;
+            advanced = true;
+            if (idx >= M.n_waypoints && M.loop) { idx = 0; lapped = true; }
             M.wp_index[i] = idx;
-            if (idx >= M.n_waypoints) return;
+            if (idx >= M.n_waypoints) { ms[1] += T(1); ms[3] += T(1); return; }      // reached the last waypoint: mission complete
 #pragma unroll
             for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
         }
+        if (M.stats) mission_stats_one(M, idx, wp, s, d, advanced, lapped, ms);
         waypoint_guidance(C, M.guidance, wp, s, d, hc);
         if (hsa_cmd_out) {
 #pragma unroll
@@ -248,8 +320,11 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kern
                                                              MissionPtrs<T> M, float dt_ctrl, int K, T h,
                                                              T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out) {
     const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
-    if (i >= f.n) return;
-    guided_step_one<T, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i);
+    T ms[kMissionStats];
+#pragma unroll
+    for (int k = 0; k < kMissionStats; ++k) ms[k] = T(0);
+    if (i < f.n) guided_step_one<T, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i, ms);
+    if (LEVEL == ACB200_LEVEL_WAYPOINT && M.stats) block_accumulate_mission(ms, M.stats);      // uniform branch: whole block or nobody
 }
 
 // ---- env memory <-> registers ----------------------------------------------------------------------
@@ -612,8 +687,8 @@ cudaError_t Launch<T>::step_guided(const acb200_aircraft_params& ap, const acb20
     if (f.n <= 0) return cudaSuccess;
     const DynParams<T> P = make_dyn_params<T>(ap);
     const CtrlParams<T> C = make_ctrl_params<T>(cp);
-    MissionPtrs<T> M{nullptr, 0, 0, nullptr, 0, T(0)};
-    if (m) M = MissionPtrs<T>{(const T*)m->waypoints, m->n_waypoints, m->guidance, m->wp_index, m->loop, (T)m->acceptance_radius};
+    MissionPtrs<T> M{nullptr, 0, 0, nullptr, 0, T(0), nullptr};
+    if (m) M = MissionPtrs<T>{(const T*)m->waypoints, m->n_waypoints, m->guidance, m->wp_index, m->loop, (T)m->acceptance_radius, m->stats};
 #ifdef ACB_PAIR_KERNEL
     if constexpr (sizeof(T) == 4) {
         // measured on B200 (profiles/r01g_fleet_probe.json): with the nine PIDs and the guidance run per lane the pair kernel wins

@@ -344,18 +344,24 @@ step_fleet_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_
 template <int LEVEL>
 static __device__ __noinline__ void guided_step_one_cold(const DynParams<float>& P, const CtrlParams<float>& C, const FleetPtrs<float>& f,
                                                          float* pid_outer, const float* cmd, const MissionPtrs<float>& M, float dt_ctrl,
-                                                         int K, float h, float* surfaces_out, float* hsa_cmd_out, int64_t i) {
-    guided_step_one<float, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i);
+                                                         int K, float h, float* surfaces_out, float* hsa_cmd_out, int64_t i, float* ms_out) {
+    float ms[kMissionStats];
+#pragma unroll
+    for (int k = 0; k < kMissionStats; ++k) ms[k] = 0.0f;
+    guided_step_one<float, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i, ms);
+#pragma unroll
+    for (int k = 0; k < kMissionStats; ++k) ms_out[k] += ms[k];
 }
 
 #ifndef ACB_GUIDED_PAIR_MIN_BLOCKS
 #define ACB_GUIDED_PAIR_MIN_BLOCKS 3
 #endif
 template <int LEVEL>
-__global__ void __launch_bounds__(kBlock, ACB_GUIDED_PAIR_MIN_BLOCKS)
-step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C, FleetPtrs<float> f,
-                        float* __restrict__ pid_outer, const float* __restrict__ cmd, MissionPtrs<float> M, float dt_ctrl, int K,
-                        float h, float* __restrict__ surfaces_out, float* __restrict__ hsa_cmd_out, int64_t pairs) {
+__device__ __forceinline__ void step_guided_pair_body(const DynParams<float>& P, const CtrlParams<float>& C, const FleetPtrs<float>& f,
+                                                      float* __restrict__ pid_outer, const float* __restrict__ cmd,
+                                                      const MissionPtrs<float>& M, float dt_ctrl, int K, float h,
+                                                      float* __restrict__ surfaces_out, float* __restrict__ hsa_cmd_out, int64_t pairs,
+                                                      float (&ms)[kMissionStats]) {
     const int64_t n = f.n;
     const int64_t pair_idx = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (pair_idx >= pairs) return;
@@ -377,8 +383,13 @@ step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid
             if (Math<float>::norm3(dx, dy, dz) < M.acceptance_radius && idx + 1 >= M.n_waypoints && !M.loop) leaves = true;
         }
         if (leaves) {
-            guided_step_one_cold<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i);
-            guided_step_one_cold<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i + 1);
+            float tmp[kMissionStats];
+#pragma unroll
+            for (int k = 0; k < kMissionStats; ++k) tmp[k] = 0.0f;
+            guided_step_one_cold<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i, tmp);
+            guided_step_one_cold<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i + 1, tmp);
+#pragma unroll
+            for (int k = 0; k < kMissionStats; ++k) ms[k] = tmp[k];
             return;
         }
     }
@@ -406,13 +417,16 @@ step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid
 #pragma unroll
             for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
             // MissionPlanner.update (mission_planner.py:128-171): inside the acceptance radius -> next waypoint
+            bool advanced = false, lapped = false;
             if (Math<float>::norm3(wp[0] - sl[0], wp[1] - sl[1], wp[2] - sl[2]) < M.acceptance_radius) {
                 idx += 1;
-                if (idx >= M.n_waypoints && M.loop) idx = 0;
+                advanced = true;
+                if (idx >= M.n_waypoints && M.loop) { idx = 0; lapped = true; }
                 M.wp_index[il] = idx;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
             }
+            if (M.stats) mission_stats_one(M, idx, wp, sl, d, advanced, lapped, ms);
             waypoint_guidance(C, M.guidance, wp, sl, d, hc);
 #pragma unroll
             for (int k = 0; k < 3; ++k) { if (l) hc2[k].y = hc[k]; else hc2[k].x = hc[k]; }
@@ -483,6 +497,18 @@ step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid
 #pragma unroll
         for (int k = 0; k < 4; ++k) *reinterpret_cast<v2*>(f.derived + (int64_t)k * n + i) = d2[k];
     }
+}
+
+template <int LEVEL>
+__global__ void __launch_bounds__(kBlock, ACB_GUIDED_PAIR_MIN_BLOCKS)
+step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C, FleetPtrs<float> f,
+                        float* __restrict__ pid_outer, const float* __restrict__ cmd, MissionPtrs<float> M, float dt_ctrl, int K,
+                        float h, float* __restrict__ surfaces_out, float* __restrict__ hsa_cmd_out, int64_t pairs) {
+    float ms[kMissionStats];
+#pragma unroll
+    for (int k = 0; k < kMissionStats; ++k) ms[k] = 0.0f;
+    step_guided_pair_body<LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, pairs, ms);
+    if (LEVEL == ACB200_LEVEL_WAYPOINT && M.stats) block_accumulate_mission(ms, M.stats);
 }
 
 // Whole fleets only (n even, 8-byte aligned fields); otherwise the one-aircraft kernels run.

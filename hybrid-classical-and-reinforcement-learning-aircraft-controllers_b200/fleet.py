@@ -132,16 +132,36 @@ class AircraftFleet:
                                                     dt if dt_ctrl is None else dt_ctrl, dt, self.dt_physics, _ptr(surfaces_out)))
         return self.state
 
-    def set_mission(self, waypoints, acceptance_radius: float = 40.0, guidance: str = "PP", loop: bool = False):
+    def set_mission(self, waypoints, acceptance_radius: float = 40.0, guidance: str = "PP", loop: bool = False, stats: bool = True):
         """MissionPlanner(waypoints, acceptance_radius).start() for every aircraft (mission_planner.py:56-93).
-        waypoints [n_wp][4] = north, east, down, speed (NaN = None); guidance 'LOS' | 'PP' (waypoint_agent.py:33-52)."""
+        waypoints [n_wp][4] = north, east, down, speed (NaN = None); guidance 'LOS' | 'PP' (waypoint_agent.py:33-52).
+        stats: accumulate the fleet's mission statistics on the device (``mission_stats()``, 16 doubles)."""
         wp = as_tensor(waypoints, self.device, self.dtype)
         assert wp.ndim == 2 and wp.shape[1] == 4 and wp.shape[0] >= 1
         g = {"LOS": _cabi.GUIDANCE_LOS, "PP": _cabi.GUIDANCE_PP, "PURE_PURSUIT": _cabi.GUIDANCE_PP}[guidance.upper()]
         self.waypoints = wp
         self.wp_index.zero_()
+        self.mission_stats_buf = torch.zeros((16,), device=self.device, dtype=torch.float64) if stats else None
         self._mission = _cabi.MissionC(waypoints=wp.data_ptr(), n_waypoints=wp.shape[0], guidance=g,
-                                       wp_index=self.wp_index.data_ptr(), loop=int(loop), acceptance_radius=acceptance_radius)
+                                       wp_index=self.wp_index.data_ptr(), loop=int(loop), acceptance_radius=acceptance_radius,
+                                       stats=None if not stats else self.mission_stats_buf.data_ptr())
+
+    def mission_stats(self, reset: bool = False, allreduce: bool = False) -> dict:
+        """The fleet's mission statistics since the last reset of the accumulator: counts and sums (``_cabi.MISSION_STATS_NAMES``)
+        plus the derived means.  allreduce: summed over the ranks of the default process group first (the one collective of a
+        sharded mission fleet, 128 bytes per report interval)."""
+        if self.mission_stats_buf is None:
+            raise RuntimeError("set_mission(..., stats=True) first")
+        from .sharding import allreduce_episode_stats
+        v = (allreduce_episode_stats(self.mission_stats_buf) if allreduce else self.mission_stats_buf).cpu().tolist()
+        if reset:
+            self.mission_stats_buf.zero_()
+        out = dict(zip(_cabi.MISSION_STATS_NAMES, v))
+        steps = max(out["aircraft_steps"], 1.0)
+        out.update(cross_track_mean=out["cross_track_abs_sum"] / steps, cross_track_rms=(out["cross_track_sq_sum"] / steps) ** 0.5,
+                   altitude_error_mean=out["altitude_error_abs_sum"] / steps, airspeed_mean=out["airspeed_sum"] / steps,
+                   distance_to_waypoint_mean=out["distance_to_waypoint_sum"] / steps)
+        return out
 
     def step_waypoint(self, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None, hsa_cmd_out=None):
         """One pass of the loop of examples/03_waypoint_square_demo.py:147-209: MissionPlanner.update,

@@ -120,7 +120,16 @@ typedef struct {
     int32_t loop;              /* != 0: after the last waypoint continue with waypoint 0 */
     int32_t _pad;
     double acceptance_radius;  /* 3-D distance, mission_planner.py:173-186 */
+    double* stats;             /* double[ACB200_MISSION_STATS_FIELDS], device, accumulated over calls (warp shuffle -> one atomic per
+                                  block and field); nullable.  [0] aircraft-steps flown, [1] waypoints reached (what
+                                  MissionPlanner.waypoints_reached counts, summed over the fleet), [2] laps closed (looping missions),
+                                  [3] missions completed, [4] sum |cross-track error| (horizontal distance from the leg previous ->
+                                  active waypoint) and [5] its squares, [6] sum |altitude - waypoint altitude|, [7] sum 3-D distance to
+                                  the active waypoint (MissionPlanner.get_distance_to_current_waypoint), [8] sum airspeed, [9] steps
+                                  below 5 m (the env's crash floor); [10..15] reserved.  Contributions are taken from the state the
+                                  guidance sees, before the physics step.  One all-reduce per report interval sums it over ranks. */
 } acb200_mission;
+#define ACB200_MISSION_STATS_FIELDS 16
 
 /* The aircraft fleet: what N SimulationAircraftBackend objects hold. */
 typedef struct {

@@ -616,38 +616,73 @@ int orc_step_hsa(const orc_aircraft_params* P, const orc_controller_params* C, i
     return K;
 }
 
-int orc_step_waypoint(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state,
-                      const double* waypoints, int n_wp, int32_t* wp_index, int guidance, double acceptance_radius, int loop,
-                      float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
-                      double dt_ctrl, double dt, double dt_physics, int nthreads) {
+/* mission_stats (nullable, double[16], accumulated): the fleet statistics acb200_mission.stats holds (include/acb200.h) --
+ * [0] aircraft-steps flown, [1] waypoints reached (MissionPlanner.waypoints_reached summed over the fleet,
+ * mission_planner.py:151-153), [2] laps closed, [3] missions completed (:163-165), [4] sum |cross-track error| (horizontal
+ * distance from the leg previous -> active waypoint), [5] its squares, [6] sum |altitude - waypoint altitude|, [7] sum 3-D
+ * distance to the active waypoint (:188-205), [8] sum airspeed, [9] steps below 5 m; from the state the guidance sees. */
+int orc_step_waypoint_stats(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state,
+                            const double* waypoints, int n_wp, int32_t* wp_index, int guidance, double acceptance_radius, int loop,
+                            float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
+                            double dt_ctrl, double dt, double dt_physics, int nthreads, double* mission_stats) {
     double h;
     const int K = substep_count(P, dt, dt_physics, &h);
     if (K < 0) return -1;
     if (n_wp < 1) return -2;
     const int nt = resolve_threads(nthreads);
     (void)nt;
-#pragma omp parallel for num_threads(nt) schedule(static)
+    double ms[16];
+    for (int k = 0; k < 16; ++k) ms[k] = 0.0;
+#pragma omp parallel for num_threads(nt) schedule(static) reduction(+ : ms[:16])
     for (int64_t i = 0; i < n; ++i) {
         int32_t idx = wp_index[i];
         if (idx >= n_wp) continue;                               /* mission complete: the demo stops stepping (:196-203) */
         /* MissionPlanner.update, mission_planner.py:128-171: 3-D distance < acceptance radius -> next waypoint */
         const double* wp = waypoints + (int64_t)idx * 4;
         const double dist = np_norm3(wp[0] - state[i], wp[1] - state[n + i], wp[2] - state[2 * n + i]);
+        int advanced = 0, lapped = 0;
         if (dist < acceptance_radius) {
             idx += 1;
-            if (idx >= n_wp && loop) idx = 0;
+            advanced = 1;
+            if (idx >= n_wp && loop) { idx = 0; lapped = 1; }
             wp_index[i] = idx;
-            if (idx >= n_wp) continue;
+            if (idx >= n_wp) { ms[1] += 1.0; ms[3] += 1.0; continue; }
             wp = waypoints + (int64_t)idx * 4;
         }
         double s[12], d[4], hc[3];
         for (int f = 0; f < 12; ++f) s[f] = state[(int64_t)f * n + i];
         orc_derived(s, d);
+        if (mission_stats) {
+            ms[0] += 1.0; ms[1] += advanced; ms[2] += lapped;
+            int prev = idx - 1;
+            if (prev < 0) prev = loop ? n_wp - 1 : -1;
+            double ct = 0.0;
+            if (prev >= 0) {
+                const double ax = waypoints[prev * 4 + 0], ay = waypoints[prev * 4 + 1];
+                const double bx = wp[0] - ax, by = wp[1] - ay, px = s[0] - ax, py = s[1] - ay;
+                const double len = sqrt(bx * bx + by * by);
+                if (len > 1e-6) ct = fabs((px * by - py * bx) / len);
+            }
+            ms[4] += ct; ms[5] += ct * ct;
+            ms[6] += fabs(d[1] - (-wp[2]));
+            ms[7] += np_norm3(wp[0] - s[0], wp[1] - s[1], wp[2] - s[2]);
+            ms[8] += d[0];
+            ms[9] += (d[1] < 5.0) ? 1.0 : 0.0;
+        }
         waypoint_guidance(C, guidance, wp, s, d, hc);
         if (hsa_cmd_out) for (int f = 0; f < 3; ++f) hsa_cmd_out[(int64_t)f * n + i] = hc[f];
         guided_step_one(P, C, n, i, state, hc, pid, pid_outer, surfaces_out, derived, dt_ctrl, K, h);
     }
+    if (mission_stats) for (int k = 0; k < 16; ++k) mission_stats[k] += ms[k];
     return K;
+}
+
+int orc_step_waypoint(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state,
+                      const double* waypoints, int n_wp, int32_t* wp_index, int guidance, double acceptance_radius, int loop,
+                      float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
+                      double dt_ctrl, double dt, double dt_physics, int nthreads) {
+    return orc_step_waypoint_stats(P, C, n, state, waypoints, n_wp, wp_index, guidance, acceptance_radius, loop, pid, pid_outer,
+                                   surfaces_out, derived, hsa_cmd_out, dt_ctrl, dt, dt_physics, nthreads, NULL);
 }
 
 /* ------------------------------------------------------------------------------------------

@@ -116,6 +116,12 @@ int orc_step_waypoint(const orc_aircraft_params* P, const orc_controller_params*
                       float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
                       double dt_ctrl, double dt, double dt_physics, int nthreads);
 
+/* the same with the fleet's mission statistics accumulated into mission_stats[16] (nullable; see acb_oracle.c) */
+int orc_step_waypoint_stats(const orc_aircraft_params* P, const orc_controller_params* C, int64_t n, double* state,
+                            const double* waypoints, int n_wp, int32_t* wp_index, int guidance, double acceptance_radius, int loop,
+                            float* pid, float* pid_outer, double* surfaces_out, double* derived, double* hsa_cmd_out,
+                            double dt_ctrl, double dt, double dt_physics, int nthreads, double* mission_stats);
+
 /* ---- rate-tracking environment (learned_controllers/envs/rate_env.py) ---- */
 
 enum { ORC_CTRL_EXTERNAL = 0, ORC_CTRL_RATE_PID = 1, ORC_CTRL_ATTITUDE_PID = 2, ORC_CTRL_RESIDUAL = 3 };

@@ -131,6 +131,7 @@ def lib() -> C.CDLL:
         L.orc_step_waypoint.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.c_int64, C.c_void_p,
                                         C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int]
+        L.orc_step_waypoint_stats.argtypes = L.orc_step_waypoint.argtypes + [C.c_void_p]
         L.orc_env_reset.argtypes = [C.POINTER(AircraftParams), C.POINTER(EnvConfig), C.POINTER(EnvBuffers),
                                     C.c_void_p, C.c_int]
         L.orc_env_step.argtypes = [C.POINTER(AircraftParams), C.POINTER(ControllerParams), C.POINTER(EnvConfig),
@@ -241,16 +242,20 @@ def step_hsa(params, cparams, state, cmd, pid, pid_outer, dt, dt_ctrl=None, dt_p
 
 def step_waypoint(params, cparams, state, waypoints, wp_index, pid, pid_outer, dt, guidance=GUIDANCE_PP, acceptance_radius=40.0,
                   loop=False, dt_ctrl=None, dt_physics=0.001, surfaces_out=None, derived_out=None, hsa_cmd_out=None,
-                  nthreads=0) -> int:
-    """MissionPlanner.update + WaypointAgent.compute_action + step; waypoints [n_wp][4] = north, east, down, speed."""
+                  nthreads=0, mission_stats=None) -> int:
+    """MissionPlanner.update + WaypointAgent.compute_action + step; waypoints [n_wp][4] = north, east, down, speed.
+    mission_stats: float64[16] accumulated (the fields of acb200_mission.stats)."""
     n = state.shape[1]
     _chk(state, np.float64, (13, n)); _chk(waypoints, np.float64); _chk(wp_index, np.int32, (n,))
     _chk(pid, np.float32, (18, n)); _chk(pid_outer, np.float32, (9, n))
     assert waypoints.ndim == 2 and waypoints.shape[1] == 4
-    k = lib().orc_step_waypoint(C.byref(params), C.byref(cparams), n, state.ctypes.data, waypoints.ctypes.data,
-                                waypoints.shape[0], wp_index.ctypes.data, guidance, acceptance_radius, int(loop),
-                                pid.ctypes.data, pid_outer.ctypes.data, _ptr(surfaces_out), _ptr(derived_out),
-                                _ptr(hsa_cmd_out), dt if dt_ctrl is None else dt_ctrl, dt, dt_physics, nthreads)
+    if mission_stats is not None:
+        _chk(mission_stats, np.float64, (16,))
+    k = lib().orc_step_waypoint_stats(C.byref(params), C.byref(cparams), n, state.ctypes.data, waypoints.ctypes.data,
+                                      waypoints.shape[0], wp_index.ctypes.data, guidance, acceptance_radius, int(loop),
+                                      pid.ctypes.data, pid_outer.ctypes.data, _ptr(surfaces_out), _ptr(derived_out),
+                                      _ptr(hsa_cmd_out), dt if dt_ctrl is None else dt_ctrl, dt, dt_physics, nthreads,
+                                      _ptr(mission_stats))
     if k < 0:
         raise ValueError(f"step_waypoint failed ({k})")
     return k

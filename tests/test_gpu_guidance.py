@@ -140,3 +140,50 @@ def test_fp32_build_flies_the_same_mission(mods):
     print(f"fp32 vs fp64 after 3000 control steps (30 s) of the square mission: ground track {dpos.max():.3f} m, altitude {dalt.max():.4f} m, "
           f"airspeed {dV.max():.4f} m/s apart at worst")
     assert dpos.max() <= 5.0 and dalt.max() <= 0.5 and dV.max() <= 0.2
+
+
+@pytest.mark.parametrize("K,loop", [(1, True), (10, False)])
+def test_mission_statistics_match_the_oracle(K, loop):
+    """acb200_mission.stats (BASELINE config 5's fleet statistics) from the one-aircraft kernel (K = 1) and the pair kernel
+    (K = 10, fp32) against the oracle's: event counts identical (fp64), sums to round-off / the fp32 tolerance."""
+    import torch
+    import acb200
+    from oracle import oracle as orc
+    from tools.bench_c5 import SQUARE, initial_states
+    n, steps, dt = 1024, 400, 0.01
+    dtp = dt / K
+    s0, idx0 = initial_states(n, 0)
+    wps = np.asarray(SQUARE, np.float64)
+    P, CP = orc.default_aircraft_params(), orc.default_controller_params()
+    state = s0.copy(); idx = idx0.copy()        # copies: the oracle advances them in place
+    pid = np.zeros((18, n), np.float32); outer = np.zeros((9, n), np.float32); ref = np.zeros(16)
+    for _ in range(steps):
+        orc.step_waypoint(P, CP, state, wps, idx, pid, outer, dt, guidance=orc.GUIDANCE_PP, acceptance_radius=40.0, loop=loop,
+                          dt_physics=dtp, mission_stats=ref)
+    assert ref[1] > n // 20 and ref[0] > 0.9 * n * steps                 # the advance branch ran
+    if not loop:
+        assert ref[3] > 0                                                # some aircraft completed the open mission
+    for precision, rtol in ((64, 1e-9), (32, 2e-3)):
+        fleet = acb200.AircraftFleet(n, precision=precision, config={"dt_physics": dtp})
+        fleet.reset(torch.as_tensor(s0))
+        fleet.set_mission(SQUARE, acceptance_radius=40.0, guidance="PP", loop=loop)
+        fleet.wp_index.copy_(torch.as_tensor(idx0))
+        for _ in range(steps):
+            fleet.step_waypoint(dt)
+        got = fleet.mission_stats_buf.cpu().numpy()
+        if precision == 64:
+            assert np.array_equal(got[[0, 1, 2, 3, 9]], ref[[0, 1, 2, 3, 9]]), (got, ref)
+            assert np.array_equal(fleet.wp_index.cpu().numpy(), idx)
+        else:
+            assert np.allclose(got[[0, 1, 2, 3]], ref[[0, 1, 2, 3]], rtol=5e-3), (got, ref)
+        assert np.allclose(got[[4, 5, 6, 7, 8]], ref[[4, 5, 6, 7, 8]], rtol=rtol), (precision, got, ref)
+        st = fleet.mission_stats(reset=True)
+        assert st["waypoints_reached"] == got[1] and abs(st["airspeed_mean"] - got[8] / got[0]) < 1e-12
+        assert float(fleet.mission_stats_buf.abs().sum()) == 0.0
+    # stats=False: no accumulator, same trajectories
+    a = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dtp}); b = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dtp})
+    for f, st in ((a, True), (b, False)):
+        f.reset(torch.as_tensor(s0)); f.set_mission(SQUARE, guidance="PP", loop=loop, stats=st); f.wp_index.copy_(torch.as_tensor(idx0))
+        for _ in range(50):
+            f.step_waypoint(dt)
+    assert torch.equal(a.state, b.state) and b.mission_stats_buf is None

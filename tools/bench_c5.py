@@ -13,6 +13,7 @@ METRIC = "aircraft control-steps/sec (waypoint->HSA->attitude->rate->surface cas
 UNIT = "env-steps/s"
 DT = 0.01
 SQUARE = [[300.0, 0.0, -100.0, 15.0], [300.0, 300.0, -100.0, 15.0], [0.0, 300.0, -100.0, 15.0], [0.0, 0.0, -100.0, 15.0]]
+# (+ 10 warp-reduced mission statistics per block: 80 B per 128 aircraft, not counted)
 # step_guided_kernel<T,1>: loads state 13 + pid 18 + pid_outer 9 + wp_index 1, stores state 13 + controls 4 + derived 4 +
 # pid 18 + pid_outer 9 + wp_index 1 (4-byte words, fp32 build)
 BYTES_PER_STEP = (13 + 18 + 9 + 1 + 13 + 4 + 4 + 18 + 9 + 1) * 4
@@ -35,11 +36,23 @@ def initial_states(n, id_offset, seed=7):
             x ^= x >> np.uint64(31)
         return (x >> np.uint64(11)).astype(np.float64) / float(1 << 53)
 
+    # The fleet is spread over the whole circuit: arc position by global id, +-20 m across the leg, +-10 deg of heading
+    # (BASELINE config 5's jitter), active waypoint = the end of the leg the aircraft is on.  In any window of the benchmark
+    # some aircraft are inside an acceptance radius, so MissionPlanner's index-advance branch and the corner guidance run
+    # (r01 started everyone at the first corner: nobody reached a waypoint in the timed 10 s).
+    arc = 1200.0 * u(4)
+    leg = np.minimum((arc // 300.0).astype(np.int64), 3)
+    along, across = arc - 300.0 * leg, -20.0 + 40.0 * u(1)
+    corner = np.array([[0.0, 0.0], [300.0, 0.0], [300.0, 300.0], [0.0, 300.0]])[leg]
+    direc = np.array([[1.0, 0.0], [0.0, 1.0], [-1.0, 0.0], [0.0, -1.0]])[leg]
     s = np.zeros((13, n), np.float64)
-    s[0] = -20.0 + 40.0 * u(1); s[1] = -20.0 + 40.0 * u(2); s[2] = -100.0
+    s[0] = corner[:, 0] + along * direc[:, 0] - across * direc[:, 1]
+    s[1] = corner[:, 1] + along * direc[:, 1] + across * direc[:, 0]
+    s[2] = -100.0
     s[3] = 15.0
-    s[8] = np.radians(-10.0 + 20.0 * u(3))
-    return s
+    yaw = np.array([0.0, np.pi / 2, np.pi, -np.pi / 2])[leg] + np.radians(-10.0 + 20.0 * u(3))
+    s[8] = np.arctan2(np.sin(yaw), np.cos(yaw))
+    return s, leg.astype(np.int32)
 
 
 def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
@@ -50,11 +63,19 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
     barrier, max_over_ranks = rt.barrier, rt.max_over_ranks
     n = args.envs
     fleet = acb200.AircraftFleet(n, precision=32, device=local, config={"dt_physics": DT})
-    fleet.reset(torch.as_tensor(initial_states(n, rank * n)))
-    fleet.set_mission(SQUARE, acceptance_radius=40.0, guidance="PP", loop=True)
+    s0, idx0 = initial_states(n, rank * n)
+    fleet.reset(torch.as_tensor(s0))
+    fleet.set_mission(SQUARE, acceptance_radius=40.0, guidance="PP", loop=True, stats=True)
+    if os.environ.get("ACB200_C5_STATS", "1") == "0":        # A/B aid: the kernel without the statistics accumulation
+        keep = fleet.mission_stats_buf
+        fleet.set_mission(SQUARE, acceptance_radius=40.0, guidance="PP", loop=True, stats=False)
+        fleet.mission_stats_buf = keep
+    fleet.wp_index.copy_(torch.as_tensor(idx0))
 
     for _ in range(warmup):
         fleet.step_waypoint(DT)
+    acb200.sharding.allreduce_episode_stats(fleet.mission_stats_buf)        # warm the communicator outside the timed region
+    fleet.mission_stats_buf.zero_()
     barrier()
     if clocks is not None and rank == 0:
         clocks.start()
@@ -62,12 +83,23 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    for _ in range(steps):
+    cev, mstats = [], None
+    for s_ in range(steps):
         fleet.step_waypoint(DT)
+        # the one collective of the path: mission statistics summed over ranks once per report interval (100 steps) and at the
+        # end of the run, inside the timed region, bracketed by its own events
+        if (s_ + 1) % 100 == 0 or s_ + 1 == steps:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            mstats = acb200.sharding.allreduce_episode_stats(fleet.mission_stats_buf)
+            b.record()
+            cev.append((a, b))
     ev1.record()
     barrier()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = fleet.ctx.launch_count - l0
+    coll_us = [1e3 * a.elapsed_time(b) for a, b in cev]
+    mvals = dict(zip(acb200._cabi.MISSION_STATS_NAMES, mstats.cpu().tolist()))
     value = n * world * steps / (ms * 1e-3)
 
     # end to end: the caller reads every aircraft's state back each step (AircraftInterface.step returns the state);
@@ -112,7 +144,16 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
                 "note": "autonomous mission: no per-step host input; state + derived outputs read back every step"},
         "gpu_launches": int(launches),
         "clocks": clk,
-        "mission": {"mean_waypoint_index": float(wp.float().mean()), "altitude_mean": float(alt.mean()), "altitude_min": float(alt.min()),
+        "collective": {"op": "all_reduce(sum) of the mission statistics, float64[16]" + ("" if world > 1 else " (one rank: a device copy, no NCCL call)"),
+                       "bytes": 128, "calls_in_timed_region": len(cev), "us_mean": sum(coll_us) / len(coll_us), "us_max": max(coll_us),
+                       "backend": "nccl" if world > 1 else None, "interval_steps": 100},
+        "mission": {"stats_all_ranks_timed_region": mvals,
+                    "waypoints_reached_per_1000_aircraft_steps": 1e3 * mvals["waypoints_reached"] / max(mvals["aircraft_steps"], 1.0),
+                    "cross_track_mean_m": mvals["cross_track_abs_sum"] / max(mvals["aircraft_steps"], 1.0),
+                    "altitude_error_mean_m": mvals["altitude_error_abs_sum"] / max(mvals["aircraft_steps"], 1.0),
+                    "airspeed_mean": mvals["airspeed_sum"] / max(mvals["aircraft_steps"], 1.0),
+                    "altitude_mean_rank0": float(alt.mean()), "altitude_min_rank0": float(alt.min()),
+                    "layout": "fleet spread over the circuit by global id (arc position, +-20 m across, +-10 deg heading)",
                     "sim_seconds": (warmup + steps + e2e_steps + 2) * DT},
     }
     if world == 1 and cpu_baseline and rank == 0:
@@ -128,9 +169,10 @@ def time_cpu(n, budget_s=None, steps=None, warmup=1):
     from oracle import oracle as orc
     cores = os.cpu_count() or 1
     P, CP = orc.default_aircraft_params(), orc.default_controller_params()
-    state = initial_states(n, 0)
+    state, idx = initial_states(n, 0)
+    state = np.ascontiguousarray(state); idx = np.ascontiguousarray(idx)
     wp = np.asarray(SQUARE, np.float64)
-    idx = np.zeros(n, np.int32); pid = np.zeros((18, n), np.float32); pid_outer = np.zeros((9, n), np.float32)
+    pid = np.zeros((18, n), np.float32); pid_outer = np.zeros((9, n), np.float32)
 
     def step():
         orc.step_waypoint(P, CP, state, wp, idx, pid, pid_outer, DT, guidance=orc.GUIDANCE_PP, acceptance_radius=40.0, loop=True,
