@@ -15,11 +15,13 @@ from .rollout import RolloutBufferB200
 from . import sensor, telemetry
 from . import config_loader, guidance
 from . import gym_env
+from . import flight_episode
+from .flight_episode import FlightEpisodeWriterB200
 from .gym_env import RateControlEnvB200, ResidualRateControlEnvB200
 from .guidance import HSAAgent, MissionPlanner, WaypointAgent
 from .telemetry import TelemetryRecorderB200
 from .sensor import NoisySensorB200, NoisySensorInterfaceB200, PerfectSensorB200
 
-__all__ = ["gym_env", "RateControlEnvB200", "ResidualRateControlEnvB200", "config_loader", "guidance", "HSAAgent", "WaypointAgent", "MissionPlanner", "telemetry", "TelemetryRecorderB200", "sensor", "NoisySensorB200", "NoisySensorInterfaceB200", "PerfectSensorB200", "policy", "LearnedPolicyB200", "rollout", "RolloutBufferB200", "_cabi", "adapters", "pid_bindings", "SimulationAircraftBackendB200", "vecenv", "sharding", "B200VecEnv", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
+__all__ = ["flight_episode", "FlightEpisodeWriterB200", "gym_env", "RateControlEnvB200", "ResidualRateControlEnvB200", "config_loader", "guidance", "HSAAgent", "WaypointAgent", "MissionPlanner", "telemetry", "TelemetryRecorderB200", "sensor", "NoisySensorB200", "NoisySensorInterfaceB200", "PerfectSensorB200", "policy", "LearnedPolicyB200", "rollout", "RolloutBufferB200", "_cabi", "adapters", "pid_bindings", "SimulationAircraftBackendB200", "vecenv", "sharding", "B200VecEnv", "Context", "AircraftFleet", "BatchedRateControlEnv", "default_aircraft_params",
            "default_controller_params", "kernel_info"]
 __version__ = "0.1.0"

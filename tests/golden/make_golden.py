@@ -697,7 +697,53 @@ def gen_policy_features():
     print("policy_features", feats.shape, "state_dict", [k for k in fe.state_dict()], "|features| max", float(feats.abs().max()))
 
 
+def gen_flight_episode():
+    """TensorBoard flight plugin: one episode logged by the UNMODIFIED FlightLoggerCallback._extract_flight_data
+    (tensorboard_flight/callbacks.py:152-263) and FlightLogger (logger.py:93-293) from a recorded RateControlEnv episode
+    (first 40 steps of case 0 of rate_env.npz, info dicts rebuilt from the recorded states).  Run with
+    PYTHONPATH=oracle/_ref:/root/reference:/root/reference/tensorboard_flight_plugin/src.  The fixture keeps the inputs,
+    the reference's step records and the episode JSON read back from the event file it wrote."""
+    import json
+    import tempfile
+    from tensorboard.backend.event_processing.event_file_loader import EventFileLoader
+    from tensorboard_flight.callbacks import FlightLoggerCallback
+    from tensorboard_flight.logger import FlightLogger
+    g = np.load(os.path.join(HERE, "rate_env.npz"))
+    T = 40
+    names = ("tracking", "smoothness", "stability", "oscillation", "survival")
+    with tempfile.TemporaryDirectory() as d:
+        logger = FlightLogger(d)
+        cb = FlightLoggerCallback(logger, agent_id="golden_agent")
+        inputs, records = [], []
+        for t in range(T):
+            obs, act, rew, st = g["c0_obs"][t], g["c0_actions"][t], float(g["c0_reward"][t]), g["c0_states"][t]
+            comp = {n: float(g["c0_components"][t][j]) for j, n in enumerate(names)}
+            info = {"time": 0.02 * (t + 1), "step": t + 1, "position": st[0:3].copy(), "reward_components": comp}
+            if t == T - 1:
+                info.update(termination_reason="crash_altitude", dones=True)
+            rec = cb._extract_flight_data(obs, act, rew, info, 1000 + t)
+            logger.log_flight_data(**rec)
+            inputs.append({"obs": obs.tolist(), "action": act.tolist(), "reward": rew, "step": 1000 + t,
+                           "info": {k: (v.tolist() if isinstance(v, np.ndarray) else v) for k, v in info.items()}})
+            records.append(json.loads(json.dumps(rec, default=lambda o: o.tolist())))
+        logger.end_episode(success=False, termination_reason="crash_altitude", config={"episode_num": 7}, tags=["training_step_1040"])
+        logger.close()
+        episodes = []
+        for fn in sorted(os.listdir(d)):
+            for ev in EventFileLoader(os.path.join(d, fn)).Load():
+                for v in ev.summary.value:
+                    if v.metadata.plugin_data.plugin_name == "flight":
+                        episodes.append({"tag": v.tag, "step": ev.step, "content": json.loads(v.metadata.plugin_data.content.decode())})
+    assert len(episodes) == 1
+    with open(os.path.join(HERE, "flight_episode.json"), "w") as f:
+        json.dump({"inputs": inputs, "records": records, "episode": episodes[0]}, f)
+    print("flight_episode.json", len(inputs), "steps; tag", episodes[0]["tag"], "keys", sorted(episodes[0]["content"]))
+
+
 if __name__ == "__main__":
+    if "flight" in sys.argv[1:]:
+        gen_flight_episode()
+        sys.exit(0)
     if "policy" in sys.argv[1:]:
         gen_policy_features()
         sys.exit(0)
