@@ -238,7 +238,8 @@ def measure_c3(args, rt, k_sub, steps, warmup, e2e_steps, cpu_baseline, clocks=N
     # ---- device-resident arm: `value` -------------------------------------------------------------
     for _ in range(warmup):
         env.step()
-    stats = acb200.sharding.allreduce_episode_stats(env.stats)       # warm the communicator outside the timed region
+    own_comm = acb200.sharding.init_comm(env.ctx)                    # the library's own NCCL communicator (C ABI) when world > 1
+    stats = acb200.sharding.allreduce_episode_stats(env.stats, ctx=env.ctx)       # warm it outside the timed region
     barrier()
     if clocks is not None and rank == 0:
         clocks.start()
@@ -254,7 +255,7 @@ def measure_c3(args, rt, k_sub, steps, warmup, e2e_steps, cpu_baseline, clocks=N
         if (s_ + 1) % 100 == 0 or s_ + 1 == steps:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            stats = acb200.sharding.allreduce_episode_stats(env.stats)
+            stats = acb200.sharding.allreduce_episode_stats(env.stats, ctx=env.ctx)
             b.record()
             cev.append((a, b))
     ev1.record()
@@ -264,7 +265,8 @@ def measure_c3(args, rt, k_sub, steps, warmup, e2e_steps, cpu_baseline, clocks=N
     coll_us = [1e3 * a.elapsed_time(b) for a, b in cev]
     collective = {"op": "all_reduce(sum) of the episode statistics, float64[16]" + ("" if world > 1 else " (one rank: a device copy, no NCCL call)"),
                   "bytes": 128, "calls_in_timed_region": len(cev), "us_mean": sum(coll_us) / len(coll_us), "us_max": max(coll_us),
-                  "backend": "nccl" if world > 1 else None, "interval_steps": 100}
+                  "backend": ("nccl, issued by the library (acb200_episode_stats, C ABI)" if own_comm else "nccl (torch.distributed)") if world > 1 else None,
+                  "interval_steps": 100}
     value = n * world * steps / (ms * 1e-3)
 
     # ---- end-to-end arm: host buffers, H2D of the step's commands + D2H of obs/reward/done every step

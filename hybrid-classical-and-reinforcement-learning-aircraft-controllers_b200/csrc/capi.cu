@@ -113,6 +113,7 @@ void acb200_destroy(acb200_ctx* ctx) {
     }
     if (ctx->fork) cudaEventDestroy(ctx->fork);
     if (ctx->scratch_i32) cudaFree(ctx->scratch_i32);
+    if (ctx->comm) acb200_comm_destroy(ctx);
     delete ctx;
 }
 

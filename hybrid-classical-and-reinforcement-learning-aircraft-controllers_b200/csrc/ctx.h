@@ -28,6 +28,9 @@ struct acb200_ctx {
     const void* param_table = nullptr;
     int64_t table_n = 0;
     int32_t table_precision = 0;
+    // NCCL communicator of the statistics all-reduce (comm.cu); opaque here, created by acb200_comm_init
+    void* comm = nullptr;
+    int comm_world = 0, comm_rank = 0;
     // device scratch owned by the handle (acb200_env_gather_done: one int per 1024 aircraft)
     int32_t* scratch_i32 = nullptr;
     int scratch_i32_len = 0;

@@ -19,9 +19,44 @@ def shard_range(n_total: int, rank: int, world: int):
     return first, base + (1 if rank < extra else 0)
 
 
-def allreduce_episode_stats(stats: torch.Tensor, group=None) -> torch.Tensor:
-    """Sum of the per-rank statistics vectors (envs.STATS_NAMES order); returns a new tensor, `stats` keeps accumulating."""
+def init_comm(ctx, group=None) -> bool:
+    """Give `ctx` (an ``_cabi.Context``) the library's own NCCL communicator over the ranks of the (initialised)
+    ``torch.distributed`` group: rank 0 draws the unique id through the C ABI, torch.distributed is only the plumbing that
+    carries its 128 bytes, every rank calls ``acb200_comm_init``.  Returns False (and leaves the context without a
+    communicator) when there is one rank, no process group, or a CPU-only (gloo) world."""
+    import ctypes as C
     import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2 or dist.get_backend(group) != "nccl":
+        return False
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    buf = (C.c_ubyte * 128)()
+    if rank == 0:
+        ctx.check(ctx.lib.acb200_comm_unique_id(ctx.handle, buf))
+    t = torch.tensor(list(buf), dtype=torch.uint8, device=torch.device("cuda", ctx.device))
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    raw = bytes(t.cpu().tolist())
+    ctx.check(ctx.lib.acb200_comm_init(ctx.handle, world, rank, raw))
+    return True
+
+
+def comm_info(ctx) -> dict:
+    import ctypes as C
+    w, r, v = C.c_int(), C.c_int(), C.c_int()
+    ctx.check(ctx.lib.acb200_comm_info(ctx.handle, C.byref(w), C.byref(r), C.byref(v)))
+    return {"world": w.value, "rank": r.value, "nccl_version": v.value}
+
+
+def allreduce_episode_stats(stats: torch.Tensor, group=None, ctx=None) -> torch.Tensor:
+    """Sum of the per-rank statistics vectors (envs.STATS_NAMES order); returns a new tensor, `stats` keeps accumulating.
+    With a context that owns a communicator (``init_comm``) this is ``acb200_episode_stats`` -- ncclAllReduce issued by the
+    library on torch's current stream; otherwise torch.distributed (gloo in the CPU tests, or no process group: a copy)."""
+    import ctypes as C
+    import torch.distributed as dist
+    if ctx is not None and stats.is_cuda and comm_info(ctx)["world"] > 0:
+        out = torch.empty_like(stats)
+        ctx.set_stream(torch.cuda.current_stream(stats.device).cuda_stream)
+        ctx.check(ctx.lib.acb200_episode_stats(ctx.handle, C.c_void_p(stats.data_ptr()), C.c_void_p(out.data_ptr()), stats.numel(), 1))
+        return out
     out = stats.detach().clone()
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)

@@ -299,6 +299,23 @@ int64_t acb200_noalloc_max_aircraft(void);
 /* number of chunks acb200_env_step_host cuts the fleet into; 0 = automatic (about 128k aircraft per chunk) */
 int acb200_set_host_chunks(acb200_ctx* ctx, int chunks);
 
+/* ---- the one collective of the path ----------------------------------------------------------------
+ * The aircraft are independent, so a fleet sharded over G GPUs (one process and one context per GPU) exchanges nothing per
+ * step; what crosses GPUs is the sum of the 16-double statistics vectors (acb200_env.stats, acb200_mission.stats) once per
+ * report interval: ncclAllReduce(SUM, float64) over NVLink / NVSwitch, latency-bound (128 bytes).  NCCL is resolved at run
+ * time (dlopen: $ACB200_NCCL_LIB, else the copy already loaded in the process, else the loader's path); without it these
+ * calls return ACB200_ENOSUP and everything else works.
+ *   rank 0:      acb200_comm_unique_id(ctx, id)            128 bytes, carried to the other ranks by the caller's own plumbing
+ *   every rank:  acb200_comm_init(ctx, world, rank, id)    collective (ncclCommInitRank)
+ *   every rank:  acb200_episode_stats(ctx, stats, out, 16, 1)   out = sum over ranks, enqueued on the context's stream
+ * do_allreduce = 0 copies stats to out (no communicator needed).  stats / out are device pointers; out may equal stats. */
+#define ACB200_COMM_ID_BYTES 128
+int acb200_comm_unique_id(acb200_ctx* ctx, void* id_out);
+int acb200_comm_init(acb200_ctx* ctx, int world, int rank, const void* id);
+int acb200_comm_destroy(acb200_ctx* ctx);
+int acb200_comm_info(const acb200_ctx* ctx, int* world, int* rank, int* nccl_version);
+int acb200_episode_stats(acb200_ctx* ctx, const double* stats, double* out, int32_t count, int32_t do_allreduce);
+
 /* ---- sensor model ------------------------------------------------------------------------
  * NoisySensorInterface, interfaces/sensor.py:137-263: Gaussian noise on position, velocity, attitude, angular rate (plus a
  * slowly drifting gyro bias), airspeed and altitude; gyro / accelerometer biases take one random-walk step per update.

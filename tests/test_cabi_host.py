@@ -29,7 +29,7 @@ def test_struct_sizes_match_header():
     cab = acb200._cabi
     assert C.sizeof(cab.AircraftParamsC) == 39 * 8
     assert C.sizeof(cab.PidConfigC) == 32 and C.sizeof(cab.PidStateC) == 24
-    assert C.sizeof(cab.ControllerParamsC) == 9 * 32 + 20 * 8 and C.sizeof(cab.MissionC) == 40
+    assert C.sizeof(cab.ControllerParamsC) == 9 * 32 + 20 * 8 and C.sizeof(cab.MissionC) == 48          # + the statistics pointer (r02)
     assert C.sizeof(cab.FleetC) == 8 + 8 + 4 * 8
     assert C.sizeof(cab.EnvC) == C.sizeof(cab.FleetC) + 19 * 8
     assert C.sizeof(cab.EnvConfigC) == 64

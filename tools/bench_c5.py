@@ -74,7 +74,8 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
 
     for _ in range(warmup):
         fleet.step_waypoint(DT)
-    acb200.sharding.allreduce_episode_stats(fleet.mission_stats_buf)        # warm the communicator outside the timed region
+    own_comm = acb200.sharding.init_comm(fleet.ctx)
+    acb200.sharding.allreduce_episode_stats(fleet.mission_stats_buf, ctx=fleet.ctx)        # warm the communicator outside the timed region
     fleet.mission_stats_buf.zero_()
     barrier()
     if clocks is not None and rank == 0:
@@ -91,7 +92,7 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
         if (s_ + 1) % 100 == 0 or s_ + 1 == steps:
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            mstats = acb200.sharding.allreduce_episode_stats(fleet.mission_stats_buf)
+            mstats = acb200.sharding.allreduce_episode_stats(fleet.mission_stats_buf, ctx=fleet.ctx)
             b.record()
             cev.append((a, b))
     ev1.record()
@@ -146,7 +147,8 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
         "clocks": clk,
         "collective": {"op": "all_reduce(sum) of the mission statistics, float64[16]" + ("" if world > 1 else " (one rank: a device copy, no NCCL call)"),
                        "bytes": 128, "calls_in_timed_region": len(cev), "us_mean": sum(coll_us) / len(coll_us), "us_max": max(coll_us),
-                       "backend": "nccl" if world > 1 else None, "interval_steps": 100},
+                       "backend": ("nccl, issued by the library (acb200_episode_stats, C ABI)" if own_comm else "nccl (torch.distributed)") if world > 1 else None,
+                       "interval_steps": 100},
         "mission": {"stats_all_ranks_timed_region": mvals,
                     "waypoints_reached_per_1000_aircraft_steps": 1e3 * mvals["waypoints_reached"] / max(mvals["aircraft_steps"], 1.0),
                     "cross_track_mean_m": mvals["cross_track_abs_sum"] / max(mvals["aircraft_steps"], 1.0),
