@@ -123,6 +123,7 @@ SYMBOLS = [
     "acb200_set_param_groups", "acb200_env_gather_done",
     "acb200_env_gather_done_noalloc", "acb200_noalloc_max_aircraft",
     "acb200_param_table_words", "acb200_build_param_table", "acb200_set_param_table",
+    "acb200_policy_env_rollout",
     "acb200_comm_unique_id", "acb200_comm_init", "acb200_comm_destroy", "acb200_comm_info", "acb200_episode_stats",
 ]
 
@@ -156,6 +157,7 @@ def load() -> C.CDLL:
     L.acb200_get_controller_params.argtypes = [vp, P(ControllerParamsC)]
     L.acb200_set_param_groups.argtypes = [vp, vp, P(i64), C.c_int32]
     L.acb200_env_gather_done.argtypes = [vp, P(EnvC), i64, vp, vp, vp, vp]
+    L.acb200_policy_env_rollout.argtypes = [vp, vp, P(EnvC), P(EnvConfigC), vp, vp, vp, C.c_int32, C.c_int32]
     L.acb200_comm_unique_id.argtypes = [vp, vp]
     L.acb200_comm_init.argtypes = [vp, i32, i32, vp]
     L.acb200_comm_destroy.argtypes = [vp]

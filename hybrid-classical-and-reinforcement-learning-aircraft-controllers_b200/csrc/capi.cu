@@ -485,15 +485,8 @@ int acb200_env_step_host(acb200_ctx* ctx, const acb200_env* env, const acb200_en
     const int64_t n = env->fleet.n;
     if (n == 0) return ACB200_OK;
     cudaSetDevice(ctx->device);
-    cudaError_t e = cudaSuccess;
-    if (!ctx->fork) {
-        for (int s = 0; s < acb200_ctx::kPipe && e == cudaSuccess; ++s) {
-            e = cudaStreamCreateWithFlags(&ctx->pipe[s], cudaStreamNonBlocking);
-            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->pipe_done[s], cudaEventDisableTiming);
-        }
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming);
-        if (e != cudaSuccess) return cuda_fail(ctx, e, "env_step_host: stream setup");
-    }
+    cudaError_t e = acb200_ctx_pipe_streams(ctx);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "env_step_host: stream setup");
     // chunks of a multiple of 128 aircraft (whole blocks, 16-byte aligned obs rows), about 128k aircraft each
     int chunks = ctx->host_chunks > 0 ? ctx->host_chunks : (int)((n + 131071) / 131072);
     if (chunks > 64) chunks = 64;
@@ -556,6 +549,28 @@ int acb200_set_host_chunks(acb200_ctx* ctx, int chunks) {
     ctx->host_chunks = chunks;
     return ACB200_OK;
 }
+
+}  // extern "C"
+
+cudaError_t acb200_ctx_pipe_streams(acb200_ctx* ctx) {
+    cudaError_t e = cudaSuccess;
+    if (ctx->fork) return e;
+    for (int s = 0; s < acb200_ctx::kPipe && e == cudaSuccess; ++s) {
+        e = cudaStreamCreateWithFlags(&ctx->pipe[s], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->pipe_done[s], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming);
+    return e;
+}
+
+int acb200_env_step_range_on(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action, int64_t first,
+                             int64_t count, cudaStream_t stream) {
+    if (first < 0 || count < 0 || first + count > env->fleet.n || first % 128) return fail(ctx, ACB200_EVALUE, "env_step_range: bad range");
+    if (count == 0) return ACB200_OK;
+    return env_step_impl(ctx, env, cfg, action, nullptr, first, count, stream, true);
+}
+
+extern "C" {
 
 float acb200_pid_compute_f32(const acb200_pid_config* cfg, acb200_pid_state* st, float setpoint, float measurement, float dt) {
     const float old_prev = st->error_prev;

@@ -35,3 +35,9 @@ struct acb200_ctx {
     int32_t* scratch_i32 = nullptr;
     int scratch_i32_len = 0;
 };
+
+// internal (not part of the C ABI): the worker streams of the host-step / rollout pipelines, created on first use (capi.cu)
+cudaError_t acb200_ctx_pipe_streams(acb200_ctx* ctx);
+// acb200_env_step_range on a given stream instead of the context's (capi.cu)
+int acb200_env_step_range_on(acb200_ctx* ctx, const acb200_env* env, const acb200_env_config* cfg, const float* action, int64_t first,
+                             int64_t count, cudaStream_t stream);

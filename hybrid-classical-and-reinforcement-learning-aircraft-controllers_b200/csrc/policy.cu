@@ -34,8 +34,9 @@ enum { B_FULL = 0, B_EMPTY = 4, B_ACC_FULL = 8, B_ACC_EMPTY = 10, B_ACT = 12, B_
 // 256-row tile: the leader's MMA warp issues cta_group::2 instructions for both, each block stages only HALF of every
 // weight stage (a 16 KB ring slot then carries twice the K depth: half the L2 traffic and half the ring round trips
 // per FLOP), epilogues and recurrent state stay per block.
-template <int CTA>
-__global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __grid_constant__ PolicyParams P) {
+template <int CTA, int kStages>
+__device__ __forceinline__ void policy_forward_body(const PolicyParams& P) {
+    constexpr uint32_t kBarOff = bar_off(kStages);
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* act = smem;
     const float* sbias = reinterpret_cast<const float*>(smem + kBiasOff);
@@ -393,6 +394,19 @@ __global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __gri
     }
 }
 
+template <int CTA, int kStages>
+__global__ void __launch_bounds__(kThreads, 1) policy_forward_kernel(const __grid_constant__ PolicyParams P) {
+    policy_forward_body<CTA, kStages>(P);
+}
+// The variant that shares its SMs with a block of the env step kernel (acb200_policy_env_rollout): 2 ring slots (204 KB of
+// shared memory) and at most 128 registers, so that 320 x 128 + 128 x 128 registers and 204 + 19 KB fit one SM together.
+#ifndef ACB_POLICY_LEAN_REGS
+#define ACB_POLICY_LEAN_REGS 128
+#endif
+__global__ void __maxnreg__(ACB_POLICY_LEAN_REGS) policy_forward_lean_kernel(const __grid_constant__ PolicyParams P) {
+    policy_forward_body<2, 2>(P);
+}
+
 // ---- recurrent state <-> (n, 256) f32 ---------------------------------------------------------------------------
 __global__ void state_export_kernel(int64_t n, const __nv_bfloat16* h_state, const float* c_state, float* h_out, float* c_out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over n * 256, unit fastest
@@ -594,8 +608,9 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         (e = alloc_error_flag(&p->d_error, &p->h_error)) != cudaSuccess ||
         (e = cudaMemcpy(p->d_weights, packed.data(), p->weight_bytes, cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMemcpy(p->d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(policy_forward_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(policy_forward_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes)) != cudaSuccess) {
+        (e = cudaFuncSetAttribute(policy_forward_kernel<1, kStagesDefault>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(kStagesDefault))) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(policy_forward_kernel<2, kStagesDefault>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(kStagesDefault))) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(policy_forward_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(2))) != cudaSuccess) {
         return pfail(ctx, ACB200_ECUDA, std::string("policy upload: ") + cudaGetErrorString(e));
     }
     if (p->cta == 2) {
@@ -681,8 +696,12 @@ int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes
     return ACB200_OK;
 }
 
-int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
-                          const uint8_t* episode_start_b, void* h_state, void* c_state, float* action_out) {
+}  // extern "C"
+
+// One forward of n aircraft on `stream` with a weight ring of `stages` slots (3: the standalone forward; 2: beside an env block).
+static int policy_forward_impl(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
+                               const uint8_t* episode_start_b, void* h_state, void* c_state, float* action_out, cudaStream_t stream,
+                               int stages) {
     if (!ctx || !p || !obs || !action_out) return pfail(ctx, ACB200_ENULL, "policy_forward: NULL argument");
     if (n < 0) return pfail(ctx, ACB200_EVALUE, "policy_forward: n < 0");
     if (n == 0) return ACB200_OK;
@@ -690,6 +709,8 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
     if (rec && (!h_state || !c_state)) return pfail(ctx, ACB200_ENULL, "policy_forward: recurrent policy needs h_state and c_state");
     if (((uintptr_t)obs & 7) || ((uintptr_t)action_out & 15) || (rec && (((uintptr_t)h_state & 15) || ((uintptr_t)c_state & 3))))
         return pfail(ctx, ACB200_EVALUE, "policy_forward: misaligned buffer");
+    if (p->cta != 2) stages = kStagesDefault;            // the 2-slot variant exists for the SM-pair kernel only
+    const uint32_t smem = smem_bytes(stages);
     cudaSetDevice(ctx->device);
     PolicyParams P = p->params;
     P.obs = obs; P.episode_start = episode_start; P.episode_start_b = episode_start_b;
@@ -709,13 +730,13 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
         p->resident = sms > 0 ? sms / p->cta : 1;
         if (p->cta == 2) {
             cudaLaunchConfig_t q = {};
-            q.gridDim = dim3(2 * (unsigned)p->resident); q.blockDim = dim3(kThreads); q.dynamicSmemBytes = kSmemBytes;
+            q.gridDim = dim3(2 * (unsigned)p->resident); q.blockDim = dim3(kThreads); q.dynamicSmemBytes = smem_bytes(kStagesDefault);
             cudaLaunchAttribute a[1];
             a[0].id = cudaLaunchAttributeClusterDimension;
             a[0].val.clusterDim.x = 2; a[0].val.clusterDim.y = 1; a[0].val.clusterDim.z = 1;
             q.attrs = a; q.numAttrs = 1;
             int clusters = 0;
-            if (cudaOccupancyMaxActiveClusters(&clusters, policy_forward_kernel<2>, &q) == cudaSuccess && clusters > 0)
+            if (cudaOccupancyMaxActiveClusters(&clusters, policy_forward_kernel<2, kStagesDefault>, &q) == cudaSuccess && clusters > 0)
                 p->resident = clusters;
             else
                 cudaGetLastError();
@@ -729,15 +750,16 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(2 * n_blocks);
         cfg.blockDim = dim3(kThreads);
-        cfg.dynamicSmemBytes = kSmemBytes;
-        cfg.stream = ctx->stream;
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
-        e = cudaLaunchKernelEx(&cfg, policy_forward_kernel<2>, P);
+        e = (stages == 2) ? cudaLaunchKernelEx(&cfg, policy_forward_lean_kernel, P)
+                          : cudaLaunchKernelEx(&cfg, policy_forward_kernel<2, kStagesDefault>, P);
     } else {
-        policy_forward_kernel<1><<<n_blocks, kThreads, kSmemBytes, ctx->stream>>>(P);
+        policy_forward_kernel<1, kStagesDefault><<<n_blocks, kThreads, smem, stream>>>(P);
         e = cudaGetLastError();
     }
     ctx->launches += 1;
@@ -746,13 +768,74 @@ int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const fl
         static int dumped = 0;
         if (dumped++ == 3) {
             std::vector<long long> h(2048);
-            cudaStreamSynchronize(ctx->stream);
+            cudaStreamSynchronize(stream);
             cudaMemcpy(h.data(), trace, h.size() * sizeof(long long), cudaMemcpyDeviceToHost);
             FILE* f = fopen(getenv("ACB200_POLICY_TRACE"), "w");
             if (f) { for (size_t i = 0; i < h.size(); ++i) if (h[i]) fprintf(f, "%zu %lld\n", i, h[i]); fclose(f); }
         }
     }
     return ACB200_OK;
+}
+
+extern "C" {
+
+int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
+                          const uint8_t* episode_start_b, void* h_state, void* c_state, float* action_out) {
+    if (!ctx) return ACB200_ENULL;
+    static const int ring = getenv("ACB200_POLICY_RING") ? atoi(getenv("ACB200_POLICY_RING")) : kStagesDefault;   // A/B aid: 2 or 3
+    return policy_forward_impl(ctx, p, n, obs, episode_start, episode_start_b, h_state, c_state, action_out, ctx->stream, ring == 2 ? 2 : kStagesDefault);
+}
+
+// K closed-loop steps (policy forward -> env step with that action) for the whole fleet in ONE call (BASELINE config C4:
+// "policy forward fused with env step and reward").  The fleet is cut into `parts` ranges (multiples of 256 aircraft: whole
+// SM-pair tiles of the recurrent state), each with its own stream: within a part the steps are ordered, forward -> env ->
+// forward ...; between parts nothing is, so part A's env step (FP32 / SFU pipes, 19 KB of shared memory per block) runs on
+// the same SMs, at the same time, as part B's policy forward (tensor pipe + MUFU; persistent, 204 KB with the 2-slot ring) --
+// the policy kernel leaves the FP32 pipes ~85 % idle, which is where the env step goes.  Everything is enqueued behind the
+// context's stream and that stream continues after all parts: the call is asynchronous and can be captured in a CUDA graph.
+int acb200_policy_env_rollout(acb200_ctx* ctx, acb200_policy* p, const acb200_env* env, const acb200_env_config* cfg, void* h_state,
+                              void* c_state, float* action, int32_t steps, int32_t parts) {
+    if (!ctx || !p || !env || !cfg || !action) return pfail(ctx, ACB200_ENULL, "policy_env_rollout: NULL argument");
+    if (steps < 0 || parts < 0 || parts > acb200_ctx::kPipe) return pfail(ctx, ACB200_EVALUE, "policy_env_rollout: steps < 0 or parts outside [0, 3]");
+    if (cfg->controller != ACB200_CTRL_EXTERNAL && cfg->controller != ACB200_CTRL_RESIDUAL)
+        return pfail(ctx, ACB200_EVALUE, "policy_env_rollout: the env must take its action from the policy (controller external or residual)");
+    const int64_t n = env->fleet.n;
+    if (n == 0 || steps == 0) return ACB200_OK;
+    if (parts == 0) parts = n >= 65536 ? 2 : 1;
+    const bool rec = p->params.recurrent_layer >= 0;
+    int64_t per = ((n + parts - 1) / parts + 255) / 256 * 256;
+    cudaSetDevice(ctx->device);
+    cudaError_t e = cudaSuccess;
+    if (parts == 1) {
+        for (int s = 0; s < steps; ++s) {
+            int rc = policy_forward_impl(ctx, p, n, env->obs, env->terminated, env->truncated, h_state, c_state, action, ctx->stream, kStagesDefault);
+            if (!rc) rc = acb200_env_step(ctx, env, cfg, action);
+            if (rc) return rc;
+        }
+        return ACB200_OK;
+    }
+    if ((e = acb200_ctx_pipe_streams(ctx)) != cudaSuccess) return pfail(ctx, ACB200_ECUDA, std::string("rollout streams: ") + cudaGetErrorString(e));
+    e = cudaEventRecord(ctx->fork, ctx->stream);
+    int used = 0;
+    for (int k = 0; k < parts && e == cudaSuccess; ++k) {
+        const int64_t first = (int64_t)k * per, count = (n - first < per) ? (n - first) : per;
+        if (count <= 0) break;
+        used = k + 1;
+        const cudaStream_t st = ctx->pipe[k];
+        if ((e = cudaStreamWaitEvent(st, ctx->fork, 0)) != cudaSuccess) break;
+        const int64_t tile = first / kTile;
+        void* hk = rec ? (void*)((uint8_t*)h_state + tile * (int64_t)kHTileBytes) : nullptr;
+        void* ck = rec ? (void*)((float*)c_state + tile * (int64_t)kHidden * kTile) : nullptr;
+        for (int s = 0; s < steps; ++s) {
+            int rc = policy_forward_impl(ctx, p, count, env->obs + first * ACB200_POLICY_OBS, env->terminated + first, env->truncated + first, hk,
+                                         ck, action + first * ACB200_POLICY_ACT, st, 2);
+            if (!rc) rc = acb200_env_step_range_on(ctx, env, cfg, action, first, count, st);
+            if (rc) return rc;
+        }
+        if ((e = cudaEventRecord(ctx->pipe_done[k], st)) != cudaSuccess) break;
+    }
+    for (int k = 0; k < used && e == cudaSuccess; ++k) e = cudaStreamWaitEvent(ctx->stream, ctx->pipe_done[k], 0);
+    return e == cudaSuccess ? ACB200_OK : pfail(ctx, ACB200_ECUDA, std::string("policy_env_rollout: ") + cudaGetErrorString(e));
 }
 
 int acb200_policy_state_export(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const void* h_state, const void* c_state,
@@ -787,7 +870,7 @@ int acb200_policy_info(const acb200_policy* p, double* flops_per_aircraft, size_
     if (!p) return ACB200_ENULL;
     if (flops_per_aircraft) *flops_per_aircraft = p->flops_per_aircraft;
     if (weight_bytes) *weight_bytes = p->weight_bytes;
-    if (smem_bytes) *smem_bytes = (int)kSmemBytes;
+    if (smem_bytes) *smem_bytes = (int)acbp::smem_bytes(kStagesDefault);
     return ACB200_OK;
 }
 

@@ -21,15 +21,22 @@ constexpr int kMaxLayers = 8;
 #ifndef ACB_POLICY_STAGES
 #define ACB_POLICY_STAGES 3
 #endif
-constexpr int kStages = ACB_POLICY_STAGES;   // weight ring depth
-constexpr uint32_t kStageBytes = 16384;
+constexpr int kStagesDefault = ACB_POLICY_STAGES;   // weight ring depth of the standalone forward
+constexpr int kStagesMax = 4;
+#ifndef ACB_POLICY_STAGE_BYTES
+#define ACB_POLICY_STAGE_BYTES 16384
+#endif
+constexpr uint32_t kStageBytes = ACB_POLICY_STAGE_BYTES;
 constexpr uint32_t kXBytes = 98304;      // activation buffer X: up to K = 384 (features 128 | h 256)
 constexpr uint32_t kYBytes = 65536;      // activation buffer Y: up to K = 256
 constexpr int kMaxBias = 3072;           // every layer's bias, fp32, resident for the whole chain
 constexpr uint32_t kBiasOff = kXBytes + kYBytes;
 constexpr uint32_t kStageOff = kBiasOff + kMaxBias * 4;
-constexpr uint32_t kBarOff = kStageOff + kStages * kStageBytes;
-constexpr uint32_t kSmemBytes = kBarOff + 256;
+// The ring depth is a template parameter of the kernel: 3 slots for the forward on its own; 2 slots (16 KB less shared
+// memory: 204 KB) where a block of the env step kernel has to fit on the same SM beside the persistent policy block
+// (acb200_policy_env_rollout).  Measured, 262 144 aircraft: 0.526 ms with 3 x 16 KB, 0.556 with 2 x 16 KB, 0.599 with 4 x 8 KB.
+__host__ __device__ constexpr uint32_t bar_off(int stages) { return kStageOff + (uint32_t)stages * kStageBytes; }
+__host__ __device__ constexpr uint32_t smem_bytes(int stages) { return bar_off(stages) + 256; }
 constexpr uint32_t kKChunkBytes = kTile * 16;   // one 8-wide K slab of an activation buffer (2048 B)
 constexpr int kHidden = 256;
 constexpr uint32_t kHTileBytes = kHidden * kTile * 2;   // one tile of h, bf16, already in operand layout

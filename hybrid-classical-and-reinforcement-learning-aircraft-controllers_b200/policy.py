@@ -158,6 +158,24 @@ class LearnedPolicyB200:
             out.data_ptr() + first * ACT_DIM * 4))
         return out
 
+    def rollout(self, env, steps: int, parts: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``steps`` closed-loop steps of ``env`` (a ``BatchedRateControlEnv`` with controller "external" or "residual" on the
+        SAME context) flown by this policy, in one C-ABI call (``acb200_policy_env_rollout``): per step the action is
+        ``forward(env.obs, (env.terminated, env.truncated))`` and the env takes it.  The fleet advances in ``parts``
+        independent ranges (0 = automatic) so that one range's env step overlaps another's forward; the results equal the
+        step-by-step sequence.  Asynchronous on torch's current stream; capture it in a ``torch.cuda.CUDAGraph`` after one
+        warm-up call to replay a whole rollout with one launch.  Returns the action tensor (the last step's actions)."""
+        if env.ctx is not self.ctx:
+            raise ValueError("policy and env must share one context (pass ctx=env.ctx to LearnedPolicyB200)")
+        if env.n != self.n:
+            raise ValueError(f"policy is for {self.n} aircraft, env has {env.n}")
+        out = self.action if out is None else out
+        self._bind_stream()
+        self.ctx.check(self.lib.acb200_policy_env_rollout(
+            self.ctx.handle, self.handle, C.byref(env.c), C.byref(env.cfg), self.h_state.data_ptr() if self.recurrent else None,
+            self.c_state.data_ptr() if self.recurrent else None, out.data_ptr(), int(steps), int(parts)))
+        return out
+
     def predict(self, observation, state=None, episode_start=None, deterministic: bool = True):
         """stable-baselines3's ``predict`` signature over numpy arrays (learned_rate_agent.py:220-227): returns
         ``(actions, state)`` where ``state`` is ``(h, c)`` with shapes (1, n, 256), as sb3-contrib hands them around."""

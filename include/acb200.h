@@ -397,6 +397,16 @@ int acb200_policy_state_bytes(const acb200_policy* p, int64_t n, size_t* h_bytes
  * in place; NULL for the MLP policy); action_out f32[n][4] clipped to the action space (rate_env.py:128-138). */
 int acb200_policy_forward(acb200_ctx* ctx, acb200_policy* p, int64_t n, const float* obs, const uint8_t* episode_start,
                           const uint8_t* episode_start_b, void* h_state, void* c_state, float* action_out);
+/* `steps` closed-loop steps of the whole fleet in one call: action = policy(env.obs, episode_start = env.terminated |
+ * env.truncated); acb200_env_step(action); ... (BASELINE config C4: policy forward fused with env step and reward; the loop
+ * of learned_controllers/eval_rate.py:89-108 for every aircraft).  cfg->controller must be EXTERNAL or RESIDUAL.  `action`
+ * float[n][4] is the caller's buffer the actions travel through (it holds the last step's afterwards).  The fleet is cut into
+ * `parts` ranges (0 = automatic: 2 from 65 536 aircraft, else 1; at most 3) that advance independently on internal streams,
+ * so that one part's env step runs beside another part's policy forward on the same SMs; results are identical to the
+ * sequence of acb200_policy_forward + acb200_env_step calls.  Asynchronous (the context's stream continues after every part)
+ * and capturable in a CUDA graph after one warm-up call. */
+int acb200_policy_env_rollout(acb200_ctx* ctx, acb200_policy* p, const acb200_env* env, const acb200_env_config* cfg, void* h_state,
+                              void* c_state, float* action, int32_t steps, int32_t parts);
 /* recurrent state <-> the (n, 256) f32 arrays of SB3's lstm_states; all device pointers */
 int acb200_policy_state_export(acb200_ctx* ctx, const acb200_policy* p, int64_t n, const void* h_state, const void* c_state,
                                float* h_out, float* c_out);

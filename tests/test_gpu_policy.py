@@ -209,3 +209,64 @@ def test_pipelined_host_step_equals_the_plain_closed_loop():
     assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2].view(torch.int32), outs[1][2].view(torch.int32))
     assert torch.equal(outs[0][3].view(torch.int32), outs[1][3].view(torch.int32))
     assert sum(int(h[2].sum() + h[3].sum()) for h in outs[1][0]) >= n          # episodes ended and restarted on the way
+
+
+@pytest.mark.parametrize("kind,n,parts", [("lstm", 1024, 2), ("lstm", 1300, 3), ("mlp", 2048, 2), ("lstm", 512, 1)])
+def test_rollout_call_equals_the_step_by_step_closed_loop(kind, n, parts):
+    """acb200_policy_env_rollout (K closed-loop steps in one call, the fleet in `parts` ranges on their own streams, the
+    2-slot-ring policy kernel beside the env kernel) against forward + env.step in a Python loop: every buffer bit-identical,
+    through auto-resets; and the same rollout replayed from a CUDA graph."""
+    import acb200
+    from acb200.policy import random_policy_state_dict
+    sd = random_policy_state_dict(kind, 0)
+    envs, pols = [], []
+    for _ in range(3):
+        env = acb200.BatchedRateControlEnv(n, controller="external", precision=32, seed=13, episode_length=0.3)     # 15-step episodes
+        pol = acb200.LearnedPolicyB200(sd, kind=kind, n=n, ctx=env.ctx)
+        env.reset()
+        envs.append(env); pols.append(pol)
+    (ea, pa), (eb, pb), (ec, pc) = zip(envs, pols)
+    steps = 40
+    for _ in range(steps):
+        ea.step(pa(ea.obs, (ea.terminated, ea.truncated)))
+    pb.rollout(eb, steps, parts=parts)
+    torch.cuda.synchronize()
+    names = ("state", "obs", "reward", "terminated", "truncated", "prev_action", "rew_mem", "step_count", "episode_idx")
+    for name in names:
+        assert torch.equal(getattr(ea, name), getattr(eb, name)), name
+    assert torch.equal(pa.action, pb.action)
+    if kind == "lstm":
+        assert torch.equal(pa.h_state, pb.h_state) and torch.equal(pa.c_state, pb.c_state)
+    assert float(ea.stats[0]) > 0                                     # episodes ended on the way
+    # CUDA graph: 10 steps in a warm-up call, 10 steps captured (a capture records, it does not run), replayed 3 times = 40
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        pc.rollout(ec, 10, parts=parts)
+    s.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        pc.rollout(ec, 10, parts=parts)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for name in names:
+        assert torch.equal(getattr(ea, name), getattr(ec, name)), "graph: " + name
+
+
+def test_rollout_argument_errors():
+    import acb200
+    from acb200.policy import random_policy_state_dict
+    env = acb200.BatchedRateControlEnv(512, controller="rate_pid", precision=32)
+    pol = acb200.LearnedPolicyB200(random_policy_state_dict("mlp", 0), kind="mlp", n=512, ctx=env.ctx)
+    env.reset()
+    with pytest.raises(ValueError, match="external or residual"):
+        pol.rollout(env, 2)
+    other = acb200.BatchedRateControlEnv(512, controller="external", precision=32)
+    with pytest.raises(ValueError, match="share one context"):
+        pol.rollout(other, 2)
+    ext = acb200.BatchedRateControlEnv(512, controller="external", precision=32, ctx=env.ctx)
+    ext.reset()
+    with pytest.raises(ValueError):
+        pol.rollout(ext, 2, parts=7)
+    pol.rollout(ext, 0)                                                # zero steps: a no-op

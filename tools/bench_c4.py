@@ -1,6 +1,7 @@
 """bench.py --workload c4: BASELINE.json configs[3] -- 262 144 aircraft per GPU flown by the learned LSTM rate policy
 (random init, torch seed 0), medium difficulty, dt 0.02 (20 RK4 substeps).  One step = policy forward
-(policy_forward_kernel, tcgen05) + env step (env_step_kernel<float>, external action) for every aircraft."""
+(policy_forward_kernel, tcgen05) + env step (env_step_pair_kernel, external action) for every aircraft, issued as ONE
+acb200_policy_env_rollout call for all the timed steps (two halves of the fleet on their own streams)."""
 from __future__ import annotations
 
 import json
@@ -50,9 +51,39 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
         env.step(act)
     ev1.record()
     barrier()
-    ms = max_over_ranks(ev0.elapsed_time(ev1))
+    seq_ms = max_over_ranks(ev0.elapsed_time(ev1))
     policy_ms = sum(a.elapsed_time(b) for a, b in pev) / steps
+    # ---- the same closed loop as ONE call (acb200_policy_env_rollout): two halves of the fleet on their own streams, one
+    # half's env step beside the other half's policy forward.  This is the C4 step that `value` reports; the sequence above
+    # stays for the per-kernel times (the policy kernel alone, on the launching stream) behind the roofline.
+    parts = int(os.environ.get("ACB200_C4_PARTS", "2"))
+    pol.rollout(env, 4, parts=parts)
+    barrier()
+    l0 = env.ctx.launch_count
+    ev0.record()
+    pol.rollout(env, steps, parts=parts)
+    ev1.record()
+    barrier()
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = env.ctx.launch_count - l0
+    # and replayed from a CUDA graph (one graph launch per 20 steps)
+    graph_ms = None
+    try:
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                pol.rollout(env, 20, parts=parts)
+        barrier()
+        reps = max(1, steps // 20)
+        ev0.record()
+        for _ in range(reps):
+            g.replay()
+        ev1.record()
+        barrier()
+        graph_ms = max_over_ranks(ev0.elapsed_time(ev1)) / (20 * reps)
+    except Exception as exc:                      # a failed capture must not cost the measurement
+        graph_ms = f"capture failed: {exc}"
     stats = acb200.sharding.allreduce_episode_stats(env.stats)
     value = n * world * steps / (ms * 1e-3)
 
@@ -106,7 +137,9 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
                      "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if "bf16_tflops_sustained" in peaks else "fallback",
                      "flop_per_aircraft": info["flops_per_aircraft"], "algorithmic_flop_per_launch": flops,
                      "weight_bytes_per_tile": info["weight_bytes"], "traffic": traffic, "traffic_source": rt.traffic.get("_source")},
-        "kernels_ms": {"policy_forward_kernel": policy_ms, "env_step_kernel": ms / steps - policy_ms},
+        "kernels_ms": {"policy_forward_kernel": policy_ms, "env_step_kernel": seq_ms / steps - policy_ms,
+                       "sequential_step": seq_ms / steps, "rollout_call_step": ms / steps, "rollout_graph_step": graph_ms,
+                       "rollout_parts": parts},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": e2e_ms / e2e_steps},
         "gpu_launches": int(launches),
