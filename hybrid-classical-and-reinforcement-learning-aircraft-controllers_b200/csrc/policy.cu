@@ -290,7 +290,10 @@ __device__ __forceinline__ void policy_forward_body(const PolicyParams& P) {
                     }
                 } else if (L.epi == EPI_LSTM0) {
                     // h0 = c0 = 0 on every call (lstm_policy.py:86): c = sig(i) tanh(g), h = sig(o) tanh(c); f unused
-                    const int U = L.N_c / 3, w = U / kParts, j0 = part * w;
+                    // chunk = [i | g | o] of U units (N_c = 3U) or [i | (f: zero, unused) | g | o] (N_c = 4U = 256, full-width MMAs)
+                    const bool four = L.N_c == 256;
+                    const int U = four ? 64 : L.N_c / 3, w = U / kParts, j0 = part * w;
+                    const int og = four ? 2 * U : U, oo = four ? 3 * U : 2 * U;
                     mbar_wait(bar(B_ACC_FULL + a), (chunk_it >> 1) & 1, P.error_flag, 500 + l);
                     __syncwarp();
                     tc_fence_after();
@@ -303,10 +306,10 @@ __device__ __forceinline__ void policy_forward_body(const PolicyParams& P) {
                     for (int j = j0; j < j0 + w; j += 16) {
                         uint32_t vi[16], vg[16], vo[16]; float bi[16], bg[16], bo[16], h[16];
                         tmem_ld16_issue(t0 + j, vi);
-                        tmem_ld16_issue(t0 + U + j, vg);
-                        tmem_ld16_issue(t0 + 2 * U + j, vo);
+                        tmem_ld16_issue(t0 + og + j, vg);
+                        tmem_ld16_issue(t0 + oo + j, vo);
                         tmem_ld_wait(vi); tmem_ld_wait(vg); tmem_ld_wait(vo);
-                        load_bias16(bias + j, bi); load_bias16(bias + U + j, bg); load_bias16(bias + 2 * U + j, bo);
+                        load_bias16(bias + j, bi); load_bias16(bias + og + j, bg); load_bias16(bias + oo + j, bo);
 #pragma unroll
                         for (int q = 0; q < 16; ++q) {
                             const float cc = sigmoid_half(__uint_as_float(vi[q]), bi[q]) * tanh_fast(__uint_as_float(vg[q]) + bg[q]);
@@ -520,21 +523,27 @@ HostLayer dense_layer(int epi, const float* W, const float* B, int out, int in, 
 // stateless (h0 = c0 = 0): i,g,o (3 gates, W_hh and the f gate drop out); stateful: i,f,g,o over [W_ih | W_hh].
 HostLayer lstm_layer(bool stateful, const float* W_ih, const float* W_hh, const float* b_ih, const float* b_hh, int in, int U,
                      uint32_t in_off, uint32_t out_off) {
-    const int gates = stateful ? 4 : 3, K = stateful ? in + kHidden : in;
+    // ACB200_POLICY_WIDE=1 (experiment, off by default): the stateless layers issue full-width N = 256 instructions, the unused
+    // forget gate carried as a fourth block of ZERO rows (33 % more multiply-adds on those two layers).  The idea: a K = 16 step
+    // of an SM pair costs 126 cycles at N = 256 against 148-162 at N = 192.  Measured (r02, 262 144 aircraft): 0.5349 ms against
+    // 0.5316 ms -- slower; those chunks are not bound by the instruction shape.  Results are identical either way.
+    static const bool wide = getenv("ACB200_POLICY_WIDE") && getenv("ACB200_POLICY_WIDE")[0] == '1';
+    const int gates = (stateful || wide) ? 4 : 3, K = stateful ? in + kHidden : in;
     static const int kStateless[3] = {0, 2, 3};
     HostLayer h = make_layer(stateful ? EPI_LSTM : EPI_LSTM0, K, 32, gates * U, kHidden / U, in_off, out_off);
     for (int c = 0; c < kHidden / U; ++c)
         for (int g = 0; g < gates; ++g)
             for (int u = 0; u < U; ++u) {
-                const int src = (stateful ? g : kStateless[g]) * kHidden + c * U + u;
+                if (!stateful && gates == 4 && g == 1) continue;                       // the unused forget gate: zero rows, zero bias
+                const int src = ((stateful || gates == 4) ? g : kStateless[g]) * kHidden + c * U + u;
                 const size_t dst = (size_t)(c * gates + g) * U + u;
                 for (int k = 0; k < in; ++k) h.w[dst * K + k] = W_ih[(size_t)src * in + k];
                 if (stateful)
                     for (int k = 0; k < kHidden; ++k) h.w[dst * K + in + k] = W_hh[(size_t)src * kHidden + k];
-                const bool sigmoid_gate = (stateful ? g : kStateless[g]) != 2;        // i, f, o; g is the tanh gate
+                const bool sigmoid_gate = ((stateful || gates == 4) ? g : kStateless[g]) != 2;        // i, f, o; g is the tanh gate
                 h.b[dst] = (sigmoid_gate ? 0.5f : 1.0f) * (b_ih[src] + b_hh[src]);   // see sigmoid_half()
             }
-    h.real_flops = 2.0 * gates * kHidden * K;
+    h.real_flops = 2.0 * (stateful ? 4 : 3) * kHidden * K;          // algorithmic: the zero forget-gate block is not counted
     return h;
 }
 
@@ -574,7 +583,7 @@ int finish_policy(acb200_ctx* ctx, acb200_policy* p, std::vector<HostLayer>& lay
         d.bias_off = (int)bias.size();
         bias.insert(bias.end(), h.b.begin(), h.b.end());
         if (d.epi == EPI_LSTM) p->params.recurrent_layer = (int)l;
-        if ((d.epi == EPI_LSTM && d.N_c != 256) || (d.epi == EPI_LSTM0 && d.N_c % (48 * kParts)) ||
+        if ((d.epi == EPI_LSTM && d.N_c != 256) || (d.epi == EPI_LSTM0 && (d.N_c != 256 && d.N_c % (48 * kParts))) ||
             (d.epi == EPI_RELU && d.N_c % (16 * kParts)))
             return pfail(ctx, ACB200_EVALUE, "policy: chunk width does not split into 16-column groups over the epilogue warps");
         const int n_half = d.N_c / p->cta;      // a CTA pair splits every stage's columns in two halves, leader first

@@ -29,7 +29,7 @@ constexpr int kStagesMax = 4;
 constexpr uint32_t kStageBytes = ACB_POLICY_STAGE_BYTES;
 constexpr uint32_t kXBytes = 98304;      // activation buffer X: up to K = 384 (features 128 | h 256)
 constexpr uint32_t kYBytes = 65536;      // activation buffer Y: up to K = 256
-constexpr int kMaxBias = 3072;           // every layer's bias, fp32, resident for the whole chain
+constexpr int kMaxBias = 3584;           // every layer's bias, fp32, resident for the whole chain (3 536 with full-width stateless chunks)
 constexpr uint32_t kBiasOff = kXBytes + kYBytes;
 constexpr uint32_t kStageOff = kBiasOff + kMaxBias * 4;
 // The ring depth is a template parameter of the kernel: 3 slots for the forward on its own; 2 slots (16 KB less shared
