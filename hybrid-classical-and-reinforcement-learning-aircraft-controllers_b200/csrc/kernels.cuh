@@ -420,6 +420,61 @@ __global__ void __launch_bounds__(kBlock) env_reset_kernel(EnvPtrs<T> B, const _
     for (int k = 0; k < ACB200_OBS_DIM; ++k) B.obs[i * ACB200_OBS_DIM + k] = o[k];   // masked resets are sparse: direct rows
 }
 
+// Sum of every thread's 16 statistics contributions (STATS order of acb200.h) into the global vector; every thread of the
+// block must call it.  Written for instruction count (it is ~6 % of a K = 1 step as a five-step tree per field): the six
+// integer-valued fields -- episodes, length, crashes, truncations, repairs, aircraft-steps -- go through the integer warp
+// reduction (one REDUX each); the eight reward components through a TRANSPOSED warp reduction (lanes split the fields
+// between them while they fold: 4 + 2 + 1 + 2 = 9 shuffles for eight values); return and return^2 as a transposed pair
+// (5 shuffles).  14 shuffles instead of 80; warp results meet in shared memory without atomics.
+template <typename T, int BLOCK>
+__device__ __forceinline__ void block_accumulate_env_stats(const T (&v)[ACB200_STATS_FIELDS], double* __restrict__ global) {
+    __shared__ T part[BLOCK / 32][ACB200_STATS_FIELDS];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = __reduce_add_sync(full, (int)v[0]), c3 = __reduce_add_sync(full, (int)v[3]), c4 = __reduce_add_sync(full, (int)v[4]),
+              c5 = __reduce_add_sync(full, (int)v[5]), c14 = __reduce_add_sync(full, (int)v[14]), c15 = __reduce_add_sync(full, (int)v[15]);
+    const bool b16 = (lane & 16) != 0, b8 = (lane & 8) != 0, b4 = (lane & 4) != 0;
+    // components 6..13
+    T x[4], z[2];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        x[q] = b16 ? v[10 + q] : v[6 + q];
+        const T y = b16 ? v[6 + q] : v[10 + q];
+        x[q] += __shfl_xor_sync(full, y, 16);
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        z[r] = b8 ? x[2 + r] : x[r];
+        const T w = b8 ? x[r] : x[2 + r];
+        z[r] += __shfl_xor_sync(full, w, 8);
+    }
+    T a = b4 ? z[1] : z[0];
+    const T b = b4 ? z[0] : z[1];
+    a += __shfl_xor_sync(full, b, 4);
+    a += __shfl_xor_sync(full, a, 2); a += __shfl_xor_sync(full, a, 1);
+    // lanes 0, 4, ..., 28 hold the warp totals of fields 6 .. 13
+    // return (1) and return^2 (2)
+    T r1 = b16 ? v[2] : v[1];
+    const T r2 = b16 ? v[1] : v[2];
+    r1 += __shfl_xor_sync(full, r2, 16);
+#pragma unroll
+    for (int off = 8; off > 0; off >>= 1) r1 += __shfl_xor_sync(full, r1, off);
+    // lane 0: field 1, lane 16: field 2
+    if ((lane & 3) == 0) part[warp][6 + (lane >> 2)] = a;
+    if ((lane & 15) == 0) part[warp][1 + (lane >> 4)] = r1;
+    if (lane == 0) {
+        part[warp][0] = (T)c0; part[warp][3] = (T)c3; part[warp][4] = (T)c4; part[warp][5] = (T)c5; part[warp][14] = (T)c14;
+        part[warp][15] = (T)c15;
+    }
+    __syncthreads();
+    if (threadIdx.x < ACB200_STATS_FIELDS) {
+        double t = 0.0;
+#pragma unroll
+        for (int wv = 0; wv < BLOCK / 32; ++wv) t += (double)part[wv][threadIdx.x];
+        if (t != 0.0) atomicAdd(&global[threadIdx.x], t);
+    }
+}
+
 // ---- K-C: controller + RateControlEnv.step + reward + termination + in-kernel auto-reset -----------
 // Loads are staged so that only what the substep loop needs is live across it: (A) state + PID memory
 // -> controller -> PID memory stored back; (B) K RK4 substeps on 12 states + held controls; (C) the
@@ -429,12 +484,10 @@ __device__ __forceinline__ void env_step_body(const DynParams<T>& P, const CtrlP
                                               const float* __restrict__ action, int64_t first, int64_t count) {
     // aircraft [first, first + count) of the fleet; n stays the field stride of the SoA buffers
     __shared__ __align__(16) float stage[kBlock * ACB200_OBS_DIM];
-    __shared__ double block_stats[ACB200_STATS_FIELDS];
     const int64_t n = B.f.n;
     const int64_t block_first = first + (int64_t)blockIdx.x * kBlock;
     const int64_t i = block_first + threadIdx.x;
     const bool valid = i < first + count;
-    if (threadIdx.x < ACB200_STATS_FIELDS) block_stats[threadIdx.x] = 0.0;
 
     float o[18];
     T st[ACB200_STATS_FIELDS];
@@ -554,18 +607,7 @@ __device__ __forceinline__ void env_step_body(const DynParams<T>& P, const CtrlP
     }
     store_obs_block(B.obs, block_first, first + count, o, valid, stage);
 
-    if (B.stats) {
-        // warp tree, one shared-memory atomic per warp and field, one global atomic per block and field
-#pragma unroll
-        for (int k = 0; k < ACB200_STATS_FIELDS; ++k) {
-            T v = st[k];
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-            if ((threadIdx.x & 31) == 0) atomicAdd(&block_stats[k], (double)v);
-        }
-        __syncthreads();
-        if (threadIdx.x < ACB200_STATS_FIELDS) atomicAdd(&B.stats[threadIdx.x], block_stats[threadIdx.x]);
-    }
+    if (B.stats) block_accumulate_env_stats<T, kBlock>(st, B.stats);      // uniform branch: whole block or nobody
 }
 
 // Default: ONE parameter set per launch, in the constant bank (__grid_constant__).

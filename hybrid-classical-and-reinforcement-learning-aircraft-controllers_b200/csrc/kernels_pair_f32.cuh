@@ -43,14 +43,11 @@ __device__ __forceinline__ void env_step_pair_body(const DynParams<float>& P, co
                                                    int64_t pairs) {
     // aircraft [first, first + 2 pairs) of the fleet; first and the field stride n are even (checked by the launcher)
     __shared__ __align__(16) float stage[2 * BLOCK * ACB200_OBS_DIM];
-    __shared__ double block_stats[ACB200_STATS_FIELDS];
     const int64_t n = B.f.n;
     const int64_t pair_idx = (int64_t)blockIdx.x * BLOCK + threadIdx.x;
     const int64_t block_first = first + (int64_t)blockIdx.x * (2 * BLOCK);
     const int64_t i = first + 2 * pair_idx;
     const bool valid = pair_idx < pairs;
-    if (threadIdx.x < ACB200_STATS_FIELDS) block_stats[threadIdx.x] = 0.0;
-
     float st[ACB200_STATS_FIELDS];
 #pragma unroll
     for (int k = 0; k < ACB200_STATS_FIELDS; ++k) st[k] = 0.0f;
@@ -220,17 +217,7 @@ __device__ __forceinline__ void env_step_pair_body(const DynParams<float>& P, co
         }
     }
 
-    if (B.stats) {
-#pragma unroll
-        for (int k = 0; k < ACB200_STATS_FIELDS; ++k) {
-            float v = st[k];
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-            if ((threadIdx.x & 31) == 0) atomicAdd(&block_stats[k], (double)v);
-        }
-        __syncthreads();
-        if (threadIdx.x < ACB200_STATS_FIELDS) atomicAdd(&B.stats[threadIdx.x], block_stats[threadIdx.x]);
-    }
+    if (B.stats) block_accumulate_env_stats<float, BLOCK>(st, B.stats);
 }
 
 template <int BLOCK, int MIN_BLOCKS>
