@@ -14,6 +14,8 @@ The tolerances stated here (and repeated in DESIGN.md) were measured on a B200 a
             one-float-ulp sensitivity at 10, 25 and 50 env steps (measured: <= 2.8x)
   FLAGS     terminated/truncated identical wherever the trajectories still agree to 1e-4 and the
             oracle is not within 1e-3 (relative) of a termination threshold
+  REWARD    every reward component and the reward after ONE env step from the oracle's state (re-synchronised every step):
+            <= 2e-5 x max(1, |value|); settle flag, done flags and the crash penalty identical away from decision thresholds
   STATS     full-episode statistics (mean return, mean length, crash rate) of 16k aircraft agree with
             the fp64 build within sampling-level differences (stated below)
 The fp32 PID core itself is bit-exact (same float ops, tests/test_cabi_host.py + the f64 tests).
@@ -169,3 +171,77 @@ def test_kernel_resources():
     for name in ("step_surface", "step_cascade_rate", "step_cascade_attitude", "env_step"):
         info = acb200.kernel_info(32, name)
         assert info["regs"] <= 128, (name, info)
+
+
+REWARD_COMPONENT_TOL = 2e-5   # x max(1, |value|): each of the 8 reward components after ONE env step from the oracle's state
+REWARD_TOL = 2e-5             # x max(1, |value|): the reward.  Measured (r02, 4 controller modes x 245 k aircraft-steps): 4.2e-6 on
+                              # the tracking term, <= 2e-7 on stability / oscillation, 3e-9 on smoothness, exactly 0 on survival,
+                              # settle bonus, crash penalty and residual bonus; reward 3.5e-6
+
+
+@pytest.mark.parametrize("controller", ["rate_pid", "attitude_pid", "external", "residual"])
+def test_reward_components_per_step_from_resynchronised_states(mods, controller):
+    """the closed-loop reward bar alone could hide a mis-ordered reward term on a few aircraft.  Here the fp32 env
+    starts EVERY step from the fp64 oracle's own state -- physics state, PID memory, reward memory, command, previous action,
+    counters narrowed to the fp32 buffers -- takes one env step, and every reward component (tracking, smoothness, stability,
+    oscillation, survival, settle bonus, crash penalty, residual bonus), the reward, the settle flag and the done flags are
+    compared for every aircraft that is not within rounding distance of a discrete decision."""
+    torch, acb200, orc = mods
+    n, steps = 4096, 60
+    rng = np.random.default_rng(21)
+    ct = (np.arange(n) % 4).astype(np.uint8)
+    diff = np.array([0.3, 0.5, 0.7], np.float32)[rng.integers(0, 3, n)]
+    env = acb200.BatchedRateControlEnv(n, controller=controller, precision=32, seed=9, track_components=True, auto_reset=False)
+    ref = orc.Env(n, controller=acb200.envs.CONTROLLERS[controller], seed=9, difficulty=diff, command_type=ct, auto_reset=False)
+    env.set_curriculum(torch.as_tensor(diff), torch.as_tensor(ct))
+    att = np.zeros((4, n)); att[0] = rng.uniform(-0.35, 0.35, n); att[1] = rng.uniform(-0.03, 0.08, n)
+    att[2] = np.inf; att[3] = rng.uniform(0.5, 0.8, n)
+    env.att_cmd.copy_(_t(torch, att, torch.float32)); ref.att_cmd[:] = att
+    env.reset(); ref.reset()
+    f32 = lambda a: _t(torch, a, torch.float32)
+    worst = np.zeros(8); worst_r = 0.0; compared = 0
+    for t in range(steps):
+        # ---- re-synchronise: the fp32 env takes the oracle's state as it is
+        env.state.copy_(f32(ref.state)); env.derived.copy_(f32(ref.derived)); env.pid.copy_(_t(torch, ref.pid))
+        env.rate_cmd.copy_(f32(ref.rate_cmd)); env.prev_action.copy_(_t(torch, ref.prev_action)); env.rew_mem.copy_(f32(ref.rew_mem))
+        env.sched.copy_(f32(ref.sched)); env.env_time.copy_(f32(ref.env_time)); env.step_count.copy_(_t(torch, ref.step_count))
+        env.is_settled.copy_(_t(torch, ref.is_settled)); env.episode_idx.copy_(_t(torch, ref.episode_idx.astype(np.int32)))
+        # the fp32 build counts settled STEPS where the oracle accumulates dt (DESIGN.md: fp64 timer rule): translate the timer
+        env.rew_mem[6] = f32(np.round(ref.rew_mem[6] / 0.02))
+        a = None
+        if controller in ("external", "residual"):
+            a = (rng.uniform(-1, 1, (n, 4)) * (0.05 if controller == "external" else 1.0)).astype(np.float32)
+            if controller == "external":
+                a[:, 3] = 0.6
+        alive = np.ones(n, bool)          # finished aircraft were reset in the oracle at the end of the previous step
+        pre_err = ref.rate_cmd - ref.state[9:12]
+        env.step(None if a is None else _t(torch, a)); ref.step(a)
+        comp, rcomp = env.components.cpu().numpy().astype(np.float64), ref.components
+        err = ref.rate_cmd - ref.state[9:12]
+        # discrete decisions that a 1e-6 state difference may flip legitimately: a sign change of an error close to zero
+        # (oscillation term), the settle band edge, a termination threshold
+        band = np.maximum(np.abs(ref.rate_cmd) * 0.05, 0.05)
+        near = (np.abs(err) < 1e-4).any(axis=0) | (np.abs(np.abs(err) - band) < 1e-4).any(axis=0) | (np.abs(np.abs(pre_err) - 0.01) < 1e-4).any(axis=0)
+        d = ref.derived
+        near |= (np.abs(d[1] - 5.0) < 1e-3) | (np.abs(d[0] - 8.0) < 1e-3) | (np.abs(np.abs(ref.state[6]) - np.radians(120)) < 1e-4) \
+            | (np.abs(np.abs(ref.state[7]) - np.radians(80)) < 1e-4)
+        ok = alive & ~near
+        # aircraft that left the envelope inside this step (a crash mid-step) integrate ill-conditioned states: excluded like
+        # in the per-step physics test, but their crash penalty and flags are still compared below
+        flying = ok & in_envelope(ref.state, ref.derived)
+        e8 = np.abs(comp - rcomp) / np.maximum(np.abs(rcomp), 1.0)
+        worst = np.maximum(worst, e8[:, flying].max(axis=1))
+        assert (e8[:, flying] <= REWARD_COMPONENT_TOL).all(), (t, np.argwhere(e8[:, flying] > REWARD_COMPONENT_TOL)[:5], e8[:, flying].max(axis=1))
+        dr = np.abs(env.reward.cpu().numpy().astype(np.float64) - ref.reward) / np.maximum(np.abs(ref.reward), 1.0)
+        worst_r = max(worst_r, float(dr[flying].max()))
+        assert (dr[flying] <= REWARD_TOL).all(), (t, dr[flying].max())
+        assert np.array_equal(env.terminated.cpu().numpy()[ok], ref.terminated[ok]) and np.array_equal(env.truncated.cpu().numpy()[ok], ref.truncated[ok])
+        assert np.array_equal(env.is_settled.cpu().numpy()[ok], ref.is_settled[ok])
+        assert np.array_equal(comp[6][ok], rcomp[6][ok])                    # crash penalty: exactly -100 or 0
+        compared += int(flying.sum())
+        # finished aircraft start a new episode in both (same Philox stream): reset them in the oracle and carry on
+        done = (ref.terminated | ref.truncated).astype(bool)
+        if done.any():
+            ref.reset(done.astype(np.uint8))
+    assert compared > 0.9 * n * steps
+    print(f"{controller}: worst |component error| {np.array2string(worst, precision=2)}  worst |reward error| {worst_r:.2e}  ({compared} aircraft-steps)")
