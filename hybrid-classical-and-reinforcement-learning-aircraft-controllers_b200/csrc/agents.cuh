@@ -74,8 +74,8 @@ __device__ __forceinline__ void hsa_agent(const CtrlParams<T>& C, PidMem (&outer
     // :167-186 TECS specific energies
     const T g = T(9.81), h = d[1], V = d[0];
     const T half_v2 = T(0.5) * M::sq(V), half_vc2 = T(0.5) * M::sq(speed_cmd);
-    const T e_specific = g * h + half_v2, e_specific_cmd = g * altitude_cmd + half_vc2;
-    const T e_balance = g * h - half_v2, e_balance_cmd = g * altitude_cmd - half_vc2;
+    const T e_specific = M::mad(g, h, half_v2), e_specific_cmd = M::mad(g, altitude_cmd, half_vc2);
+    const T e_balance = M::mad(g, h, -half_v2), e_balance_cmd = M::mad(g, altitude_cmd, -half_vc2);
     // :192-197 total energy -> throttle
     const T throttle_adjustment = (T)pid_compute(C.energy, outer[1], (float)e_specific_cmd, (float)e_specific, dt);
     const T throttle = np_clip(C.baseline_throttle + throttle_adjustment, T(0), T(1));
@@ -84,7 +84,7 @@ __device__ __forceinline__ void hsa_agent(const CtrlParams<T>& C, PidMem (&outer
     const T cos_roll = M::cos(roll_angle);
     if (M::abs(cos_roll) > T(0.01)) {
         const T load_factor = M::div(T(1), cos_roll);
-        pitch_angle = pitch_angle + C.load_factor_gain * (load_factor - T(1));
+        pitch_angle = M::mad(C.load_factor_gain, load_factor - T(1), pitch_angle);
     }
     pitch_angle = np_clip(pitch_angle, -C.max_pitch_cmd, C.max_pitch_cmd);
     // :216-229 yaw command = current yaw
@@ -110,7 +110,7 @@ __device__ __forceinline__ void waypoint_guidance(const CtrlParams<T>& C, int gu
         const T anticipation_dist = M::div(turn_radius * M::abs(heading_error), C.rad90);
         if (horizontal_distance < anticipation_dist && M::abs(heading_error) > C.rad20) {
             const T blend = T(1) - M::div(horizontal_distance, anticipation_dist);
-            heading_cmd = heading_cmd + blend * C.los_lead_angle * np_sign(heading_error);
+            heading_cmd = M::mad(blend * C.los_lead_angle, np_sign(heading_error), heading_cmd);
             heading_cmd = M::atan2(M::sin(heading_cmd), M::cos(heading_cmd));
         }
     } else {                                                             // pure pursuit :148-182
@@ -118,7 +118,7 @@ __device__ __forceinline__ void waypoint_guidance(const CtrlParams<T>& C, int gu
         T lookahead_dist = C.lookahead_time * V;
         const T proximity_dist = C.proximity_scale_distance * turn_radius;
         if (horizontal_distance < proximity_dist) {
-            const T scale = T(0.6) + T(0.4) * M::div(horizontal_distance, proximity_dist);
+            const T scale = M::mad(T(0.4), M::div(horizontal_distance, proximity_dist), T(0.6));
             lookahead_dist = lookahead_dist * scale;
         }
         lookahead_dist = np_clip(lookahead_dist, C.lookahead_min, C.lookahead_max);

@@ -196,8 +196,8 @@ __device__ __forceinline__ void mission_stats_one(const MissionPtrs<T>& M, int32
     if (prev >= 0) {
         const T ax = M.waypoints[prev * 4 + 0], ay = M.waypoints[prev * 4 + 1];
         const T bx = wp[0] - ax, by = wp[1] - ay, px = s[0] - ax, py = s[1] - ay;
-        const T len2 = bx * bx + by * by;
-        if (len2 > T(1e-12)) ct = Mt::kParity ? Mt::abs(Mt::div(px * by - py * bx, Mt::sqrt(len2))) : Mt::abs(px * by - py * bx) * (T)rsqrtf((float)len2);
+        const T len2 = Mt::mad(bx, bx, by * by), cross = Mt::mad(px, by, -(py * bx));
+        if (len2 > T(1e-12)) ct = Mt::kParity ? Mt::abs(Mt::div(cross, Mt::sqrt(len2))) : Mt::abs(cross) * (T)rsqrtf((float)len2);
     }
     ms[4] += ct; ms[5] += ct * ct;
     ms[6] += Mt::abs(d[1] - (-wp[2]));               // |altitude - waypoint altitude|
@@ -247,20 +247,31 @@ __device__ __forceinline__ void block_accumulate_mission(const T (&v)[kMissionSt
     }
 }
 
-// One aircraft's whole guided step (the body of step_guided_kernel; also the cold path of the pair kernel).
+// One aircraft's guided step in two halves (step_guided_kernel runs the block's statistics reduction between them, so that the
+// ten statistics words are dead before the register-hungry half starts; guided_step_one below is the two back to back).
+//
+// guided_front: state and derived outputs in, MissionPlanner.update + mission statistics + WaypointAgent guidance (level 1) or
+// the caller's HSA command (level 2).  Returns false when the aircraft takes no step (mission complete).
+// The derived outputs the agents read (airspeed, altitude, heading: what get_state() hands them) are LOADED from f.derived
+// when the fleet has that buffer: every entry point that writes the state refreshes it (acb200.h), so it holds
+// derived_outputs(state) bit for bit and the 140 instructions of recomputing it are saved; with derived == NULL they are
+// recomputed here.
 template <typename T, int LEVEL>
-__device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
-                                                float* __restrict__ pid_outer, const T* __restrict__ cmd, const MissionPtrs<T>& M,
-                                                float dt_ctrl, int K, T h, T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out,
-                                                int64_t i, T (&ms)[kMissionStats]) {
-    T s[12], time, hc[3], surf[4], c[4], d[4];
+__device__ __forceinline__ bool guided_front(const CtrlParams<T>& C, const FleetPtrs<T>& f, const T* __restrict__ cmd,
+                                             const MissionPtrs<T>& M, T* __restrict__ hsa_cmd_out, int64_t i, T (&s)[12], T& time,
+                                             T (&d)[4], T (&hc)[3], T (&ms)[kMissionStats]) {
 #pragma unroll
     for (int k = 0; k < 12; ++k) s[k] = ldf(f.state, k, f.n, i);
     time = ldf(f.state, 12, f.n, i);
-    derived_outputs(s, d);
+    if (f.derived) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) d[k] = ldf(f.derived, k, f.n, i);
+    } else {
+        derived_outputs(s, d);
+    }
     if (LEVEL == ACB200_LEVEL_WAYPOINT) {
         int32_t idx = M.wp_index[i];
-        if (idx >= M.n_waypoints) return;                 // mission complete: examples/03_waypoint_square_demo.py:196-203 stops stepping
+        if (idx >= M.n_waypoints) return false;           // mission complete: examples/03_waypoint_square_demo.py:196-203 stops stepping
         T wp[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
@@ -271,7 +282,7 @@ __device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const Ctr
             advanced = true;
             if (idx >= M.n_waypoints && M.loop) { idx = 0; lapped = true; }
             M.wp_index[i] = idx;
-            if (idx >= M.n_waypoints) { ms[1] += T(1); ms[3] += T(1); return; }      // reached the last waypoint: mission complete
+            if (idx >= M.n_waypoints) { ms[1] += T(1); ms[3] += T(1); return false; }   // reached the last waypoint: mission complete
 #pragma unroll
             for (int k = 0; k < 4; ++k) wp[k] = M.waypoints[idx * 4 + k];
         }
@@ -285,11 +296,20 @@ __device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const Ctr
 #pragma unroll
         for (int k = 0; k < 3; ++k) hc[k] = ldf(cmd, k, f.n, i);
     }
+    return true;
+}
+
+// guided_back: HSAAgent (levels 2-4: nine PIDs) on the command, set_controls, K substeps, state / controls / derived out.
+template <typename T>
+__device__ __forceinline__ void guided_back(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
+                                            float* __restrict__ pid_outer, float dt_ctrl, int K, T h, T* __restrict__ surfaces_out,
+                                            int64_t i, T (&s)[12], T time, const T (&d_in)[4], const T (&hc)[3]) {
+    T surf[4], c[4], d[4];
     PidMem rate[3], ang[3], outer[3];
     load_pid(f.pid, f.n, i, 0, rate);
     load_pid(f.pid, f.n, i, 1, ang);
     load_outer(pid_outer, f.n, i, outer);
-    hsa_agent(C, outer, ang, rate, hc[0], hc[1], hc[2], s, d, dt_ctrl, surf);
+    hsa_agent(C, outer, ang, rate, hc[0], hc[1], hc[2], s, d_in, dt_ctrl, surf);
     store_pid(f.pid, f.n, i, 0, rate);
     store_pid(f.pid, f.n, i, 1, ang);
     store_outer(pid_outer, f.n, i, outer);
@@ -313,6 +333,17 @@ __device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const Ctr
     }
 }
 
+// One aircraft's whole guided step (the cold path of the pair kernel).
+template <typename T, int LEVEL>
+__device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
+                                                float* __restrict__ pid_outer, const T* __restrict__ cmd, const MissionPtrs<T>& M,
+                                                float dt_ctrl, int K, T h, T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out,
+                                                int64_t i, T (&ms)[kMissionStats]) {
+    T s[12], time, d[4], hc[3];
+    if (guided_front<T, LEVEL>(C, f, cmd, M, hsa_cmd_out, i, s, time, d, hc, ms))
+        guided_back<T>(P, C, f, pid_outer, dt_ctrl, K, h, surfaces_out, i, s, time, d, hc);
+}
+
 template <typename T, int LEVEL>
 __global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kernel(const __grid_constant__ DynParams<T> P,
                                                              const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
@@ -320,11 +351,16 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kern
                                                              MissionPtrs<T> M, float dt_ctrl, int K, T h,
                                                              T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out) {
     const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
-    T ms[kMissionStats];
+    T s[12], time = T(0), d[4], hc[3];
+    bool active = false;
+    {
+        T ms[kMissionStats];
 #pragma unroll
-    for (int k = 0; k < kMissionStats; ++k) ms[k] = T(0);
-    if (i < f.n) guided_step_one<T, LEVEL>(P, C, f, pid_outer, cmd, M, dt_ctrl, K, h, surfaces_out, hsa_cmd_out, i, ms);
-    if (LEVEL == ACB200_LEVEL_WAYPOINT && M.stats) block_accumulate_mission(ms, M.stats);      // uniform branch: whole block or nobody
+        for (int k = 0; k < kMissionStats; ++k) ms[k] = T(0);
+        if (i < f.n) active = guided_front<T, LEVEL>(C, f, cmd, M, hsa_cmd_out, i, s, time, d, hc, ms);
+        if (LEVEL == ACB200_LEVEL_WAYPOINT && M.stats) block_accumulate_mission(ms, M.stats);   // uniform branch: whole block or nobody
+    }
+    if (active) guided_back<T>(P, C, f, pid_outer, dt_ctrl, K, h, surfaces_out, i, s, time, d, hc);
 }
 
 // ---- env memory <-> registers ----------------------------------------------------------------------

@@ -391,13 +391,25 @@ __device__ __forceinline__ void step_guided_pair_body(const DynParams<float>& P,
 #pragma unroll
         for (int k = 0; k < 3; ++k) hc2[k] = ld2(cmd, k, n, i);
     }
+    // the derived outputs the agents read are loaded when the fleet keeps them (guided_front, kernels.cuh): the same words
+    // the one-aircraft kernel reads, so the two kernels cannot drift apart over how an inlined copy of derived_outputs rounds
+    v2 dv[4];
+    if (f.derived) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) dv[k] = ld2(f.derived, k, n, i);
+    }
 #pragma unroll 1
     for (int l = 0; l < 2; ++l) {
         const int64_t il = i + l;
         float sl[12], d[4], hc[3], surf[4], c[4];
 #pragma unroll
         for (int k = 0; k < 12; ++k) sl[k] = lane(s2[k], l);
-        derived_outputs(sl, d);
+        if (f.derived) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) d[k] = lane(dv[k], l);
+        } else {
+            derived_outputs(sl, d);
+        }
         if (LEVEL == ACB200_LEVEL_WAYPOINT) {
             int32_t idx = l ? idx2.y : idx2.x;
             float wp[4];

@@ -19,6 +19,8 @@ template <> struct Math<double> {
     using real = double;
     static constexpr bool kParity = true;
     static __device__ __forceinline__ double sq(double x) { return x * x; }  // numpy scalar x**2 (pow(x,2.0), 1 ulp)
+    // a * b + c as the reference evaluates it: two roundings (this build is compiled with -fmad=false)
+    static __device__ __forceinline__ double mad(double a, double b, double c) { return a * b + c; }
     static __device__ __forceinline__ double norm3(double u, double v, double w) {
         return ::sqrt(__fma_rn(w, w, __fma_rn(v, v, u * u)));                // np.linalg.norm -> ddot, fused tail
     }
@@ -123,6 +125,9 @@ template <> struct Math<float> {
     using real = float;
     static constexpr bool kParity = false;
     static __device__ __forceinline__ float sq(float x) { return x * x; }
+    // a * b + c, ALWAYS fused: the throughput build leaves no multiply-add to the compiler's contraction heuristics, so that
+    // two kernels (one aircraft per thread / a pair per thread) that inline the same function round it the same way
+    static __device__ __forceinline__ float mad(float a, float b, float c) { return fmaf(a, b, c); }
     static __device__ __forceinline__ float norm3(float u, float v, float w) { return sqrtf(fmaf(w, w, fmaf(v, v, u * u))); }
     static __device__ __forceinline__ float norm2(float a, float b) { return sqrtf(fmaf(b, b, a * a)); }
     static __device__ __forceinline__ float row_dot3(float r0, float r1, float r2, float x0, float x1, float x2) {

@@ -179,8 +179,8 @@ template <typename T> __device__ __forceinline__ void derived_outputs(const T (&
     M::sincos(s[6], &sphi, &cphi);
     M::sincos(s[7], &sth, &cth);
     M::sincos(s[8], &sps, &cps);
-    const T r00 = cth * cps, r01 = sphi * sth * cps - cphi * sps, r02 = cphi * sth * cps + sphi * sps;
-    const T r10 = cth * sps, r11 = sphi * sth * sps + cphi * cps, r12 = cphi * sth * sps - sphi * cps;
+    const T r00 = cth * cps, r01 = M::mad(sphi * sth, cps, -(cphi * sps)), r02 = M::mad(cphi * sth, cps, sphi * sps);
+    const T r10 = cth * sps, r11 = M::mad(sphi * sth, sps, cphi * cps), r12 = M::mad(cphi * sth, sps, -(sphi * cps));
     const T vn = M::row_dot3(r00, r01, r02, u, v, w);
     const T ve = M::row_dot3(r10, r11, r12, u, v, w);
     d[0] = M::norm3(u, v, w);

@@ -395,10 +395,11 @@ __device__ __forceinline__ int backend_step(const DynParams<float>& P, float (&s
         if (substep_angles_in_sfu_range(P, s, h)) {
             repaired += rk4_step_f32_impl<false>(P, H, s, time, h);
         } else {
-            float tmp[12], tt = time;          // only this copy lives in local memory, not the loop-carried state
+            float tmp[12], tt = time;          // only these copies live in local memory, not the loop-carried state / the held terms
+            const HeldControlsF32 Hc = H;
 #pragma unroll
             for (int i = 0; i < 12; ++i) tmp[i] = s[i];
-            repaired += rk4_step_f32_guarded(P, H, tmp, &tt, h);
+            repaired += rk4_step_f32_guarded(P, Hc, tmp, &tt, h);
 #pragma unroll
             for (int i = 0; i < 12; ++i) s[i] = tmp[i];
             time = tt;

@@ -198,10 +198,11 @@ __device__ __forceinline__ int rk4_step_f32x2(const DynParams<float>& P, const H
         const float gain = dt * P.euler_rate_gain, dacc = dt * P.max_angular_acceleration;
         const float b0 = fmaf(gain, rate0 + dacc, ang0), b1 = fmaf(gain, rate1 + dacc, ang1);
         if (!(fmaxf(b0, b1) <= 11.5f)) {
-            v2 tmp[12];                       // only this copy lives in local memory, not the loop-carried state
+            v2 tmp[12];                       // only these copies live in local memory, not the loop-carried state / the held terms
+            const HeldControlsF32x2 Hc = H;
 #pragma unroll
             for (int i = 0; i < 12; ++i) tmp[i] = s[i];
-            const int repaired = rk4_step_lanes_f32(P, H, tmp, dt);
+            const int repaired = rk4_step_lanes_f32(P, Hc, tmp, dt);
 #pragma unroll
             for (int i = 0; i < 12; ++i) s[i] = tmp[i];
             return repaired;

@@ -124,7 +124,9 @@ class AircraftFleet:
         return self._cascade(_cabi.LEVEL_ATTITUDE, cmd, dt, dt_ctrl, surfaces_out)
 
     def step_hsa(self, cmd: torch.Tensor, dt: float, dt_ctrl: Optional[float] = None, surfaces_out=None):
-        """HSAAgent.compute_action (hsa_agent.py:119-231) + set_controls + step(dt); cmd [3][n] = heading, speed, altitude."""
+        """HSAAgent.compute_action (hsa_agent.py:119-231) + set_controls + step(dt); cmd [3][n] = heading, speed, altitude.
+        The agent's airspeed / altitude / heading are read from ``self.derived`` (kept current by every step and by
+        ``reset``): after writing ``self.state`` by hand, call ``reset(init_state=...)`` rather than stepping on."""
         self._bind_stream()
         cmd = as_tensor(cmd, self.device, self.dtype)
         assert cmd.shape == (3, self.n)

@@ -138,7 +138,11 @@ typedef struct {
     int32_t _pad;
     void* state;           /* real[13][n] */
     void* controls;        /* real[4][n]  controls held by the simulator (clipped)   simplified_6dof.py:221-226; nullable */
-    void* derived;         /* real[4][n]  refreshed at the end of every step call; nullable */
+    void* derived;         /* real[4][n]  airspeed, altitude, ground_speed, heading = what get_state() derives from the state
+                            * (simplified_6dof.py:295-331).  Every entry point that writes the state refreshes it; the HSA and
+                            * waypoint steps READ it as the agents' measurements instead of deriving it again, so a caller that
+                            * writes `state` itself must go through acb200_fleet_reset(mask, init_state) -- or pass NULL here,
+                            * then they derive it from the state on every step.  nullable */
     float* pid;            /* float[18][n] PID memory of the rate and angle loops; required for levels 3,4 */
 } acb200_fleet;
 

@@ -14,9 +14,9 @@ UNIT = "env-steps/s"
 DT = 0.01
 SQUARE = [[300.0, 0.0, -100.0, 15.0], [300.0, 300.0, -100.0, 15.0], [0.0, 300.0, -100.0, 15.0], [0.0, 0.0, -100.0, 15.0]]
 # (+ 10 warp-reduced mission statistics per block: 80 B per 128 aircraft, not counted)
-# step_guided_kernel<T,1>: loads state 13 + pid 18 + pid_outer 9 + wp_index 1, stores state 13 + controls 4 + derived 4 +
-# pid 18 + pid_outer 9 + wp_index 1 (4-byte words, fp32 build)
-BYTES_PER_STEP = (13 + 18 + 9 + 1 + 13 + 4 + 4 + 18 + 9 + 1) * 4
+# step_guided_kernel<T,1>: loads state 13 + derived 4 + pid 18 + pid_outer 9 + wp_index 1, stores state 13 + controls 4 +
+# derived 4 + pid 18 + pid_outer 9 + wp_index 1 (4-byte words, fp32 build)
+BYTES_PER_STEP = (13 + 4 + 18 + 9 + 1 + 13 + 4 + 4 + 18 + 9 + 1) * 4
 
 
 def workload_name(n):
