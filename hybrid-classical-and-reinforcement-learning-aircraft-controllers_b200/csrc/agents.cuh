@@ -12,14 +12,30 @@ namespace acb {
 // wrap_angle: (a + pi) % (2 pi) - pi with Python's floored modulo (range [-pi, pi))
 template <typename T> __device__ __forceinline__ T wrap_angle(T a) {
     using M = Math<T>;
-    const T two_pi = T(2) * T(3.141592653589793);
-    T m = M::fmod(a + T(3.141592653589793), two_pi);
-    if (m != T(0)) {
-        if (m < T(0)) m += two_pi;
+    if constexpr (!M::kParity) {
+        // throughput build: a - 2 pi floor((a + pi) / (2 pi)) with a two-word 2 pi (as Math<float>::wrap_pi); an angle already
+        // in [-pi, pi) comes back bit for bit (k = 0), so "hold the current yaw" still gives an error of exactly zero
+        const float k = floorf((a + 3.14159274101257324f) * 0.159154943091895346f);
+        float r = fmaf(k, -6.28318548202514648f, a);
+        r = fmaf(k, 1.74845553146951715e-07f, r);
+        return r;
     } else {
-        m = T(0);
+        const T two_pi = T(2) * T(3.141592653589793);
+        T m = M::fmod(a + T(3.141592653589793), two_pi);
+        if (m != T(0)) {
+            if (m < T(0)) m += two_pi;
+        } else {
+            m = T(0);
+        }
+        return m - T(3.141592653589793);
     }
-    return m - T(3.141592653589793);
+}
+// The reference's arctan2(sin(a), cos(a)) idiom (waypoint_agent.py:132,147,185,189): the parity build evaluates it as
+// written, the throughput build as a - 2 pi round(a / 2 pi) (its arguments are sums of two wrapped angles).
+template <typename T> __device__ __forceinline__ T wrap_atan(T a) {
+    using M = Math<T>;
+    if constexpr (M::kParity) return M::atan2(M::sin(a), M::cos(a));
+    else return M::wrap_pi(a);
 }
 
 // RateAgent.compute_action.  surf = elevator, aileron, rudder, throttle (ControlSurfaces.to_array order)
@@ -81,9 +97,9 @@ __device__ __forceinline__ void hsa_agent(const CtrlParams<T>& C, PidMem (&outer
     const T throttle = np_clip(C.baseline_throttle + throttle_adjustment, T(0), T(1));
     // :203-213 energy balance -> pitch, load-factor compensation in the turn
     T pitch_angle = (T)pid_compute(C.balance, outer[2], (float)e_balance_cmd, (float)e_balance, dt);
-    const T cos_roll = M::cos(roll_angle);
+    const T cos_roll = M::cos_bounded(roll_angle);
     if (M::abs(cos_roll) > T(0.01)) {
-        const T load_factor = M::div(T(1), cos_roll);
+        const T load_factor = M::fdiv(T(1), cos_roll);
         pitch_angle = M::mad(C.load_factor_gain, load_factor - T(1), pitch_angle);
     }
     pitch_angle = np_clip(pitch_angle, -C.max_pitch_cmd, C.max_pitch_cmd);
@@ -104,40 +120,40 @@ __device__ __forceinline__ void waypoint_guidance(const CtrlParams<T>& C, int gu
     T heading_cmd;
     if (guidance == ACB200_GUIDANCE_LOS) {                               // :121-146
         heading_cmd = M::atan2(e1, e0);
-        const T turn_radius = M::div(M::sq(V), T(9.81) * M::tan(C.los_max_bank));
+        const T turn_radius = M::kParity ? M::div(M::sq(V), T(9.81) * M::tan(C.los_max_bank)) : M::sq(V) * C.los_inv_g_tan;
         T heading_error = heading_cmd - heading;
-        heading_error = M::atan2(M::sin(heading_error), M::cos(heading_error));
-        const T anticipation_dist = M::div(turn_radius * M::abs(heading_error), C.rad90);
+        heading_error = wrap_atan(heading_error);
+        const T anticipation_dist = M::fdiv(turn_radius * M::abs(heading_error), C.rad90);
         if (horizontal_distance < anticipation_dist && M::abs(heading_error) > C.rad20) {
-            const T blend = T(1) - M::div(horizontal_distance, anticipation_dist);
+            const T blend = T(1) - M::fdiv(horizontal_distance, anticipation_dist);
             heading_cmd = M::mad(blend * C.los_lead_angle, np_sign(heading_error), heading_cmd);
-            heading_cmd = M::atan2(M::sin(heading_cmd), M::cos(heading_cmd));
+            heading_cmd = wrap_atan(heading_cmd);
         }
     } else {                                                             // pure pursuit :148-182
-        const T turn_radius = M::div(M::sq(V), T(9.81) * M::tan(C.pp_max_bank));
+        const T turn_radius = M::kParity ? M::div(M::sq(V), T(9.81) * M::tan(C.pp_max_bank)) : M::sq(V) * C.pp_inv_g_tan;
         T lookahead_dist = C.lookahead_time * V;
         const T proximity_dist = C.proximity_scale_distance * turn_radius;
         if (horizontal_distance < proximity_dist) {
-            const T scale = M::mad(T(0.4), M::div(horizontal_distance, proximity_dist), T(0.6));
+            const T scale = M::mad(T(0.4), M::fdiv(horizontal_distance, proximity_dist), T(0.6));
             lookahead_dist = lookahead_dist * scale;
         }
         lookahead_dist = np_clip(lookahead_dist, C.lookahead_min, C.lookahead_max);
         if (horizontal_distance > T(1)) {
-            const T dir0 = M::div(e0, horizontal_distance), dir1 = M::div(e1, horizontal_distance);
+            const T dir0 = M::fdiv(e0, horizontal_distance), dir1 = M::fdiv(e1, horizontal_distance);
             const T effective = (horizontal_distance < lookahead_dist) ? horizontal_distance : lookahead_dist;
             heading_cmd = M::atan2(dir1 * effective, dir0 * effective);
         } else {
             heading_cmd = M::atan2(e1, e0);
         }
     }
-    heading_cmd = M::atan2(M::sin(heading_cmd), M::cos(heading_cmd));  // :189
+    heading_cmd = wrap_atan(heading_cmd);  // :189
     // :207-232 altitude and speed commands, slowing down into sharp turns
     T speed_cmd = (wp[3] != wp[3]) ? airspeed : wp[3];
     const T heading_to_wp = M::atan2(e1, e0);
     T heading_error = M::abs(heading_to_wp - heading);
-    heading_error = M::abs(M::atan2(M::sin(heading_error), M::cos(heading_error)));
+    heading_error = M::abs(wrap_atan(heading_error));
     if (horizontal_distance < C.turn_threshold_distance && heading_error > C.turn_threshold_angle) {
-        const T reduction = C.max_speed_reduction * (T(1) - M::div(horizontal_distance, C.turn_threshold_distance));
+        const T reduction = C.max_speed_reduction * (T(1) - M::fdiv(horizontal_distance, C.turn_threshold_distance));
         speed_cmd = speed_cmd * (T(1) - reduction);
         speed_cmd = py_max(speed_cmd, C.min_speed);
     }

@@ -38,6 +38,8 @@ template <> struct Math<double> {
     static __device__ __forceinline__ double sqrt(double x) { return ::sqrt(x); }
     static __device__ __forceinline__ double log(double x) { return ::log(x); }
     static __device__ __forceinline__ double div(double a, double b) { return a / b; }
+    static __device__ __forceinline__ double fdiv(double a, double b) { return a / b; }     // guidance-level quotients
+    static __device__ __forceinline__ double cos_bounded(double x) { return ::cos(x); }
     static __device__ __forceinline__ double abs(double x) { return ::fabs(x); }
     static __device__ __forceinline__ double fmod(double a, double b) { return ::fmod(a, b); }
     static __device__ __forceinline__ bool finite(double x) { return isfinite(x); }
@@ -143,6 +145,10 @@ template <> struct Math<float> {
     static __device__ __forceinline__ float sqrt(float x) { return ::sqrtf(x); }
     static __device__ __forceinline__ float log(float x) { return ::logf(x); }
     static __device__ __forceinline__ float div(float a, float b) { return a / b; }
+    // quotients of the guidance levels (turn radii, blend factors, unit vectors): MUFU.RCP x multiply, 2 ulp
+    static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+    // cosine of a clipped bank / heading-sized angle (|x| <= 2 pi): the SFU's cos.approx, abs err ~5e-7
+    static __device__ __forceinline__ float cos_bounded(float x) { return __cosf(x); }
     static __device__ __forceinline__ float abs(float x) { return ::fabsf(x); }
     static __device__ __forceinline__ float fmod(float a, float b) { return ::fmodf(a, b); }
     static __device__ __forceinline__ bool finite(float x) { return isfinite(x); }

@@ -56,6 +56,7 @@ template <typename T> struct CtrlParams {
     T pp_max_bank, los_max_bank, los_lead_angle, turn_threshold_angle, rad90, rad20;
     T lookahead_time, lookahead_min, lookahead_max, proximity_scale_distance;
     T turn_threshold_distance, max_speed_reduction, min_speed;
+    T pp_inv_g_tan, los_inv_g_tan;      // 1 / (9.81 tan(max bank)): the turn radius per V^2 (throughput build; the parity build divides)
 };
 
 static inline double host_radians(double deg) { return deg * (3.141592653589793 / 180.0); }  // np.radians
@@ -131,6 +132,8 @@ template <typename T> static inline CtrlParams<T> make_ctrl_params(const acb200_
     o.lookahead_time = (T)c.lookahead_time; o.lookahead_min = (T)c.lookahead_min; o.lookahead_max = (T)c.lookahead_max;
     o.proximity_scale_distance = (T)c.proximity_scale_distance; o.turn_threshold_distance = (T)c.turn_threshold_distance;
     o.max_speed_reduction = (T)c.max_speed_reduction; o.min_speed = (T)c.min_speed;
+    o.pp_inv_g_tan = (T)(1.0 / (9.81 * tan(host_radians(c.max_bank_angle_deg))));
+    o.los_inv_g_tan = (T)(1.0 / (9.81 * tan(host_radians(c.los_max_bank_deg))));
     return o;
 }
 

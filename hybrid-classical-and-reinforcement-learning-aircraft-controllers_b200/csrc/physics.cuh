@@ -172,6 +172,9 @@ __device__ __forceinline__ int rk4_step(const DynParams<T>& P, T (&s)[12], T& ti
 
 // Simplified6DOF.get_state + _body_to_ned, simplified_6dof.py:295-331,505-530:
 // d = airspeed, altitude, ground_speed, heading.
+// (Throughput build: the general Cody-Waite sincos stays here on purpose.  The SFU's sin/cos (abs err 5e-7) and the short-range
+// polynomial pairs (1.5e-7) were both tried for these three angles and cost the ground speed / heading of a steeply climbing
+// aircraft -- ground speed << airspeed amplifies them -- more than the 1e-5 / 2e-5 bars of tests/test_gpu_parity_f32.py.)
 template <typename T> __device__ __forceinline__ void derived_outputs(const T (&s)[12], T (&d)[4]) {
     using M = Math<T>;
     const T u = s[3], v = s[4], w = s[5];
