@@ -41,7 +41,7 @@ template <typename T> __device__ __forceinline__ T wrap_atan(T a) {
 // RateAgent.compute_action.  surf = elevator, aileron, rudder, throttle (ControlSurfaces.to_array order)
 template <typename T>
 __device__ __forceinline__ void rate_agent(const CtrlParams<T>& C, PidMem (&mem)[3], T p_cmd_in, T q_cmd_in, T r_cmd_in,
-                                           T throttle, T p, T q, T r, float dt, T (&surf)[4]) {
+                                           T throttle, T p, T q, T r, const PidDt& dt, T (&surf)[4]) {
     const T p_cmd = np_clip(p_cmd_in, -C.max_roll_rate, C.max_roll_rate);      // rate_agent.py:92-94
     const T q_cmd = np_clip(q_cmd_in, -C.max_pitch_rate, C.max_pitch_rate);
     const T r_cmd = np_clip(r_cmd_in, -C.max_yaw_rate, C.max_yaw_rate);
@@ -58,7 +58,7 @@ __device__ __forceinline__ void rate_agent(const CtrlParams<T>& C, PidMem (&mem)
 // current yaw, which is the command HSAAgent issues every step (hsa_agent.py:214-216).
 template <typename T>
 __device__ __forceinline__ void attitude_agent(const CtrlParams<T>& C, PidMem (&ang)[3], PidMem (&rate)[3], T roll_cmd_in,
-                                               T pitch_cmd_in, T yaw_cmd_in, T throttle, const T (&s)[12], float dt,
+                                               T pitch_cmd_in, T yaw_cmd_in, T throttle, const T (&s)[12], const PidDt& dt,
                                                T (&surf)[4]) {
     const T roll_cmd = np_clip(roll_cmd_in, -C.max_roll, C.max_roll);            // attitude_agent.py:116-117
     const T pitch_cmd = np_clip(pitch_cmd_in, -C.max_pitch, C.max_pitch);
@@ -79,7 +79,7 @@ __device__ __forceinline__ void attitude_agent(const CtrlParams<T>& C, PidMem (&
 // d = airspeed, altitude, ground_speed, heading of the current state (what get_state() hands the agent).
 template <typename T>
 __device__ __forceinline__ void hsa_agent(const CtrlParams<T>& C, PidMem (&outer)[3], PidMem (&ang)[3], PidMem (&rate)[3],
-                                          T heading_cmd, T speed_cmd, T altitude_cmd, const T (&s)[12], const T (&d)[4], float dt,
+                                          T heading_cmd, T speed_cmd, T altitude_cmd, const T (&s)[12], const T (&d)[4], const PidDt& dt,
                                           T (&surf)[4]) {
     using M = Math<T>;
     // :147-160 heading error wrapped, fed to the PID as a virtual setpoint

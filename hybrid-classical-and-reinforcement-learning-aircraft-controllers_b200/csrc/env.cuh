@@ -25,6 +25,7 @@ template <typename T> struct EnvRegs {
 template <typename T> struct EnvConst {
     T dt, h, pid_throttle;
     float dt_f32, residual_scale;
+    PidDt pid_dt;          // dt_f32 with the reciprocal the PIDs divide by (pid.cuh)
     int32_t K, max_steps, controller, auto_reset;
     int32_t settle_steps;   // throughput build: consecutive settled steps before the bonus starts
     uint64_t seed;
@@ -219,12 +220,12 @@ __device__ __forceinline__ void env_action(const CtrlParams<T>& C, const EnvCons
         for (int k = 0; k < 4; ++k) act[k] = act_in[k];
     } else if (E.controller == ACB200_CTRL_ATTITUDE_PID) {
         T surf[4];
-        attitude_agent(C, ang, rate, att_cmd[0], att_cmd[1], att_cmd[2], att_cmd[3], s, E.dt_f32, surf);
+        attitude_agent(C, ang, rate, att_cmd[0], att_cmd[1], att_cmd[2], att_cmd[3], s, E.pid_dt, surf);
         act[0] = (float)surf[1]; act[1] = (float)surf[0]; act[2] = (float)surf[2]; act[3] = (float)surf[3];
     } else {
         // pid_demonstrations.py:55-78 / residual_rate_env.py:112-135
         T surf[4];
-        rate_agent(C, rate, rate_cmd[0], rate_cmd[1], rate_cmd[2], E.pid_throttle, s[9], s[10], s[11], E.dt_f32, surf);
+        rate_agent(C, rate, rate_cmd[0], rate_cmd[1], rate_cmd[2], E.pid_throttle, s[9], s[10], s[11], E.pid_dt, surf);
         act[0] = (float)surf[1]; act[1] = (float)surf[0]; act[2] = (float)surf[2]; act[3] = (float)surf[3];
         if (E.controller == ACB200_CTRL_RESIDUAL) {
             // residual_rate_env.py:138-155, float32 arithmetic (individually rounded, as numpy does it)

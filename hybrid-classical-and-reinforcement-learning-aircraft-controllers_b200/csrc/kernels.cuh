@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kBlock, MinBlocks<T>::cascade) step_surface_ke
 template <typename T, int LEVEL>
 __global__ void __launch_bounds__(kBlock, MinBlocks<T>::cascade) step_cascade_kernel(const __grid_constant__ DynParams<T> P,
                                                               const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
-                                                              const T* __restrict__ cmd, float dt_ctrl, int K, T h,
+                                                              const T* __restrict__ cmd, PidDt dt_ctrl, int K, T h,
                                                               T* __restrict__ surfaces_out) {
     const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (i >= f.n) return;
@@ -302,7 +302,7 @@ __device__ __forceinline__ bool guided_front(const CtrlParams<T>& C, const Fleet
 // guided_back: HSAAgent (levels 2-4: nine PIDs) on the command, set_controls, K substeps, state / controls / derived out.
 template <typename T>
 __device__ __forceinline__ void guided_back(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
-                                            float* __restrict__ pid_outer, float dt_ctrl, int K, T h, T* __restrict__ surfaces_out,
+                                            float* __restrict__ pid_outer, PidDt dt_ctrl, int K, T h, T* __restrict__ surfaces_out,
                                             int64_t i, T (&s)[12], T time, const T (&d_in)[4], const T (&hc)[3]) {
     T surf[4], c[4], d[4];
     PidMem rate[3], ang[3], outer[3];
@@ -337,7 +337,7 @@ __device__ __forceinline__ void guided_back(const DynParams<T>& P, const CtrlPar
 template <typename T, int LEVEL>
 __device__ __forceinline__ void guided_step_one(const DynParams<T>& P, const CtrlParams<T>& C, const FleetPtrs<T>& f,
                                                 float* __restrict__ pid_outer, const T* __restrict__ cmd, const MissionPtrs<T>& M,
-                                                float dt_ctrl, int K, T h, T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out,
+                                                PidDt dt_ctrl, int K, T h, T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out,
                                                 int64_t i, T (&ms)[kMissionStats]) {
     T s[12], time, d[4], hc[3];
     if (guided_front<T, LEVEL>(C, f, cmd, M, hsa_cmd_out, i, s, time, d, hc, ms))
@@ -348,7 +348,7 @@ template <typename T, int LEVEL>
 __global__ void __launch_bounds__(kBlock, MinBlocks<T>::guided) step_guided_kernel(const __grid_constant__ DynParams<T> P,
                                                              const __grid_constant__ CtrlParams<T> C, FleetPtrs<T> f,
                                                              float* __restrict__ pid_outer, const T* __restrict__ cmd,
-                                                             MissionPtrs<T> M, float dt_ctrl, int K, T h,
+                                                             MissionPtrs<T> M, PidDt dt_ctrl, int K, T h,
                                                              T* __restrict__ surfaces_out, T* __restrict__ hsa_cmd_out) {
     const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     T s[12], time = T(0), d[4], hc[3];
@@ -702,6 +702,7 @@ template <typename T> static inline EnvConst<T> make_env_const(const acb200_env_
     EnvConst<T> E;
     E.dt = (T)cfg.dt; E.h = (T)h; E.pid_throttle = (T)cfg.pid_throttle;
     E.dt_f32 = (float)cfg.dt; E.residual_scale = (float)cfg.residual_scale;
+    E.pid_dt = make_pid_dt(E.dt_f32);
     E.K = K; E.max_steps = cfg.max_steps; E.controller = cfg.controller; E.auto_reset = cfg.auto_reset;
     E.settle_steps = settle_steps_for(cfg.dt);
     E.seed = cfg.seed; E.id_offset = cfg.id_offset;
@@ -723,7 +724,7 @@ cudaError_t Launch<T>::step_surface(const acb200_aircraft_params& ap, const Flee
     if constexpr (sizeof(T) == 4) {
         if (fleet_pair_ok(f, ctrl_in, nullptr, K)) {
             step_fleet_pair_kernel<0><<<grid_for(f.n / 2), kBlock, 0, st>>>(make_dyn_params<float>(ap), CtrlParams<float>{}, f, ctrl_in,
-                                                                           0.0f, K, (float)h, nullptr, f.n / 2);
+                                                                           make_pid_dt(0.0f), K, (float)h, nullptr, f.n / 2);
             return cudaGetLastError();
         }
     }
@@ -742,19 +743,19 @@ cudaError_t Launch<T>::step_cascade(const acb200_aircraft_params& ap, const acb2
     if constexpr (sizeof(T) == 4) {
         if (fleet_pair_ok(f, cmd, surfaces_out, K)) {
             if (level == ACB200_LEVEL_ATTITUDE)
-                step_fleet_pair_kernel<ACB200_LEVEL_ATTITUDE><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (float)h,
+                step_fleet_pair_kernel<ACB200_LEVEL_ATTITUDE><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, cmd, make_pid_dt((float)dt_ctrl), K, (float)h,
                                                                                                    surfaces_out, f.n / 2);
             else
-                step_fleet_pair_kernel<ACB200_LEVEL_RATE><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (float)h,
+                step_fleet_pair_kernel<ACB200_LEVEL_RATE><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, cmd, make_pid_dt((float)dt_ctrl), K, (float)h,
                                                                                                surfaces_out, f.n / 2);
             return cudaGetLastError();
         }
     }
 #endif
     if (level == ACB200_LEVEL_ATTITUDE)
-        step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (T)h, surfaces_out);
+        step_cascade_kernel<T, ACB200_LEVEL_ATTITUDE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, make_pid_dt((float)dt_ctrl), K, (T)h, surfaces_out);
     else
-        step_cascade_kernel<T, ACB200_LEVEL_RATE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, (float)dt_ctrl, K, (T)h, surfaces_out);
+        step_cascade_kernel<T, ACB200_LEVEL_RATE><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, cmd, make_pid_dt((float)dt_ctrl), K, (T)h, surfaces_out);
     return cudaGetLastError();
 }
 
@@ -773,20 +774,20 @@ cudaError_t Launch<T>::step_guided(const acb200_aircraft_params& ap, const acb20
         // from a few substeps on (HSA level, K = 10: 0.297 -> 0.250 ms per 2^20 aircraft) and loses at K = 1 (0.074 -> 0.088 ms)
         if (K >= 4 && fleet_pair_ok(f, cmd, surfaces_out, K, pid_outer, hsa_cmd_out, m ? m->wp_index : nullptr)) {
             if (m)
-                step_guided_pair_kernel<ACB200_LEVEL_WAYPOINT><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K,
+                step_guided_pair_kernel<ACB200_LEVEL_WAYPOINT><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, make_pid_dt((float)dt_ctrl), K,
                                                                                                     (float)h, surfaces_out, hsa_cmd_out, f.n / 2);
             else
-                step_guided_pair_kernel<ACB200_LEVEL_HSA><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K,
+                step_guided_pair_kernel<ACB200_LEVEL_HSA><<<grid_for(f.n / 2), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, make_pid_dt((float)dt_ctrl), K,
                                                                                                (float)h, surfaces_out, hsa_cmd_out, f.n / 2);
             return cudaGetLastError();
         }
     }
 #endif
     if (m) {
-        step_guided_kernel<T, ACB200_LEVEL_WAYPOINT><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K, (T)h,
+        step_guided_kernel<T, ACB200_LEVEL_WAYPOINT><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, make_pid_dt((float)dt_ctrl), K, (T)h,
                                                                                        surfaces_out, hsa_cmd_out);
     } else {
-        step_guided_kernel<T, ACB200_LEVEL_HSA><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, (float)dt_ctrl, K, (T)h,
+        step_guided_kernel<T, ACB200_LEVEL_HSA><<<grid_for(f.n), kBlock, 0, st>>>(P, C, f, pid_outer, cmd, M, make_pid_dt((float)dt_ctrl), K, (T)h,
                                                                                   surfaces_out, hsa_cmd_out);
     }
     return cudaGetLastError();

@@ -266,7 +266,7 @@ static inline const void* env_step_pair_entry() {
 template <int LEVEL>
 __global__ void __launch_bounds__(kBlock, 4)
 step_fleet_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C, FleetPtrs<float> f,
-                       const float* __restrict__ in, float dt_ctrl, int K, float h, float* __restrict__ surfaces_out, int64_t pairs) {
+                       const float* __restrict__ in, PidDt dt_ctrl, int K, float h, float* __restrict__ surfaces_out, int64_t pairs) {
     const int64_t n = f.n;
     const int64_t pair_idx = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     if (pair_idx >= pairs) return;
@@ -330,7 +330,7 @@ step_fleet_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_
 // leaves that aircraft untouched) takes the one-aircraft code for both lanes, out of line.
 template <int LEVEL>
 static __device__ __noinline__ void guided_step_one_cold(const DynParams<float>& P, const CtrlParams<float>& C, const FleetPtrs<float>& f,
-                                                         float* pid_outer, const float* cmd, const MissionPtrs<float>& M, float dt_ctrl,
+                                                         float* pid_outer, const float* cmd, const MissionPtrs<float>& M, PidDt dt_ctrl,
                                                          int K, float h, float* surfaces_out, float* hsa_cmd_out, int64_t i, float* ms_out) {
     float ms[kMissionStats];
 #pragma unroll
@@ -346,7 +346,7 @@ static __device__ __noinline__ void guided_step_one_cold(const DynParams<float>&
 template <int LEVEL>
 __device__ __forceinline__ void step_guided_pair_body(const DynParams<float>& P, const CtrlParams<float>& C, const FleetPtrs<float>& f,
                                                       float* __restrict__ pid_outer, const float* __restrict__ cmd,
-                                                      const MissionPtrs<float>& M, float dt_ctrl, int K, float h,
+                                                      const MissionPtrs<float>& M, PidDt dt_ctrl, int K, float h,
                                                       float* __restrict__ surfaces_out, float* __restrict__ hsa_cmd_out, int64_t pairs,
                                                       float (&ms)[kMissionStats]) {
     const int64_t n = f.n;
@@ -501,7 +501,7 @@ __device__ __forceinline__ void step_guided_pair_body(const DynParams<float>& P,
 template <int LEVEL>
 __global__ void __launch_bounds__(kBlock, ACB_GUIDED_PAIR_MIN_BLOCKS)
 step_guided_pair_kernel(const __grid_constant__ DynParams<float> P, const __grid_constant__ CtrlParams<float> C, FleetPtrs<float> f,
-                        float* __restrict__ pid_outer, const float* __restrict__ cmd, MissionPtrs<float> M, float dt_ctrl, int K,
+                        float* __restrict__ pid_outer, const float* __restrict__ cmd, MissionPtrs<float> M, PidDt dt_ctrl, int K,
                         float h, float* __restrict__ surfaces_out, float* __restrict__ hsa_cmd_out, int64_t pairs) {
     float ms[kMissionStats];
 #pragma unroll
