@@ -129,6 +129,11 @@ __device__ __forceinline__ void waypoint_guidance(const CtrlParams<T>& C, int gu
             heading_cmd = M::mad(blend * C.los_lead_angle, np_sign(heading_error), heading_cmd);
             heading_cmd = wrap_atan(heading_cmd);
         }
+    } else if (!M::kParity) {
+        // pure pursuit, throughput build: the look-ahead point lies on the line to the waypoint (:170-182 scale the unit vector
+        // by a positive distance), so its bearing IS the bearing of the waypoint; look-ahead, proximity scaling and turn radius
+        // cancel out of atan2 and are not evaluated (the parity build below runs them as written: 1e-7 rad of rounding)
+        heading_cmd = M::atan2(e1, e0);
     } else {                                                             // pure pursuit :148-182
         const T turn_radius = M::kParity ? M::div(M::sq(V), T(9.81) * M::tan(C.pp_max_bank)) : M::sq(V) * C.pp_inv_g_tan;
         T lookahead_dist = C.lookahead_time * V;
