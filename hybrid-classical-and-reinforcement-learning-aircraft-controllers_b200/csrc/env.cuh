@@ -266,7 +266,7 @@ __device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<
     const T airspeed = e.d[0], altitude = e.d[1], roll = e.s[6], pitch = e.s[7];
 
     // RateTrackingReward.compute, rewards.py:48-137
-    const T tracking_error = M::div(M::sq(err[0]) + M::sq(err[1]) + M::sq(err[2]), T(3));
+    const T tracking_error = M::div_by(M::sq(err[0]) + M::sq(err[1]) + M::sq(err[2]), T(3));
     const T r_tracking = T(-0.5) * tracking_error;
     T r_smoothness;
     if (e.step_count == 1 && M::kParity) {
@@ -283,16 +283,20 @@ __device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<
         r_smoothness = (T)__fmul_rn(-0.01f, cc);
     }
     const T RAD45 = T(45.0 * (3.141592653589793 / 180.0)), RAD30 = T(30.0 * (3.141592653589793 / 180.0));
-    const T roll_stability = M::exp(M::div(-M::abs(roll), RAD45));
-    const T pitch_stability = M::exp(M::div(-M::abs(pitch), RAD30));
-    const T airspeed_stability = np_clip(M::div(airspeed - T(8), T(12)), T(0), T(1));
-    const T altitude_stability = np_clip(M::div(altitude - T(10), T(90)), T(0), T(1));
-    const T stability_score = M::div(roll_stability + pitch_stability + airspeed_stability + altitude_stability, T(4));
+    const T roll_stability = M::exp_neg(M::div_by(-M::abs(roll), RAD45));
+    const T pitch_stability = M::exp_neg(M::div_by(-M::abs(pitch), RAD30));
+    const T airspeed_stability = np_clip(M::div_by(airspeed - T(8), T(12)), T(0), T(1));
+    const T altitude_stability = np_clip(M::div_by(altitude - T(10), T(90)), T(0), T(1));
+    const T stability_score = M::div_by(roll_stability + pitch_stability + airspeed_stability + altitude_stability, T(4));
     const T r_stability = T(0.3) * stability_score;
     T osc = T(0);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const bool change = (np_sign(err[k]) != np_sign(e.prev_err[k])) && (M::abs(e.prev_err[k]) > T(0.01));
+        // (np.sign(err) != np.sign(prev_err)) and abs(prev_err) > 0.01, rewards.py:104-107.  The second condition makes prev_err
+        // a non-zero number, so its sign is +-1 and the first one says "err does not have that strict sign" (true for a zero
+        // or NaN err as well, as np.sign gives 0 / NaN there): err mirrored onto prev_err's side must not be positive.
+        const T mirrored = (e.prev_err[k] < T(0)) ? -err[k] : err[k];
+        const bool change = !(mirrored > T(0)) && (M::abs(e.prev_err[k]) > T(0.01));
         e.sign_changes[k] = T(0.9) * e.sign_changes[k] + (change ? T(1) : T(0));
         osc = osc + e.sign_changes[k];
         e.prev_err[k] = err[k];

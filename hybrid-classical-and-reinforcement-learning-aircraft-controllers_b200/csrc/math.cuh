@@ -39,6 +39,8 @@ template <> struct Math<double> {
     static __device__ __forceinline__ double log(double x) { return ::log(x); }
     static __device__ __forceinline__ double div(double a, double b) { return a / b; }
     static __device__ __forceinline__ double fdiv(double a, double b) { return a / b; }     // guidance-level quotients
+    static __device__ __forceinline__ double div_by(double a, double c) { return a / c; }   // division by a literal
+    static __device__ __forceinline__ double exp_neg(double x) { return ::exp(x); }         // exp of a non-positive argument
     static __device__ __forceinline__ double cos_bounded(double x) { return ::cos(x); }
     static __device__ __forceinline__ double abs(double x) { return ::fabs(x); }
     static __device__ __forceinline__ double fmod(double a, double b) { return ::fmod(a, b); }
@@ -147,6 +149,10 @@ template <> struct Math<float> {
     static __device__ __forceinline__ float div(float a, float b) { return a / b; }
     // quotients of the guidance levels (turn radii, blend factors, unit vectors): MUFU.RCP x multiply, 2 ulp
     static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+    // division by a literal: a multiplication by its reciprocal, folded at compile time (1 ulp from the quotient)
+    static __device__ __forceinline__ float div_by(float a, float c) { return a * (1.0f / c); }
+    // exp of a non-positive, bounded argument (the reward's stability terms): ex2.approx on x log2(e), 2 ulp
+    static __device__ __forceinline__ float exp_neg(float x) { return __expf(x); }
     // cosine of a clipped bank / heading-sized angle (|x| <= 2 pi): the SFU's cos.approx, abs err ~5e-7
     static __device__ __forceinline__ float cos_bounded(float x) { return __cosf(x); }
     static __device__ __forceinline__ float abs(float x) { return ::fabsf(x); }
