@@ -187,3 +187,84 @@ def test_mission_statistics_match_the_oracle(K, loop):
         for _ in range(50):
             f.step_waypoint(dt)
     assert torch.equal(a.state, b.state) and b.mission_stats_buf is None
+
+
+# fp32 build, ONE control step from the oracle's state (re-synchronised every step, controller memory included): what the
+# throughput build changes in the guidance levels -- angle wraps without fmod / sincos+atan2, MUFU quotients, the pure-pursuit
+# bearing taken as the waypoint bearing, the SFU cosine of the bank angle, the fused PID division -- is compared here with
+# the fp64 oracle on the command it issues, the surfaces, the controller memory and the state after the step.
+# Bars (x max(1, |value|)); measured worst on B200 in the comment.  Aircraft sitting on a discontinuity of the guidance law
+# (waypoint switch, 20 deg / turn-threshold tests: the oracle's own output moves by > 1e-4 when its state moves by one float
+# ulp) are excluded and counted.
+GUIDE_CMD_TOL = 4e-6        # heading (on the circle), speed, altitude command -- what the guidance shortcuts produce; measured 8.5e-7
+GUIDE_SURF_TOL = 1e-3       # elevator, aileron, rudder, throttle; measured 2.4e-4.  From here on the error is fp32 conditioning of the
+                            # cascade, not guidance: the TECS energies g h + V^2 / 2 are O(1e3), one float ulp of them is 1.2e-4, and
+                            # every PID level multiplies an input difference by ~10 through its derivative term (kd x 0.1 / dt)
+GUIDE_PID_TOL = 1.5e-3      # integral and previous-error words of the nine PIDs; measured 3.5e-4
+GUIDE_PID_DER_TOL = 8e-3    # their filtered-derivative words (the pitch-rate loop, three levels down, is the worst); measured 1.8e-3
+GUIDE_STATE_TOL = 1.5e-4    # position, velocity, attitude after the step (open loop, same surfaces: 5e-6 in test_gpu_parity_f32.py);
+                            # measured 3.9e-5
+GUIDE_RATE_TOL = 8e-4       # body rates after the step: the surfaces' difference x control power (up to 360 rad/s^2 per unit of
+                            # aileron at 30 m/s) x dt; measured 1.9e-4
+
+
+@pytest.mark.parametrize("guidance,gid", [("PP", 1), ("LOS", 0)])
+@pytest.mark.parametrize("dtp", [0.01, 0.001])                     # K = 1: one-aircraft kernel; K = 10: pair kernel
+def test_fp32_guidance_per_step_from_resynchronised_states(mods, guidance, gid, dtp):
+    torch, acb200, orc = mods
+    n, steps, dt, R = 4096, 120, 0.01, 40.0
+    rng = np.random.default_rng(21)
+    wps = np.array([[150.0, 0, -100.0, 15.0], [150.0, 150.0, -100.0, np.nan], [0, 150.0, -100.0, 18.0], [0, 0, -100.0, 15.0]])
+    ref = np.zeros((13, n))
+    ref[0] = rng.uniform(-100, 250, n); ref[1] = rng.uniform(-100, 250, n); ref[2] = -100 + rng.uniform(-10, 10, n)
+    ref[3] = rng.uniform(12, 25, n); ref[4] = rng.uniform(-1, 1, n); ref[5] = rng.uniform(-1, 1, n)
+    ref[6] = rng.uniform(-0.3, 0.3, n); ref[7] = rng.uniform(-0.15, 0.15, n); ref[8] = rng.uniform(-np.pi, np.pi, n)
+    ref[9:12] = rng.uniform(-0.2, 0.2, (3, n))
+    idx = rng.integers(0, 4, n).astype(np.int32)
+    pid = np.zeros((18, n), np.float32); outer = np.zeros((9, n), np.float32)
+    P, Cp = orc.default_aircraft_params(), orc.default_controller_params()
+    fleet = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dtp})
+    fleet.set_mission(wps, acceptance_radius=R, guidance=guidance, loop=True, stats=False)
+    surf = torch.zeros(4, n, device="cuda"); hc = torch.zeros(3, n, device="cuda")
+    rs, rh, rs2, rh2 = (np.zeros((k, n)) for k in (4, 3, 4, 3))
+    worst = np.zeros(6); excluded = 0; switched = 0
+
+    def rel(a, b):
+        return np.abs(a - b) / np.maximum(np.abs(b), 1.0)
+
+    for t in range(steps):
+        start32 = ref.astype(np.float32)
+        fleet.reset(_t(torch, start32))                       # state + derived; zeroes the controller memory ...
+        fleet.pid.copy_(_t(torch, pid)); fleet.pid_outer.copy_(_t(torch, outer)); fleet.wp_index.copy_(_t(torch, idx))   # ... so it goes in again
+        fleet.step_waypoint(dt, surfaces_out=surf, hsa_cmd_out=hc)
+        # the oracle's sensitivity: the same step from a state one float ulp away
+        pert = np.nextafter(start32, np.float32(np.inf)).astype(np.float64)
+        i2, p2, o2 = idx.copy(), pid.copy(), outer.copy()
+        orc.step_waypoint(P, Cp, pert, wps, i2, p2, o2, dt, guidance=gid, acceptance_radius=R, loop=True, dt_physics=dtp,
+                          surfaces_out=rs2, hsa_cmd_out=rh2)
+        ref = start32.astype(np.float64)
+        idx_before = idx.copy()
+        orc.step_waypoint(P, Cp, ref, wps, idx, pid, outer, dt, guidance=gid, acceptance_radius=R, loop=True, dt_physics=dtp,
+                          surfaces_out=rs, hsa_cmd_out=rh)
+        switched += int((idx != idx_before).sum())
+        dh2 = np.abs(np.angle(np.exp(1j * (rh2[0] - rh[0]))))
+        smooth = (i2 == idx) & (dh2 < 1e-4) & (np.abs(rh2[1] - rh[1]) < 1e-4) & (np.abs(rs2 - rs).max(axis=0) < 1e-3)
+        excluded += int((~smooth).sum())
+        got_h, got_s = hc.double().cpu().numpy(), surf.double().cpu().numpy()
+        assert np.array_equal(fleet.wp_index.cpu().numpy()[smooth], idx[smooth]), f"step {t + 1}: waypoint index"
+        e_cmd = np.maximum(np.abs(np.angle(np.exp(1j * (got_h[0] - rh[0])))), rel(got_h[1:], rh[1:]).max(axis=0))
+        e_surf = rel(got_s, rs).max(axis=0)
+        e_pid_rows = np.concatenate([rel(fleet.pid.double().cpu().numpy(), pid.astype(np.float64)),
+                                     rel(fleet.pid_outer.double().cpu().numpy(), outer.astype(np.float64))])
+        der = np.arange(27) % 3 == 2
+        e_pid, e_der = e_pid_rows[~der].max(axis=0), e_pid_rows[der].max(axis=0)
+        got_state = fleet.state.double().cpu().numpy()
+        e_state, e_rate = rel_err_cols(got_state[:9], ref[:9]), rel_err_cols(got_state[9:12], ref[9:12])
+        for k, (e, tol, name) in enumerate(((e_cmd, GUIDE_CMD_TOL, "HSA command"), (e_surf, GUIDE_SURF_TOL, "surfaces"),
+                                           (e_pid, GUIDE_PID_TOL, "controller memory"), (e_state, GUIDE_STATE_TOL, "state"),
+                                           (e_der, GUIDE_PID_DER_TOL, "filtered derivatives"), (e_rate, GUIDE_RATE_TOL, "body rates"))):
+            worst[k] = max(worst[k], float(e[smooth].max()))
+            assert (e[smooth] <= tol).all(), f"{guidance} dt_physics={dtp} step {t + 1}: {name} {e[smooth].max():.3e} > {tol}"
+    print(f"fp32 guidance per step ({guidance}, dt_physics={dtp}): command {worst[0]:.2e}, surfaces {worst[1]:.2e}, controller memory "
+          f"{worst[2]:.2e} / derivatives {worst[4]:.2e}, state {worst[3]:.2e} / rates {worst[5]:.2e}; {excluded} of {n * steps} aircraft-steps on a discontinuity, {switched} waypoint switches")
+    assert excluded <= 0.01 * n * steps and switched > 0
