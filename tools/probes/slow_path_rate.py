@@ -1,5 +1,7 @@
-"""How often does the pair substep fall back to the one-aircraft code?  Build with `make EXTRA=-DACB_SLOW_DBG`: every fallback
-then adds 1 to the nonfinite_repairs statistic (field 14)."""
+"""How often would a pair substep that TESTS the model's rarely-binding clamps fall back to the one-aircraft code?
+Belongs to profiles/experiments/r02_pair_substep_tests_instead_of_clamps.diff (not part of the shipped kernel): apply that
+diff, build with `make EXTRA=-DACB_SLOW_DBG` -- every fallback then adds 1 to the nonfinite_repairs statistic (field 14).
+Measured on the C3 workload: 0 in the first 200 steps, 4.3e-4 per pair-substep once episodes start to end in crashes."""
 import os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
