@@ -268,3 +268,52 @@ def test_fp32_guidance_per_step_from_resynchronised_states(mods, guidance, gid, 
     print(f"fp32 guidance per step ({guidance}, dt_physics={dtp}): command {worst[0]:.2e}, surfaces {worst[1]:.2e}, controller memory "
           f"{worst[2]:.2e} / derivatives {worst[4]:.2e}, state {worst[3]:.2e} / rates {worst[5]:.2e}; {excluded} of {n * steps} aircraft-steps on a discontinuity, {switched} waypoint switches")
     assert excluded <= 0.01 * n * steps and switched > 0
+
+
+@pytest.mark.parametrize("level", ["hsa", "waypoint"])
+@pytest.mark.parametrize("n", [4, 128, 132, 1000, 4100])
+def test_tma_staged_guided_step_is_bit_identical_to_the_direct_kernel(mods, level, n):
+    """fp32, K = 1: the guided step whose state / derived / controller-memory words travel through shared memory as 2-D TMA boxes
+    (step_guided_staged_kernel) against the kernel that addresses the fleet directly (ACB200_GUIDED_STAGED=0), every buffer
+    bit for bit -- whole blocks, a ragged last block that the TMA engine clips (132, 1000, 4100), a fleet smaller than a
+    block, and a finite mission in which aircraft finish at different steps (their columns go back as loaded)."""
+    torch, acb200, orc = mods
+    dt, steps = 0.01, 400
+    g = torch.Generator().manual_seed(5)
+    init = torch.zeros(13, n)
+    init[0].uniform_(-20, 20, generator=g); init[1].uniform_(-20, 20, generator=g); init[2] = -100.0
+    init[3] = 15.0; init[8].uniform_(-0.2, 0.2, generator=g)
+    cmd = torch.zeros(3, n)
+    cmd[0].uniform_(-1.0, 1.0, generator=g); cmd[1].uniform_(13, 18, generator=g); cmd[2].uniform_(80, 120, generator=g)
+    wps = [[25.0, 0.0, -100.0, 15.0], [50.0, 20.0, -100.0, 15.0]]
+    outs = []
+    for staged in ("1", "0"):
+        os.environ["ACB200_GUIDED_STAGED"] = staged
+        try:
+            fleet = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dt})
+            fleet.reset(init.cuda())
+            surf = torch.zeros(4, n, device="cuda"); hc = torch.zeros(3, n, device="cuda")
+            if level == "waypoint":
+                fleet.set_mission(wps, acceptance_radius=12.0, guidance="PP", loop=False)
+            c = cmd.cuda()
+            for _ in range(steps):
+                if level == "hsa":
+                    fleet.step_hsa(c, dt, surfaces_out=surf)
+                else:
+                    fleet.step_waypoint(dt, surfaces_out=surf, hsa_cmd_out=hc)
+            torch.cuda.synchronize()
+            bufs = [fleet.state, fleet.pid, fleet.pid_outer, fleet.controls, fleet.derived, surf, hc]
+            if level == "waypoint":
+                bufs += [fleet.wp_index, fleet.mission_stats_buf]
+            outs.append([t.cpu().numpy().copy() for t in bufs])
+        finally:
+            os.environ.pop("ACB200_GUIDED_STAGED", None)
+    names = ("state", "pid", "pid_outer", "controls", "derived", "surfaces", "hsa_cmd", "wp_index", "mission_stats")
+    for x, y, name in zip(outs[0], outs[1], names):
+        if name == "mission_stats":               # double atomics across blocks: the order of the additions is not fixed
+            assert np.allclose(x, y, rtol=1e-12, atol=0), name
+        else:
+            assert np.array_equal(x.view(np.uint8), y.view(np.uint8)), f"{level} n={n}: {name} differs in {(x != y).sum()} places"
+    assert np.isfinite(outs[0][0]).all() and np.ptp(outs[0][0][0]) > 1.0
+    if level == "waypoint" and n >= 128:
+        assert (outs[0][7] >= 2).any() and len(np.unique(outs[0][0][12][outs[0][7] >= 2])) > 1      # finished, at different times
