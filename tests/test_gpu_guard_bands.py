@@ -195,3 +195,37 @@ def test_gae_stays_inside_its_buffers(T, n):
     buf.compute_returns_and_advantage(torch.randn(n, generator=g).cuda(), (torch.rand(n, generator=g) < 0.1).cuda())
     _bands_intact(raws)
     assert torch.isfinite(buf.advantages).all() and torch.isfinite(buf.returns).all()
+
+
+@pytest.mark.parametrize("level", ["hsa", "waypoint"])
+@pytest.mark.parametrize("n,dtp", [(4, 0.01), (132, 0.01), (1000, 0.01), (4100, 0.01), (1002, 0.01), (1000, 0.001)])
+def test_guided_fleet_steps_stay_inside_their_buffers(level, n, dtp):
+    """Levels 2 and 1 on a fleet: K = 1 with the fleet a multiple of 4 takes the TMA-staged kernel (tensor stores of 128-aircraft
+    boxes: the engine must clip the ragged last block at n), 1002 the direct one-aircraft kernel, K = 10 the pair kernel."""
+    import acb200
+    fleet = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dtp})
+    raws = {}
+    for name in ("state", "controls", "derived", "pid", "pid_outer", "wp_index"):
+        view, raw = _rehome(getattr(fleet, name))
+        setattr(fleet, name, view)
+        raws[name] = raw
+        if name in ("state", "controls", "derived", "pid"):
+            setattr(fleet.c, name, view.data_ptr())
+    surf, raws["surfaces_out"] = _rehome(torch.zeros(4, n, device="cuda"))
+    hc, raws["hsa_cmd_out"] = _rehome(torch.zeros(3, n, device="cuda"))
+    g = torch.Generator().manual_seed(2)
+    init = torch.zeros(13, n)
+    init[0].uniform_(-20, 20, generator=g); init[1].uniform_(-20, 20, generator=g); init[2] = -100.0; init[3] = 15.0
+    fleet.reset(init.cuda())
+    _bands_intact(raws)
+    if level == "waypoint":
+        fleet.set_mission([[25.0, 0.0, -100.0, 15.0], [50.0, 20.0, -100.0, 15.0]], acceptance_radius=12.0, guidance="PP", loop=False)
+        assert fleet._mission.wp_index == fleet.wp_index.data_ptr()
+    cmd = torch.zeros(3, n, device="cuda"); cmd[1] = 15.0; cmd[2] = 100.0
+    for _ in range(60):
+        if level == "hsa":
+            fleet.step_hsa(cmd, 0.01, surfaces_out=surf)
+        else:
+            fleet.step_waypoint(0.01, surfaces_out=surf, hsa_cmd_out=hc)
+    _bands_intact(raws)
+    assert bool(torch.isfinite(fleet.state).all()) and float(fleet.state[12].max()) > 0.5      # the fleet really flew
