@@ -1,8 +1,9 @@
 """bench.py --workload c5: BASELINE.json configs[4] -- 2^20 aircraft per GPU flying a looping square mission
 (300 m side at 100 m altitude, 15 m/s, pure-pursuit guidance) through the full 5-level cascade
 (waypoint -> HSA/TECS -> attitude -> rate -> surface), dt = dt_physics = 0.01 (K = 1: ONE RK4 substep per control step),
-initial states jittered +-20 m / +-10 deg heading by global id.  One step = one launch of step_guided_kernel<float, 1>
-(at K = 1 the one-aircraft kernel is the faster one; the pair kernel takes over from K = 4)."""
+initial states jittered +-20 m / +-10 deg heading by global id.  One step = one launch of step_guided_staged_kernel<1>
+(at K = 1 the one-aircraft code with its arrays staged through shared memory as 2-D TMA boxes; the pair kernel takes over from
+K = 4; ACB200_GUIDED_STAGED=0 selects the direct kernel step_guided_kernel<float, 1>)."""
 from __future__ import annotations
 
 import json
@@ -14,7 +15,7 @@ UNIT = "env-steps/s"
 DT = 0.01
 SQUARE = [[300.0, 0.0, -100.0, 15.0], [300.0, 300.0, -100.0, 15.0], [0.0, 300.0, -100.0, 15.0], [0.0, 0.0, -100.0, 15.0]]
 # (+ 10 warp-reduced mission statistics per block: 80 B per 128 aircraft, not counted)
-# step_guided_kernel<T,1>: loads state 13 + derived 4 + pid 18 + pid_outer 9 + wp_index 1, stores state 13 + controls 4 +
+# step_guided_staged_kernel<1> / step_guided_kernel<T,1>: loads state 13 + derived 4 + pid 18 + pid_outer 9 + wp_index 1, stores state 13 + controls 4 +
 # derived 4 + pid 18 + pid_outer 9 + wp_index 1 (4-byte words, fp32 build)
 BYTES_PER_STEP = (13 + 4 + 18 + 9 + 1 + 13 + 4 + 4 + 18 + 9 + 1) * 4
 
@@ -136,7 +137,7 @@ def measure(args, rt, steps, warmup, e2e_steps, cpu_baseline, clocks=None):
         "config": {"workload": workload_name(n), "envs_per_gpu": n, "substeps": 1,
                    "l2": f"working set {n * BYTES_PER_STEP / 2 / 1e6:.0f} MB per step > 126 MB L2 (inputs larger than L2)",
                    "sharding": f"dp{world}: aircraft sharded by global id, no data-path collective"},
-        "roofline": {"bound": "hbm", "kernel": "step_guided_kernel<float,1>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "step_guided_kernel<float,1>" if os.environ.get("ACB200_GUIDED_STAGED", "1")[:1] == "0" else "step_guided_staged_kernel<1>", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "kernel_ms": ms / steps, "bytes_per_env_step": BYTES_PER_STEP,
                      "algorithmic_bytes_per_launch": BYTES_PER_STEP * n,
                      "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback", "traffic": traffic},
