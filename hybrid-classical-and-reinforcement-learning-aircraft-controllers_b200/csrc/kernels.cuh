@@ -486,13 +486,13 @@ step_guided_staged_kernel(const __grid_constant__ DynParams<float> P, const __gr
     }
 }
 
-// Tensor maps of a fleet's four staged arrays: encoded once per (arrays, size) and kept (the encoding is host arithmetic on
-// the pointer and the extents; no driver state is attached to it).
-static inline bool guided_maps_for(const FleetPtrs<float>& f, float* pid_outer, GuidedMaps* out) {
+// 2-D tensor map of a field-major float array [rows][n] with boxes of box_cols aircraft x all rows: encoded once per
+// (array, size, shape) and kept (the encoding is host arithmetic on the pointer and the extents; no driver state is attached).
+static inline bool cached_tensor_map(const void* base, int64_t n, uint32_t rows, uint32_t box_cols, CUtensorMap* out) {
     typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-    struct Entry { const void* p[4]; int64_t n; GuidedMaps maps; };
+    struct Entry { const void* base; int64_t n; uint32_t rows, box; CUtensorMap map; };
     static std::mutex mu;
     static std::vector<Entry> cache;
     static void* fn = nullptr;
@@ -500,28 +500,35 @@ static inline bool guided_maps_for(const FleetPtrs<float>& f, float* pid_outer, 
     std::lock_guard<std::mutex> lock(mu);
     if (unavailable) return false;
     for (const Entry& e : cache)
-        if (e.p[0] == f.state && e.p[1] == f.derived && e.p[2] == f.pid && e.p[3] == pid_outer && e.n == f.n) { *out = e.maps; return true; }
+        if (e.base == base && e.n == n && e.rows == rows && e.box == box_cols) { *out = e.map; return true; }
     if (!fn) {
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) { unavailable = true; return false; }
     }
-    Entry e{{f.state, f.derived, f.pid, pid_outer}, f.n, {}};
-    CUtensorMap* maps[4] = {&e.maps.state, &e.maps.derived, &e.maps.pid, &e.maps.outer};
-    const cuuint32_t rows[4] = {13, 4, ACB200_PID_FIELDS, 9};
-    for (int a = 0; a < 4; ++a) {
-        const cuuint64_t dims[2] = {(cuuint64_t)f.n, rows[a]};
-        const cuuint64_t strides[1] = {(cuuint64_t)f.n * sizeof(float)};
-        const cuuint32_t box[2] = {kBlock, rows[a]};
-        const cuuint32_t estr[2] = {1, 1};
-        if (((EncodeTiled)fn)(maps[a], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(e.p[a]), dims, strides, box, estr,
-                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-            return false;
-    }
-    if (cache.size() >= 64) cache.erase(cache.begin());
+    Entry e{base, n, rows, box_cols, {}};
+    const cuuint64_t dims[2] = {(cuuint64_t)n, rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)n * sizeof(float)};
+    const cuuint32_t box[2] = {box_cols, rows};
+    const cuuint32_t estr[2] = {1, 1};
+    if (((EncodeTiled)fn)(&e.map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+    if (cache.size() >= 256) cache.erase(cache.begin());
     cache.push_back(e);
-    *out = e.maps;
+    *out = e.map;
     return true;
+}
+// What every staged array must satisfy: 16-byte aligned base, row pitch a multiple of 16 bytes, 32-bit coordinates.
+static inline bool tma_stageable(const void* const* arrays, int count, int64_t n) {
+    if ((n & 3) != 0 || n >= (int64_t(1) << 31)) return false;
+    for (int a = 0; a < count; ++a)
+        if (!arrays[a] || ((uintptr_t)arrays[a] & 15)) return false;
+    return true;
+}
+static inline bool guided_maps_for(const FleetPtrs<float>& f, float* pid_outer, GuidedMaps* out) {
+    return cached_tensor_map(f.state, f.n, 13, kBlock, &out->state) && cached_tensor_map(f.derived, f.n, 4, kBlock, &out->derived) &&
+           cached_tensor_map(f.pid, f.n, ACB200_PID_FIELDS, kBlock, &out->pid) && cached_tensor_map(pid_outer, f.n, 9, kBlock, &out->outer);
 }
 
 // ---- env memory <-> registers ----------------------------------------------------------------------
@@ -948,8 +955,7 @@ cudaError_t Launch<T>::step_guided(const acb200_aircraft_params& ap, const acb20
         const char* staged_env = getenv("ACB200_GUIDED_STAGED");                // "0": the direct kernel (A/B runs, tests)
         const bool staged_off = staged_env && staged_env[0] == '0';
         const void* a16[] = {f.state, f.derived, f.pid, pid_outer};
-        bool ok = !staged_off && f.derived && (f.n & 3) == 0 && f.n < (int64_t(1) << 31);
-        for (const void* p : a16) ok = ok && (((uintptr_t)p & 15) == 0);
+        const bool ok = !staged_off && tma_stageable(a16, 4, f.n);
         GuidedMaps maps;
         if (ok && guided_maps_for(f, pid_outer, &maps)) {
             if (m)
