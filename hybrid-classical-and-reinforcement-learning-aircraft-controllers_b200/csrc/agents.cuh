@@ -158,8 +158,9 @@ __device__ __forceinline__ void waypoint_guidance(const CtrlParams<T>& C, int gu
     T heading_error = M::abs(heading_to_wp - heading);
     heading_error = M::abs(wrap_atan(heading_error));
     if (horizontal_distance < C.turn_threshold_distance && heading_error > C.turn_threshold_angle) {
-        const T reduction = C.max_speed_reduction * (T(1) - M::fdiv(horizontal_distance, C.turn_threshold_distance));
-        speed_cmd = speed_cmd * (T(1) - reduction);
+        // speed_cmd * (1 - reduction), reduction = max_speed_reduction * (1 - d / threshold)  (:224-227)
+        const T keep = M::mad(-C.max_speed_reduction, T(1) - M::fdiv(horizontal_distance, C.turn_threshold_distance), T(1));
+        speed_cmd = speed_cmd * keep;
         speed_cmd = py_max(speed_cmd, C.min_speed);
     }
     hsa[0] = heading_cmd; hsa[1] = speed_cmd; hsa[2] = -wp[2];

@@ -174,7 +174,7 @@ template <typename T> __device__ __forceinline__ void env_update_command(const E
         if (t < duration) {
             const T a = M::div(t, duration);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) e.rate_cmd[k] = (T(1) - a) * T(0) + a * e.sched[k];
+            for (int k = 0; k < 3; ++k) e.rate_cmd[k] = M::mad(a, e.sched[k], M::mul(T(1) - a, T(0)));
         } else {
 #pragma unroll
             for (int k = 0; k < 3; ++k) e.rate_cmd[k] = e.sched[k];
@@ -266,8 +266,8 @@ __device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<
     const T airspeed = e.d[0], altitude = e.d[1], roll = e.s[6], pitch = e.s[7];
 
     // RateTrackingReward.compute, rewards.py:48-137
-    const T tracking_error = M::div_by(M::sq(err[0]) + M::sq(err[1]) + M::sq(err[2]), T(3));
-    const T r_tracking = T(-0.5) * tracking_error;
+    const T tracking_error = M::div_by(M::mad(err[2], err[2], M::mad(err[1], err[1], M::sq(err[0]))), T(3));
+    const T r_tracking = M::mul(T(-0.5), tracking_error);
     T r_smoothness;
     if (e.step_count == 1 && M::kParity) {
         // first step: prev_action is the float64 array of rate_env.py:193 -> float64 arithmetic
@@ -288,7 +288,7 @@ __device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<
     const T airspeed_stability = np_clip(M::div_by(airspeed - T(8), T(12)), T(0), T(1));
     const T altitude_stability = np_clip(M::div_by(altitude - T(10), T(90)), T(0), T(1));
     const T stability_score = M::div_by(roll_stability + pitch_stability + airspeed_stability + altitude_stability, T(4));
-    const T r_stability = T(0.3) * stability_score;
+    const T r_stability = M::mul(T(0.3), stability_score);
     T osc = T(0);
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -297,11 +297,11 @@ __device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<
         // or NaN err as well, as np.sign gives 0 / NaN there): err mirrored onto prev_err's side must not be positive.
         const T mirrored = (e.prev_err[k] < T(0)) ? -err[k] : err[k];
         const bool change = !(mirrored > T(0)) && (M::abs(e.prev_err[k]) > T(0.01));
-        e.sign_changes[k] = T(0.9) * e.sign_changes[k] + (change ? T(1) : T(0));
+        e.sign_changes[k] = M::mad(T(0.9), e.sign_changes[k], change ? T(1) : T(0));
         osc = osc + e.sign_changes[k];
         e.prev_err[k] = err[k];
     }
-    const T r_oscillation = T(-0.1) * osc;
+    const T r_oscillation = M::mul(T(-0.1), osc);
     const T r_survival = T(1);
     T reward = r_tracking + r_smoothness + r_stability + r_oscillation + r_survival;
 
@@ -315,7 +315,7 @@ __device__ __forceinline__ void env_after_physics(const EnvConst<T>& E, EnvRegs<
             bool enough;
             if (M::kParity) { e.settle_timer += E.dt; enough = e.settle_timer >= T(0.2); }
             else { e.settle_timer += T(1); enough = e.settle_timer >= (T)E.settle_steps; }   // see DESIGN.md: fp64 timer rule
-            if (enough) { e.is_settled = 1; settle_reward = T(2) * E.dt; }
+            if (enough) { e.is_settled = 1; settle_reward = M::mul(T(2), E.dt); }
         } else {
             e.settle_timer = T(0);
             e.is_settled = 0;

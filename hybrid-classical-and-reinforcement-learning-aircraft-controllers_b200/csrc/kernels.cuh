@@ -203,7 +203,7 @@ __device__ __forceinline__ void mission_stats_one(const MissionPtrs<T>& M, int32
         const T len2 = Mt::mad(bx, bx, by * by), cross = Mt::mad(px, by, -(py * bx));
         if (len2 > T(1e-12)) ct = Mt::kParity ? Mt::abs(Mt::div(cross, Mt::sqrt(len2))) : Mt::abs(cross) * (T)rsqrtf((float)len2);
     }
-    ms[4] += ct; ms[5] += ct * ct;
+    ms[4] += ct; ms[5] = Mt::mad(ct, ct, ms[5]);
     ms[6] += Mt::abs(d[1] - (-wp[2]));               // |altitude - waypoint altitude|
     ms[7] += Mt::norm3(wp[0] - s[0], wp[1] - s[1], wp[2] - s[2]);
     ms[8] += d[0];                                   // airspeed
@@ -1042,6 +1042,8 @@ template <typename T> cudaError_t Launch<T>::kernel_info(const char* name, Kerne
     else if (!strcmp(name, "step_surface_pair") && sizeof(T) == 4) fn = (const void*)step_fleet_pair_kernel<0>;
     else if (!strcmp(name, "step_cascade_attitude_pair") && sizeof(T) == 4) fn = (const void*)step_fleet_pair_kernel<ACB200_LEVEL_ATTITUDE>;
 #endif
+    else if (!strcmp(name, "step_waypoint_staged") && sizeof(T) == 4) fn = (const void*)step_guided_staged_kernel<ACB200_LEVEL_WAYPOINT>;
+    else if (!strcmp(name, "step_hsa_staged") && sizeof(T) == 4) fn = (const void*)step_guided_staged_kernel<ACB200_LEVEL_HSA>;
     else if (!strcmp(name, "step_hsa")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_HSA>;
     else if (!strcmp(name, "step_waypoint")) fn = (const void*)step_guided_kernel<T, ACB200_LEVEL_WAYPOINT>;
     else if (!strcmp(name, "env_reset")) fn = (const void*)env_reset_kernel<T>;

@@ -5,7 +5,8 @@
 //                 contracts a*b+c.  The three places where the reference itself runs fused code (BLAS
 //                 ddot / dgemv behind np.linalg.norm and R @ v, see DESIGN.md "numpy semantics") use
 //                 explicit __fma_rn.
-//   Math<float>:  THROUGHPUT build.  FMA contraction on, short-range polynomial transcendentals.
+//   Math<float>:  THROUGHPUT build.  Fused multiply-adds where they are written (fmaf, mad), none added by the compiler
+//                 (-fmad=false as well); short-range polynomial transcendentals.
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
@@ -21,6 +22,7 @@ template <> struct Math<double> {
     static __device__ __forceinline__ double sq(double x) { return x * x; }  // numpy scalar x**2 (pow(x,2.0), 1 ulp)
     // a * b + c as the reference evaluates it: two roundings (this build is compiled with -fmad=false)
     static __device__ __forceinline__ double mad(double a, double b, double c) { return a * b + c; }
+    static __device__ __forceinline__ double mul(double a, double b) { return a * b; }      // a product that feeds a sum
     static __device__ __forceinline__ double norm3(double u, double v, double w) {
         return ::sqrt(__fma_rn(w, w, __fma_rn(v, v, u * u)));                // np.linalg.norm -> ddot, fused tail
     }
@@ -132,6 +134,8 @@ template <> struct Math<float> {
     // a * b + c, ALWAYS fused: the throughput build leaves no multiply-add to the compiler's contraction heuristics, so that
     // two kernels (one aircraft per thread / a pair per thread) that inline the same function round it the same way
     static __device__ __forceinline__ float mad(float a, float b, float c) { return fmaf(a, b, c); }
+    // a product that feeds a sum (or is stored AND summed): rounded on its own, never contracted into the addition
+    static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
     static __device__ __forceinline__ float norm3(float u, float v, float w) { return sqrtf(fmaf(w, w, fmaf(v, v, u * u))); }
     static __device__ __forceinline__ float norm2(float a, float b) { return sqrtf(fmaf(b, b, a * a)); }
     static __device__ __forceinline__ float row_dot3(float r0, float r1, float r2, float x0, float x1, float x2) {
@@ -148,7 +152,11 @@ template <> struct Math<float> {
     static __device__ __forceinline__ float log(float x) { return ::logf(x); }
     static __device__ __forceinline__ float div(float a, float b) { return a / b; }
     // quotients of the guidance levels (turn radii, blend factors, unit vectors): MUFU.RCP x multiply, 2 ulp
-    static __device__ __forceinline__ float fdiv(float a, float b) { return __fdividef(a, b); }
+    static __device__ __forceinline__ float fdiv(float a, float b) {
+        float r;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+        return __fmul_rn(a, r);                       // (explicitly rounded: 1 - fdiv(..) must not become one FFMA in one kernel and two instructions in another)
+    }
     // division by a literal: a multiplication by its reciprocal, folded at compile time (1 ulp from the quotient)
     static __device__ __forceinline__ float div_by(float a, float c) { return a * (1.0f / c); }
     // exp of a non-positive, bounded argument (the reward's stability terms): ex2.approx on x log2(e), 2 ulp
