@@ -202,22 +202,28 @@ __device__ __forceinline__ void env_step_pair_body(const DynParams<float>& P, co
         }
     }
 
-    // observations: float[n][18] row-major; the block's rows leave as one contiguous, coalesced run
+    // observations: float[n][18] row-major; the block's rows are one contiguous run of up to 18 KB, which ONE bulk copy of the
+    // TMA engine sends (cp.async.bulk shared -> global; rows is even, so the run is a multiple of 16 bytes and starts on one)
+    // instead of nine float4 load / store pairs per thread
+    const int64_t end = first + 2 * pairs;
+    const int64_t rows = (end - block_first < 2 * BLOCK) ? (end - block_first) : 2 * BLOCK;
+    const int count = (int)rows * ACB200_OBS_DIM;            // a multiple of 4
+    float* dst = B.obs + block_first * ACB200_OBS_DIM;
+    const bool bulk = ((uintptr_t)dst & 15) == 0;            // block-uniform
+    if (bulk) stagedetail::fence_async_smem();                // the rows written above, for the engine
     __syncthreads();
-    {
-        const int64_t end = first + 2 * pairs;
-        const int64_t rows = (end - block_first < 2 * BLOCK) ? (end - block_first) : 2 * BLOCK;
-        const int count = (int)rows * ACB200_OBS_DIM;        // rows is even: count is a multiple of 4
-        float* dst = B.obs + block_first * ACB200_OBS_DIM;
-        if (((uintptr_t)dst & 15) == 0) {
-            for (int k = threadIdx.x; k < count / 4; k += BLOCK)
-                reinterpret_cast<float4*>(dst)[k] = reinterpret_cast<const float4*>(stage)[k];
-        } else {
-            for (int k = threadIdx.x; k < count; k += BLOCK) dst[k] = stage[k];
+    if (bulk) {
+        if (threadIdx.x == 0 && count > 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(stagedetail::smem_u32(stage)),
+                         "r"((uint32_t)count * 4u) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
+    } else {
+        for (int k = threadIdx.x; k < count; k += BLOCK) dst[k] = stage[k];
     }
 
     if (B.stats) block_accumulate_env_stats<float, BLOCK>(st, B.stats);
+    if (bulk && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the stage must outlive the read
 }
 
 template <int BLOCK, int MIN_BLOCKS>
