@@ -317,3 +317,34 @@ def test_tma_staged_guided_step_is_bit_identical_to_the_direct_kernel(mods, leve
     assert np.isfinite(outs[0][0]).all() and np.ptp(outs[0][0][0]) > 1.0
     if level == "waypoint" and n >= 128:
         assert (outs[0][7] >= 2).any() and len(np.unique(outs[0][0][12][outs[0][7] >= 2])) > 1      # finished, at different times
+
+
+@pytest.mark.parametrize("level", ["hsa", "waypoint"])
+@pytest.mark.parametrize("dtp", [0.01, 0.001])
+def test_guided_step_without_the_derived_buffer_derives_the_same_values(mods, level, dtp):
+    """include/acb200.h: the HSA / waypoint steps read airspeed, altitude and heading from acb200_fleet.derived when the fleet has
+    that buffer and derive them from the state when it is NULL.  Both must give the same bits: the buffer holds what
+    derived_outputs(state) returns (K = 1: TMA-staged kernel against the direct one; K = 10: the pair kernel in both cases)."""
+    torch, acb200, orc = mods
+    n, dt = 1024, 0.01
+    g = torch.Generator().manual_seed(11)
+    init = torch.zeros(13, n)
+    init[0].uniform_(-20, 20, generator=g); init[1].uniform_(-20, 20, generator=g); init[2] = -100.0
+    init[3] = 15.0; init[8].uniform_(-0.2, 0.2, generator=g)
+    cmd = torch.zeros(3, n); cmd[0].uniform_(-1.0, 1.0, generator=g); cmd[1] = 15.0; cmd[2] = 100.0
+    outs = []
+    for with_derived in (True, False):
+        fleet = acb200.AircraftFleet(n, precision=32, config={"dt_physics": dtp})
+        fleet.reset(init.cuda())
+        if not with_derived:
+            fleet.c.derived = None
+        if level == "waypoint":
+            fleet.set_mission([[25.0, 0.0, -100.0, 15.0], [50.0, 20.0, -100.0, 15.0]], acceptance_radius=12.0, guidance="LOS", loop=True)
+        c = cmd.cuda()
+        for _ in range(200):
+            fleet.step_hsa(c, dt) if level == "hsa" else fleet.step_waypoint(dt)
+        torch.cuda.synchronize()
+        outs.append([t.cpu().numpy().copy() for t in (fleet.state, fleet.pid, fleet.pid_outer, fleet.controls, fleet.wp_index)])
+    for x, y, name in zip(outs[0], outs[1], ("state", "pid", "pid_outer", "controls", "wp_index")):
+        assert np.array_equal(x.view(np.uint8), y.view(np.uint8)), f"{level} dt_physics={dtp}: {name} differs in {(x != y).sum()} places"
+    assert np.ptp(outs[0][0][0]) > 1.0

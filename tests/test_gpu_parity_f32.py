@@ -170,7 +170,8 @@ def test_episode_statistics_match_fp64_build(mods):
 def test_kernel_resources():
     """Register budget of the throughput build: no spills, <= 128 registers (2 blocks of 128 x 4 per SM quarter)."""
     import acb200
-    for name in ("step_surface", "step_cascade_rate", "step_cascade_attitude", "env_step"):
+    for name in ("step_surface", "step_cascade_rate", "step_cascade_attitude", "env_step", "step_hsa", "step_waypoint",
+                 "step_hsa_staged", "step_waypoint_staged"):
         info = acb200.kernel_info(32, name)
         assert info["regs"] <= 128, (name, info)
 
